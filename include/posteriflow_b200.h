@@ -1,0 +1,208 @@
+/*
+ * posteriflow_b200.h -- C-ABI of the B200-native (sm_100a) posterior-flow hot path.
+ *
+ * This is the drop-in boundary for ONE path of bibinthomas123/PosteriFlow: the conditional
+ * masked-autoregressive rational-quadratic Neural Spline Flow behind LeanNPE sampling and NLL.
+ * The reference has no FFI layer of its own (it is pure Python/PyTorch over the third-party
+ * `nflows` package); each entry point below names the reference interface it replaces.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes, no torch / C++ types in any signature.
+ *   - every pointer is a DEVICE pointer on the device given at pf_flow_create, unless it is
+ *     marked [host]; all tensors are dense row-major float32 unless stated.
+ *   - the caller allocates every input, output and workspace buffer; the library owns only the
+ *     opaque packed-weights handle.  No call synchronises the stream except pf_flow_pack
+ *     (mask validation) and pf_flow_create/destroy.
+ *   - all work is enqueued on the given cudaStream_t (passed as void*; 0 = legacy default).
+ *   - return value: PF_OK (0) or a negative pf_status; never throws, never exits.
+ *   - one in-flight call per (handle, stream); handles are independent of each other.
+ *   - there is no CPU fallback: without a CUDA device every entry point returns PF_ERR_CUDA.
+ *
+ * Context addressing.  The flow is conditioned on a context row per flow row.  The reference
+ * materialises a repeated [R, C] tensor (lean_npe.py:328).  Here rows address contexts through
+ *     row2ctx != NULL : ctx row of flow row r is row2ctx[r]           (int64, device)
+ *     row2ctx == NULL : ctx row of flow row r is r / n_per_ctx         (n_per_ctx >= 1)
+ * so n_per_ctx = 1 is the reference's dense [R, C] form and n_per_ctx = N is "N posterior
+ * samples per event" with the context projected once per event.
+ */
+#ifndef POSTERIFLOW_B200_H
+#define POSTERIFLOW_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PF_ABI_VERSION 1
+
+typedef int32_t pf_status;
+enum {
+  PF_OK = 0,
+  PF_ERR_INVALID = -1,     /* bad argument / unsupported shape                         */
+  PF_ERR_CUDA = -2,        /* CUDA runtime error (see pf_last_cuda_error)              */
+  PF_ERR_NOT_PACKED = -3,  /* compute call before pf_flow_pack                          */
+  PF_ERR_WORKSPACE = -4,   /* workspace too small                                       */
+  PF_ERR_MASK = -5,        /* mask buffers differ from nflows' deterministic MADE masks */
+  PF_ERR_UNSUPPORTED = -6  /* valid request that this build has no kernel for           */
+};
+
+/* arithmetic tier of the conditioner GEMMs */
+enum {
+  PF_TIER_FP32 = 0, /* FP32 FMA everywhere: parity tier, |dtheta|,|dlogq| <= 1e-4 rel      */
+  PF_TIER_BF16 = 1  /* bf16 operands on tcgen05 tensor cores, fp32 accumulate + spline     */
+};
+
+/* flags for pf_flow_inverse / pf_flow_forward / pf_sample_fused */
+enum {
+  PF_FLAG_SANITIZE_CTX = 1u << 0, /* nan->0, +inf->1e-3, -inf->-1e-3 on ctx (flows.py:626-632)      */
+  PF_FLAG_CLAMP = 1u << 1,        /* nan_to_num(0,+1,-1) then clamp +-clamp_bound (flows.py:650-654) */
+  PF_FLAG_WRAP = 1u << 2,         /* ParamScaler.wrap (lean_npe.py:100-104)                          */
+  PF_FLAG_DENORMALIZE = 1u << 3,  /* ParamScaler.denormalize (lean_npe.py:111-114)                   */
+  PF_FLAG_CTX_IS_PROJ = 1u << 4,  /* `ctx` argument is already pf_flow_ctxproj output                */
+  PF_FLAG_SORT_MASSES = 1u << 5   /* m1 >= m2 on dims 0,1 of the output (pipeline.py:184-186)        */
+};
+
+/* workspace selectors for pf_flow_workspace_bytes */
+enum { PF_OP_CTXPROJ = 0, PF_OP_INVERSE = 1, PF_OP_FORWARD = 2, PF_OP_BACKWARD = 3, PF_OP_SAMPLE = 4 };
+
+typedef struct pf_flow pf_flow; /* opaque packed-weights handle */
+
+/* Shape of one NSFPosteriorFlow.  Replaces the constructor arguments at
+ * /root/reference/src/ahsd/models/flows.py:379-383 as used by lean_npe.py:285-295. */
+typedef struct pf_flow_desc {
+  int32_t features;         /* D: 11                                                 */
+  int32_t context_features; /* C: 288 = 256 encoder + 32 rank embedding              */
+  int32_t hidden_features;  /* H: 256                                                */
+  int32_t num_layers;       /* L: 10  ([ReversePermutation, MAF-RQS] pairs)          */
+  int32_t num_bins;         /* K: 16                                                 */
+  int32_t num_blocks;       /* residual blocks per MADE; only 2 is supported         */
+  float tail_bound;         /* 5.0  (spline domain, linear tails outside)            */
+  float clamp_bound;        /* 3.0  FLOW_NORM_BOUND, parameter_scalers.py:27         */
+  int32_t tier;             /* PF_TIER_*                                             */
+  int32_t device;           /* CUDA device ordinal                                   */
+} pf_flow_desc;
+
+/* Raw weights of ONE MADE conditioner in nflows' own layout and state-dict naming
+ * (`transform._transforms.{2l+1}.autoregressive_net.*`).  Masks may be
+ * NULL (nflows' deterministic masks are then assumed); if given they are checked against them. */
+typedef struct pf_layer_ptrs {
+  const float* initial_w;       /* initial_layer.weight  [H, D]  */
+  const float* initial_b;       /* initial_layer.bias    [H]     */
+  const float* initial_mask;    /* initial_layer.mask    [H, D]  */
+  const float* ctx_w;           /* context_layer.weight  [H, C]  */
+  const float* ctx_b;           /* context_layer.bias    [H]     */
+  const float* blk_ctx_w[2];    /* blocks.k.context_layer.weight [H, C] */
+  const float* blk_ctx_b[2];    /* blocks.k.context_layer.bias   [H]    */
+  const float* blk_lin_w[2][2]; /* blocks.k.linear_layers.j.weight [H, H] */
+  const float* blk_lin_b[2][2]; /* blocks.k.linear_layers.j.bias   [H]    */
+  const float* blk_lin_mask[2][2];
+  const float* final_w;         /* final_layer.weight [D*(3K-1), H] */
+  const float* final_b;         /* final_layer.bias   [D*(3K-1)]    */
+  const float* final_mask;
+} pf_layer_ptrs;
+
+/* Gradient destinations, same layout as pf_layer_ptrs (accumulated INTO: caller zeroes). */
+typedef struct pf_layer_grads {
+  float* initial_w;
+  float* initial_b;
+  float* ctx_w;
+  float* ctx_b;
+  float* blk_ctx_w[2];
+  float* blk_ctx_b[2];
+  float* blk_lin_w[2][2];
+  float* blk_lin_b[2][2];
+  float* final_w;
+  float* final_b;
+} pf_layer_grads;
+
+/* ParamScaler tensors (lean_npe.py:87-98), device pointers, D entries each. */
+typedef struct pf_scaler {
+  const float* lo;
+  const float* hi;
+  const uint8_t* log_mask;
+  const uint8_t* circ_mask;
+} pf_scaler;
+
+/* ---- lifetime ------------------------------------------------------------------------------ */
+
+/* Replaces NSFPosteriorFlow.__init__ (flows.py:379-548): allocates the packed-weight arena. */
+pf_status pf_flow_create(const pf_flow_desc* desc, pf_flow** out);
+void pf_flow_destroy(pf_flow* flow);
+
+/* Replaces the per-call `self.weight * self.mask` of nflows' MaskedLinear.forward and the
+ * implicit weight layout: masks are pre-multiplied, hidden units are sorted by autoregressive
+ * degree (block-triangular masks), transposed copies are made for the backward GEMMs and the
+ * sampler's per-degree weight blocks are laid out in streaming order.  Call again after every
+ * optimizer step / load_state_dict.  `layers` is a [host] array of L structs. */
+pf_status pf_flow_pack(pf_flow* flow, const pf_layer_ptrs* layers, void* stream);
+
+/* ---- context projection -------------------------------------------------------------------- */
+
+/* Replaces the three context Linear layers of every MADE (nflows MADE.context_layer and
+ * MaskedResidualBlock.context_layer, built at flows.py:511-524), evaluated ONCE per distinct
+ * context row instead of once per sample and per autoregressive pass:
+ *   proj[e, l, 0, :] = relu(Wc0_l ctx_e + b),  proj[e, l, 1|2, :] = sigmoid(Wc{1|2}_l ctx_e + b)
+ * proj is [E, L*3*H] float32, hidden units in the handle's packed (degree-sorted) order. */
+pf_status pf_flow_ctxproj(pf_flow* flow, const float* ctx, int64_t E, uint32_t flags, float* proj, void* stream);
+
+/* ---- sampling direction (z -> theta) -------------------------------------------------------- */
+
+/* Replaces NSFPosteriorFlow.inverse (flows.py:620-655) = CompositeTransform.inverse over
+ * nflows' 11-pass AutoregressiveTransform.inverse, computed incrementally (one conditioner
+ * pass of work per layer).  x [R, D]; logdet [R] or NULL (= sum over layers of -logabsdet,
+ * as the reference returns it).  flags: SANITIZE_CTX | CLAMP reproduce the reference method;
+ * WRAP | DENORMALIZE additionally fuse ParamScaler (scaler must then be non-NULL). */
+pf_status pf_flow_inverse(pf_flow* flow, const float* z, const float* ctx, const int64_t* row2ctx,
+                          int64_t n_per_ctx, int64_t R, int64_t E, float* x, float* logdet,
+                          uint32_t flags, const pf_scaler* scaler, void* workspace,
+                          size_t workspace_bytes, void* stream);
+
+/* Replaces LeanNPE.sample_posterior after the encoder (lean_npe.py:326-332): context broadcast,
+ * base noise, inverse, wrap, denormalize -> theta [E, n, D] in physical units, event-major.
+ * z == NULL draws the base noise in-kernel (Philox4x32-10 keyed by seed, counter = row index);
+ * z != NULL ([E*n, D]) reproduces the reference exactly for a given noise tensor.
+ * railed [E*n] (uint8) or NULL: pipeline.py:177 rail mask. */
+pf_status pf_sample_fused(pf_flow* flow, const float* ctx, const pf_scaler* scaler, const float* z,
+                          uint64_t seed, int64_t E, int64_t n, float* theta, float* logdet,
+                          uint8_t* railed, uint32_t flags, void* workspace, size_t workspace_bytes,
+                          void* stream);
+
+/* ---- density direction (theta -> z) and its backward ---------------------------------------- */
+
+/* Replaces NSFPosteriorFlow.forward (flows.py:610-618): z [R, D], logdet [R].
+ * nll != NULL additionally fuses compute_psd_aware_nll (flows.py:727-779) with the
+ * PSDScaledNormal base (flows.py:73-85); log_sigma [R, D] or NULL (= zeros, as LeanNPE passes).
+ * saved != NULL keeps the activations pf_flow_backward needs (pf_flow_saved_bytes(R, E)). */
+pf_status pf_flow_forward(pf_flow* flow, const float* x, const float* ctx, const int64_t* row2ctx,
+                          int64_t n_per_ctx, int64_t R, int64_t E, float* z, float* logdet,
+                          float* nll, const float* log_sigma, uint32_t flags, void* saved,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
+/* Replaces autograd through nflows for the density direction (loss.backward() at
+ * experiments/train_lean_npe.py:365).  Given gz [R, D] and glogdet [R] (either may be NULL = 0)
+ * accumulates weight grads into `grads` ([host] array of L structs, nflows layout, masked
+ * entries get zero gradient exactly as d(W*mask)/dW does) and writes gx [R, D] (or NULL) and
+ * gctx [E, C] (or NULL). */
+pf_status pf_flow_backward(pf_flow* flow, const void* saved, const float* ctx, const int64_t* row2ctx,
+                           int64_t n_per_ctx, int64_t R, int64_t E, const float* gz,
+                           const float* glogdet, float* gx, float* gctx, const pf_layer_grads* grads,
+                           void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- sizes / diagnostics -------------------------------------------------------------------- */
+
+size_t pf_flow_workspace_bytes(const pf_flow* flow, int32_t op, int64_t R, int64_t E);
+size_t pf_flow_saved_bytes(const pf_flow* flow, int64_t R, int64_t E);
+/* number of kernels the last call on this handle launched (bench.py's gpu_launches counter) */
+int64_t pf_flow_last_launch_count(const pf_flow* flow);
+/* hidden-unit permutation of the packed layout: perm[s] = nflows unit index at sorted slot s */
+pf_status pf_flow_hidden_perm(const pf_flow* flow, int32_t* perm_host /* [host] H entries */);
+const char* pf_status_str(pf_status s);
+const char* pf_last_cuda_error(void);
+int32_t pf_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* POSTERIFLOW_B200_H */
