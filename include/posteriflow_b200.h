@@ -34,6 +34,9 @@
 #ifdef __cplusplus
 extern "C" {
 #endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
 
 #define PF_ABI_VERSION 1
 
@@ -202,6 +205,9 @@ const char* pf_status_str(pf_status s);
 const char* pf_last_cuda_error(void);
 int32_t pf_abi_version(void);
 
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
 #ifdef __cplusplus
 }
 #endif

@@ -9,7 +9,7 @@
 
 #define PF_MAX_D 16      // autoregressive features supported by the kernels
 #define PF_MAX_BINS 32   // spline bins supported
-#define PF_KC 32         // k-rows per streamed weight chunk of the sampler
+#define PF_ROW_CHUNK 16384  // rows processed per pass of the FP32 tier (keeps activations L2-resident)
 
 namespace pf {
 
@@ -39,6 +39,23 @@ inline pf_status cuda_fail(cudaError_t e, const char* what, const char* file, in
 static inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
 static inline int64_t round_up64(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+// nflows' deterministic degrees (MaskedLinear._get_mask_and_degrees, random_mask=False).
+__host__ __device__ __forceinline__ int hidden_degree(int u, int D) {
+  int mx = D - 1 > 1 ? D - 1 : 1;
+  int mn = D - 1 < 1 ? D - 1 : 1;
+  return u % mx + mn;
+}
+enum MaskRule { RULE_NONE = 0, RULE_INITIAL = 1, RULE_HIDDEN = 2, RULE_FINAL = 3 };
+// mask[r][c] of a MaskedLinear in nflows' own (unsorted) index space
+__host__ __device__ __forceinline__ float rule_mask(int rule, int r, int c, int D, int MULT) {
+  switch (rule) {
+    case RULE_INITIAL: return hidden_degree(r, D) >= c + 1 ? 1.f : 0.f;
+    case RULE_HIDDEN: return hidden_degree(r, D) >= hidden_degree(c, D) ? 1.f : 0.f;
+    case RULE_FINAL: return (r / MULT + 1) > hidden_degree(c, D) ? 1.f : 0.f;
+    default: return 1.f;
+  }
+}
 
 // Row -> context-row addressing shared by every kernel (see header comment in the public .h).
 struct CtxMap {
@@ -80,8 +97,18 @@ struct pf_flow {
   float *WaT, *WbT;      // [L][2][H][H]
   float *WfT;            // [L][H][PLD]
   float *WctxT;          // [C][L*3H]   (all layers side by side: one GEMM for d(ctx))
-  // sampler stream: per layer, in consumption order, chunks of PF_KC k-rows
-  float* stream;         // [L][stream_layer_floats]
-  size_t stream_layer_floats;
-  int UH, UF;            // padded unit counts of a hidden-group block / a final (per-dim) block
+  float* W0T;            // [L][DP][H]  (d(x) through the initial layer)
+  // bf16 tensor-core tier (pf_tc.cu): per-layer streamed weight image, built by pf_flow_pack
+  void* tc_image;        // device, NULL when tier != PF_TIER_BF16
+  size_t tc_image_bytes;
+  int UF;                // padded per-dim parameter count (MULT rounded up to 4)
 };
+
+// bf16 tensor-core tier entry points (pf_tc.cu)
+pf_status pf_tc_pack(pf_flow* f, cudaStream_t st);
+pf_status pf_tc_inverse(pf_flow* f, cudaStream_t st, const float* z, uint64_t seed, const float* ctx,
+                        const int64_t* row2ctx, int64_t n_per_ctx, int64_t R, int64_t E, float* x, float* logdet,
+                        uint8_t* railed, uint32_t flags, const pf_scaler* scaler, void* workspace,
+                        size_t workspace_bytes);
+size_t pf_tc_workspace_bytes(const pf_flow* f, int64_t R, int64_t E);
+void pf_tc_destroy(pf_flow* f);

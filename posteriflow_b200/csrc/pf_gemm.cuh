@@ -8,36 +8,45 @@
 
 namespace pf {
 
-constexpr int NT_BM = 128, NT_BN = 64, NT_BK = 16, NT_THREADS = 256;
+constexpr int NT_BM = 128, NT_BK = 16, NT_THREADS = 256;
+enum { A_PLAIN = 0, A_RELU = 1, A_SANITIZE = 2 };  // transform applied to A on load
 
-template <class Epi, bool RELU_A>
+__device__ __forceinline__ float sanitize_ctx(float v) {  // flows.py:632 nan_to_num(nan=0, +inf=1e-3, -inf=-1e-3)
+  if (v != v) return 0.f;
+  if (isinf(v)) return v > 0.f ? 1e-3f : -1e-3f;
+  return v;
+}
+
+// BN = 64 (thread tile 8x4) or 32 (thread tile 8x2: the sampler's 26-unit degree groups)
+template <class Epi, int AMODE, int BN>
 __global__ void __launch_bounds__(NT_THREADS)
 sgemm_nt_kernel(const float* __restrict__ A, int lda, const float* __restrict__ B, int ldb, int M, int N, int K,
                 Epi epi) {
+  constexpr int TN = BN / 16;
   __shared__ __align__(16) float As[2][NT_BK][NT_BM + 4];
-  __shared__ __align__(16) float Bs[2][NT_BK][NT_BN + 4];
+  __shared__ __align__(16) float Bs[2][NT_BK][BN + 4];
   const int tid = threadIdx.x;
-  const int m0 = blockIdx.y * NT_BM, n0 = blockIdx.x * NT_BN;
+  const int m0 = blockIdx.y * NT_BM, n0 = blockIdx.x * BN;
   const int lk = tid & 15;   // k within tile for loads
   const int lr = tid >> 4;   // 0..15 row (stride 16) for loads
   const int ty = tid >> 4, tx = tid & 15;
 
-  float ra[8], rb[4];
-  float acc[8][4];
+  float ra[8], rb[TN];
+  float acc[8][TN];
 #pragma unroll
   for (int i = 0; i < 8; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
 
   auto gload = [&](int k0) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       int m = m0 + lr + 16 * i, k = k0 + lk;
       float v = (m < M && k < K) ? A[(int64_t)m * lda + k] : 0.f;
-      ra[i] = RELU_A ? fmaxf(v, 0.f) : v;
+      ra[i] = AMODE == A_RELU ? fmaxf(v, 0.f) : (AMODE == A_SANITIZE ? sanitize_ctx(v) : v);
     }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < TN; ++i) {
       int n = n0 + lr + 16 * i, k = k0 + lk;
       rb[i] = (n < N && k < K) ? B[(int64_t)n * ldb + k] : 0.f;
     }
@@ -46,7 +55,7 @@ sgemm_nt_kernel(const float* __restrict__ A, int lda, const float* __restrict__ 
 #pragma unroll
     for (int i = 0; i < 8; ++i) As[buf][lk][lr + 16 * i] = ra[i];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) Bs[buf][lk][lr + 16 * i] = rb[i];
+    for (int i = 0; i < TN; ++i) Bs[buf][lk][lr + 16 * i] = rb[i];
   };
 
   const int nk = (K + NT_BK - 1) / NT_BK;
@@ -60,13 +69,19 @@ sgemm_nt_kernel(const float* __restrict__ A, int lda, const float* __restrict__ 
     for (int k = 0; k < NT_BK; ++k) {
       float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 8]);
       float4 a1 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 8 + 4]);
-      float4 b = *reinterpret_cast<const float4*>(&Bs[buf][k][tx * 4]);
       const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-      const float bv[4] = {b.x, b.y, b.z, b.w};
+      float bv[TN];
+      if (TN == 4) {
+        float4 b = *reinterpret_cast<const float4*>(&Bs[buf][k][tx * 4]);
+        bv[0] = b.x; bv[1] = b.y; bv[TN - 2] = b.z; bv[TN - 1] = b.w;
+      } else {
+        float2 b = *reinterpret_cast<const float2*>(&Bs[buf][k][tx * 2]);
+        bv[0] = b.x; bv[1] = b.y;
+      }
 #pragma unroll
       for (int i = 0; i < 8; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
     }
     if (kt + 1 < nk) {
       sstore(buf ^ 1);
@@ -78,19 +93,20 @@ sgemm_nt_kernel(const float* __restrict__ A, int lda, const float* __restrict__ 
     int m = m0 + ty * 8 + i;
     if (m >= M) continue;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      int n = n0 + tx * 4 + j;
+    for (int j = 0; j < TN; ++j) {
+      int n = n0 + tx * TN + j;
       if (n < N) epi(m, n, acc[i][j]);
     }
   }
 }
 
-template <class Epi, bool RELU_A>
+template <class Epi, int AMODE, int BN>
 inline pf_status sgemm_nt(pf_flow* f, cudaStream_t st, const float* A, int lda, const float* B, int ldb, int M, int N,
                           int K, const Epi& epi) {
+  static_assert(BN == 64 || BN == 32, "tile");
   if (M <= 0 || N <= 0) return PF_OK;
-  dim3 grid((N + NT_BN - 1) / NT_BN, (M + NT_BM - 1) / NT_BM);
-  sgemm_nt_kernel<Epi, RELU_A><<<grid, NT_THREADS, 0, st>>>(A, lda, B, ldb, M, N, K, epi);
+  dim3 grid((N + BN - 1) / BN, (M + NT_BM - 1) / NT_BM);
+  sgemm_nt_kernel<Epi, AMODE, BN><<<grid, NT_THREADS, 0, st>>>(A, lda, B, ldb, M, N, K, epi);
   PF_LAUNCH_CHECK(f);
   return PF_OK;
 }

@@ -6,24 +6,6 @@
 namespace pf {
 thread_local char g_cuda_err[256] = "";
 
-// nflows' deterministic degrees (MaskedLinear._get_mask_and_degrees, random_mask=False).
-__host__ __device__ __forceinline__ int hidden_degree(int u, int D) {
-  int mx = D - 1 > 1 ? D - 1 : 1;
-  int mn = D - 1 < 1 ? D - 1 : 1;
-  return u % mx + mn;
-}
-
-enum MaskRule { RULE_NONE = 0, RULE_INITIAL = 1, RULE_HIDDEN = 2, RULE_FINAL = 3 };
-
-__device__ __forceinline__ float rule_mask(int rule, int r, int c, int D, int MULT) {
-  switch (rule) {
-    case RULE_INITIAL: return hidden_degree(r, D) >= c + 1 ? 1.f : 0.f;
-    case RULE_HIDDEN: return hidden_degree(r, D) >= hidden_degree(c, D) ? 1.f : 0.f;
-    case RULE_FINAL: return (r / MULT + 1) > hidden_degree(c, D) ? 1.f : 0.f;
-    default: return 1.f;
-  }
-}
-
 // dst[(transpose ? c : r) * dst_ld + (transpose ? r : c)] = src[rp, cp] * mask(rp, cp)
 // with rp = rperm ? rperm[r0 + r] : r0 + r, cp = cperm ? cperm[c] : c   (r < rows, c < cols)
 __global__ void pack_matrix_kernel(float* __restrict__ dst, int dst_ld, const float* __restrict__ src, int src_ld,
@@ -121,15 +103,7 @@ extern "C" pf_status pf_flow_create(const pf_flow_desc* d, pf_flow** out) {
   }
   for (int g = f->G + 1; g <= PF_MAX_D; ++g) f->off[g] = s;
   if (s != f->H) { delete[] f->perm_host; delete f; return PF_ERR_INVALID; }
-  f->UH = 4 * cdiv(f->max_group, 4);
   f->UF = round_up(f->MULT, 4);
-
-  size_t stream_layer = 0;
-  for (int dd = 1; dd <= f->D; ++dd) {
-    stream_layer += (size_t)cdiv(f->off[dd - 1], PF_KC) * PF_KC * f->UF;
-    if (dd <= f->G) stream_layer += (size_t)4 * cdiv(f->off[dd], PF_KC) * PF_KC * f->UH;
-  }
-  f->stream_layer_floats = stream_layer;
 
   const size_t L = f->L, H = f->H, C = f->C, PLD = f->PLD, DP = f->DP;
   size_t n = 0;
@@ -138,7 +112,7 @@ extern "C" pf_status pf_flow_create(const pf_flow_desc* d, pf_flow** out) {
   size_t oWa = take(L * 2 * H * H), oba = take(L * 2 * H), oWb = take(L * 2 * H * H), obb = take(L * 2 * H);
   size_t oWf = take(L * PLD * H), obf = take(L * PLD);
   size_t oWaT = take(L * 2 * H * H), oWbT = take(L * 2 * H * H), oWfT = take(L * H * PLD);
-  size_t oWctxT = take(C * L * 3 * H), ostream = take(L * stream_layer);
+  size_t oWctxT = take(C * L * 3 * H), oW0T = take(L * DP * H);
   f->arena_floats = n;
   cudaError_t e = cudaMalloc(&f->arena, n * sizeof(float));
   if (e == cudaSuccess) e = cudaMalloc(&f->d_perm, H * sizeof(int));
@@ -152,7 +126,7 @@ extern "C" pf_status pf_flow_create(const pf_flow_desc* d, pf_flow** out) {
   float* a = f->arena;
   f->W0 = a + oW0; f->b0 = a + ob0; f->Wctx = a + oWctx; f->bctx = a + obctx;
   f->Wa = a + oWa; f->ba = a + oba; f->Wb = a + oWb; f->bb = a + obb; f->Wf = a + oWf; f->bf = a + obf;
-  f->WaT = a + oWaT; f->WbT = a + oWbT; f->WfT = a + oWfT; f->WctxT = a + oWctxT; f->stream = a + ostream;
+  f->WaT = a + oWaT; f->WbT = a + oWbT; f->WfT = a + oWfT; f->WctxT = a + oWctxT; f->W0T = a + oW0T;
   *out = f;
   return PF_OK;
 }
@@ -184,6 +158,8 @@ extern "C" pf_status pf_flow_pack(pf_flow* f, const pf_layer_ptrs* layers, void*
     // initial layer [H][DP] sorted rows
     PF_TRY(pack_matrix(f, st, f->W0 + (size_t)l * H * DP, DP, w.initial_w, D, nullptr, RULE_INITIAL, H, D, 0, perm,
                        nullptr, 0));
+    PF_TRY(pack_matrix(f, st, f->W0T + (size_t)l * DP * H, H, w.initial_w, D, nullptr, RULE_INITIAL, H, D, 0, perm,
+                       nullptr, 1));
     PF_TRY(pack_vector(f, st, f->b0 + (size_t)l * H, w.initial_b, H, perm));
     // context layers: section 0 = MADE.context_layer, 1|2 = blocks.k.context_layer
     const float* cw[3] = {w.ctx_w, w.blk_ctx_w[0], w.blk_ctx_w[1]};
@@ -217,26 +193,6 @@ extern "C" pf_status pf_flow_pack(pf_flow* f, const pf_layer_ptrs* layers, void*
                        perm, 1));
     PF_TRY(pack_vector(f, st, f->bf + (size_t)l * PLD, w.final_b, P, nullptr));
 
-    // sampler stream for this layer, in consumption order (see pf_sampler.cu)
-    float* sp = f->stream + (size_t)l * f->stream_layer_floats;
-    for (int d = 1; d <= D; ++d) {
-      int Kf = f->off[d - 1];
-      // final block of dim d: dst[k][j] = Wf[(d-1)*MULT + j][slot k], k < Kf, j < MULT
-      PF_TRY(pack_matrix(f, st, sp, f->UF, w.final_w, H, nullptr, RULE_FINAL, f->MULT, Kf, (d - 1) * f->MULT,
-                         nullptr, perm, 1));
-      sp += (size_t)cdiv(Kf, PF_KC) * PF_KC * f->UF;
-      if (d <= f->G) {
-        int Kh = f->off[d], ng = f->off[d] - f->off[d - 1];
-        for (int s = 0; s < 4; ++s) {
-          const float* lw = w.blk_lin_w[s >> 1][s & 1];
-          // hidden block (group d, sublayer s): dst[k][u] = W[perm[off[d-1]+u]][perm[k]]
-          PF_TRY(pack_matrix(f, st, sp, f->UH, lw, H, nullptr, RULE_HIDDEN, ng, Kh, f->off[d - 1], perm, perm, 1));
-          sp += (size_t)cdiv(Kh, PF_KC) * PF_KC * f->UH;
-        }
-      }
-    }
-    if ((size_t)(sp - (f->stream + (size_t)l * f->stream_layer_floats)) != f->stream_layer_floats)
-      return PF_ERR_INVALID;
   }
   int flag = 0;
   PF_CUDA(cudaMemcpyAsync(&flag, f->d_flag, sizeof(int), cudaMemcpyDeviceToHost, st));

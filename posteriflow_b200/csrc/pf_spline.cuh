@@ -4,9 +4,13 @@
 // with +1e-6 on the last knot, forward / inverse map and log|det|, linear tails outside [-B, B].
 // Everything stays in registers: one (row, dim) per thread, parameters read through a functor.
 #pragma once
-#include <math_constants.h>
+#include <math.h>
 
 #include "pf_common.cuh"
+
+#ifndef PF_HD
+#define PF_HD __host__ __device__ __forceinline__
+#endif
 
 namespace pf {
 
@@ -15,7 +19,7 @@ constexpr float kMinDeriv = 1e-3f;       // DEFAULT_MIN_DERIVATIVE
 // np.log(np.exp(1 - 1e-3) - 1): the unnormalised derivative nflows pads at both ends
 constexpr float kEdgeLogit = 0.5397424172369522f;
 
-__device__ __forceinline__ float softplus_f(float x) {  // torch F.softplus, beta=1, threshold=20
+PF_HD float softplus_f(float x) {  // torch F.softplus, beta=1, threshold=20
   return x > 20.f ? x : log1pf(expf(x));
 }
 
@@ -28,9 +32,9 @@ struct RqsBin {
 // P(i) returns unnormalised parameter i of this (row, dim): [0,NB) widths, [NB,2NB) heights,
 // [2NB, 3NB-1) interior derivatives.
 template <int NB, bool INVERSE, class P>
-__device__ __forceinline__ RqsBin rqs_locate(const P& prm, float v, float B) {
+PF_HD RqsBin rqs_locate(const P& prm, float v, float B) {
   float ew[NB], eh[NB];
-  float mw = -CUDART_INF_F, mh = -CUDART_INF_F;
+  float mw = -INFINITY, mh = -INFINITY;
 #pragma unroll
   for (int i = 0; i < NB; ++i) {
     ew[i] = prm(i);
@@ -92,7 +96,7 @@ __device__ __forceinline__ RqsBin rqs_locate(const P& prm, float v, float B) {
 }
 
 // forward map inside [-B, B]: returns y, writes log|dy/dx|
-__device__ __forceinline__ float rqs_forward(const RqsBin& b, float x, float& lad) {
+PF_HD float rqs_forward(const RqsBin& b, float x, float& lad) {
   float s = b.hk / b.wk;
   float th = (x - b.xk) / b.wk;
   float tt = th * (1.f - th);
@@ -105,7 +109,7 @@ __device__ __forceinline__ float rqs_forward(const RqsBin& b, float x, float& la
 }
 
 // inverse map inside [-B, B]: returns x, writes -log|dy/dx| (the sign nflows returns)
-__device__ __forceinline__ float rqs_inverse(const RqsBin& b, float y, float& lad) {
+PF_HD float rqs_inverse(const RqsBin& b, float y, float& lad) {
   float s = b.hk / b.wk;
   float dy = y - b.yk;
   float t = b.dk + b.dk1 - 2.f * s;
@@ -127,13 +131,139 @@ __device__ __forceinline__ float rqs_inverse(const RqsBin& b, float y, float& la
 // One (row, dim) of MaskedPiecewiseRationalQuadraticAutoregressiveTransform._elementwise with
 // tails='linear'.
 template <int NB, bool INVERSE, class P>
-__device__ __forceinline__ float rqs_apply(const P& prm, float v, float B, float& lad) {
+PF_HD float rqs_apply(const P& prm, float v, float B, float& lad) {
   if (!(v >= -B && v <= B)) {  // outside (or NaN): identity, logdet 0
     lad = 0.f;
     return v;
   }
   RqsBin b = rqs_locate<NB, INVERSE>(prm, v, B);
   return INVERSE ? rqs_inverse(b, v, lad) : rqs_forward(b, v, lad);
+}
+
+
+// Reverse mode of the forward map (theta -> z direction) for ONE (row, dim): given the upstream
+// gradients gy (wrt the transformed value) and gl (wrt this dim's log|det|), writes the gradient
+// wrt each of the 3*NB-1 unnormalised parameters through G(i, value) and returns d/dx.
+// Follows exactly what autograd does through nflows' rational_quadratic_spline (Appendix A.7):
+// pinned end knots and the two padded edge derivatives carry no gradient; outside the tails the
+// map is the identity (gx = gy, no parameter gradient).
+template <int NB, class P, class GOut>
+PF_HD float rqs_forward_backward(const P& prm, float x, float B, float gy, float gl, const GOut& G) {
+  if (!(x >= -B && x <= B)) {
+#pragma unroll
+    for (int i = 0; i < 3 * NB - 1; ++i) G(i, 0.f);
+    return gy;
+  }
+  float pw[NB], ph[NB];
+  float mw = -INFINITY, mh = -INFINITY;
+#pragma unroll
+  for (int i = 0; i < NB; ++i) {
+    pw[i] = prm(i);
+    ph[i] = prm(NB + i);
+    mw = fmaxf(mw, pw[i]);
+    mh = fmaxf(mh, ph[i]);
+  }
+  float sw = 0.f, sh = 0.f;
+#pragma unroll
+  for (int i = 0; i < NB; ++i) {
+    pw[i] = expf(pw[i] - mw);
+    ph[i] = expf(ph[i] - mh);
+    sw += pw[i];
+    sh += ph[i];
+  }
+  const float scale = 1.f - kMinBin * NB;
+  const float rw = 1.f / sw, rh = 1.f / sh;
+  // knots along x (search axis) and the bin
+  int k = 0;
+  float xk = -B, wk = 0.f, yk = -B, hk = 0.f;
+  {
+    float cum = 0.f, prev = -B;
+#pragma unroll
+    for (int i = 0; i < NB; ++i) {
+      pw[i] *= rw;  // softmax probabilities from here on
+      cum += kMinBin + scale * pw[i];
+      float next = (i == NB - 1) ? B : (2.f * B) * cum + (-B);
+      if (i == 0 || x >= prev) { k = i; xk = prev; wk = next - prev; }
+      prev = next;
+    }
+    cum = 0.f; prev = -B;
+#pragma unroll
+    for (int i = 0; i < NB; ++i) {
+      ph[i] *= rh;
+      cum += kMinBin + scale * ph[i];
+      float next = (i == NB - 1) ? B : (2.f * B) * cum + (-B);
+      if (i == k) { yk = prev; hk = next - prev; }
+      prev = next;
+    }
+  }
+  float u0 = kEdgeLogit, u1 = kEdgeLogit;
+#pragma unroll
+  for (int i = 0; i < NB - 1; ++i) {
+    float u = prm(2 * NB + i);
+    if (i + 1 == k) u0 = u;
+    if (i == k) u1 = u;
+  }
+  const float dk = kMinDeriv + softplus_f(u0), dk1 = kMinDeriv + softplus_f(u1);
+
+  // forward intermediates
+  const float s = hk / wk;
+  const float th = (x - xk) / wk;
+  const float omt = 1.f - th;
+  const float tt = th * omt;
+  const float inner = s * th * th + dk * tt;
+  const float num = hk * inner;
+  const float cf = dk + dk1 - 2.f * s;
+  const float den = s + cf * tt;
+  const float Q = dk1 * th * th + 2.f * s * tt + dk * omt * omt;
+  const float dnum = s * s * Q;
+  // reverse
+  const float g_num = gy / den;
+  const float g_den = -gy * num / (den * den) - 2.f * gl / den;
+  const float g_dnum = gl / dnum;
+  const float g_Q = g_dnum * s * s;
+  float g_s = g_dnum * 2.f * s * Q + g_Q * 2.f * tt + g_den * (1.f - 2.f * tt) + g_num * hk * th * th;
+  float g_dk = g_Q * omt * omt + g_den * tt + g_num * hk * tt;
+  float g_dk1 = g_Q * th * th + g_den * tt;
+  float g_tt = g_Q * 2.f * s + g_den * cf + g_num * hk * dk;
+  float g_th = g_Q * (2.f * dk1 * th - 2.f * dk * omt) + g_num * hk * s * 2.f * th + g_tt * (1.f - 2.f * th);
+  float g_h = g_num * inner + g_s / wk;
+  float g_w = -g_th * th / wk - g_s * s / wk;
+  const float gx = g_th / wk;
+  const float g_xk = -g_th / wk;
+  const float g_yk = gy;
+  // knots -> cumulative sums.  cw_j = 2B * sum_{i<j} w_i - B for 0 < j < NB (ends pinned).
+  // bin k uses knots k (left) and k+1 (right): grad wrt knot k: g_xk - g_w ; knot k+1: g_w.
+  const float Gk = (k > 0) ? (g_xk - g_w) : 0.f;
+  const float Gk1 = (k + 1 < NB) ? g_w : 0.f;
+  const float Hk = (k > 0) ? (g_yk - g_h) : 0.f;
+  const float Hk1 = (k + 1 < NB) ? g_h : 0.f;
+  // g wrt normalised width i: 2B * (Gk [i < k] + Gk1 [i < k+1]); softmax backward
+  float dotw = 0.f, doth = 0.f;
+#pragma unroll
+  for (int i = 0; i < NB; ++i) {
+    float gw_i = (2.f * B) * ((i < k ? Gk : 0.f) + (i < k + 1 ? Gk1 : 0.f));
+    float gh_i = (2.f * B) * ((i < k ? Hk : 0.f) + (i < k + 1 ? Hk1 : 0.f));
+    dotw += gw_i * pw[i];
+    doth += gh_i * ph[i];
+  }
+#pragma unroll
+  for (int i = 0; i < NB; ++i) {
+    float gw_i = (2.f * B) * ((i < k ? Gk : 0.f) + (i < k + 1 ? Gk1 : 0.f));
+    float gh_i = (2.f * B) * ((i < k ? Hk : 0.f) + (i < k + 1 ? Hk1 : 0.f));
+    G(i, scale * pw[i] * (gw_i - dotw));
+    G(NB + i, scale * ph[i] * (gh_i - doth));
+  }
+  // softplus'(u) = sigmoid(u) (torch: 1 above the threshold of 20)
+  const float sg0 = u0 > 20.f ? 1.f : 1.f / (1.f + expf(-u0));
+  const float sg1 = u1 > 20.f ? 1.f : 1.f / (1.f + expf(-u1));
+#pragma unroll
+  for (int i = 0; i < NB - 1; ++i) {
+    float g = 0.f;
+    if (i + 1 == k) g += g_dk * sg0;
+    if (i == k) g += g_dk1 * sg1;
+    G(2 * NB + i, g);
+  }
+  return gx;
 }
 
 }  // namespace pf
