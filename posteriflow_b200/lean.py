@@ -1,0 +1,172 @@
+"""LeanNPE glue over the B200 flow: ParamScaler, rank embedding, fused sample_posterior / nll.
+
+Mirrors /root/reference/src/ahsd/models/lean_npe.py:48-114 (ParamScaler) and :255-338 (LeanNPE) for
+the part of the model on the hot path.  The strain encoder (lean_npe.py:131-252,
+coherent_encoder.py) is NOT part of this package: it stays the reference's PyTorch module and is
+passed in (`LeanNPE(encoder=...)`), or an existing reference model is converted in place with
+`accelerate(model)`.
+"""
+from __future__ import annotations
+
+import math
+import types
+from typing import List, Optional
+
+import torch
+from torch import Tensor, nn
+
+from . import _cabi as A
+from .flow import NSFPosteriorFlow
+
+PARAM_NAMES = ["mass_1", "mass_2", "luminosity_distance", "ra", "dec", "theta_jn", "psi", "phase",
+               "geocent_time", "a1", "a2"]  # lean_npe.py:41-46
+
+
+class ParamScaler:
+    """Fixed invertible map physical <-> [-1, 1] (lean_npe.py:48-114); same attributes and methods."""
+
+    RANGES = {
+        "mass_1": (1.0, 105.0, True), "mass_2": (1.0, 105.0, True),
+        "luminosity_distance": (40.0, 2200.0, True),
+        "ra": (0.0, 2 * math.pi, False), "dec": (-math.pi / 2, math.pi / 2, False),
+        "theta_jn": (0.0, math.pi, False), "psi": (0.0, math.pi, False),
+        "phase": (0.0, 2 * math.pi, False), "geocent_time": (-1.6, 1.6, False),
+        "a1": (0.0, 1.0, False), "a2": (0.0, 1.0, False),
+    }
+    CIRCULAR = ("ra", "phase", "psi")
+
+    def __init__(self, param_names: List[str] = PARAM_NAMES, premerger: bool = False):
+        self.param_names, self.premerger = param_names, premerger
+        rows = []
+        for p in param_names:
+            lo, hi, is_log = self.RANGES[p]
+            if premerger and p == "geocent_time":
+                lo, hi = -1.6, 5.2
+            rows.append((math.log(lo), math.log(hi), True) if is_log else (lo, hi, False))
+        self.lo = torch.tensor([r[0] for r in rows], dtype=torch.float32)
+        self.hi = torch.tensor([r[1] for r in rows], dtype=torch.float32)
+        self.log_mask = torch.tensor([r[2] for r in rows], dtype=torch.bool)
+        self.circ_mask = torch.tensor([p in self.CIRCULAR for p in param_names], dtype=torch.bool)
+
+    def to(self, device):
+        for k in ("lo", "hi", "log_mask", "circ_mask"):
+            setattr(self, k, getattr(self, k).to(device))
+        return self
+
+    def wrap(self, y: Tensor) -> Tensor:
+        return torch.where(self.circ_mask, torch.remainder(y + 1.0, 2.0) - 1.0, y.clamp(-1.0, 1.0))
+
+    def normalize(self, x: Tensor) -> Tensor:
+        x = torch.where(self.log_mask, torch.log(x.clamp_min(1e-6)), x)
+        return (2 * (x - self.lo) / (self.hi - self.lo) - 1).clamp(-1.0, 1.0)
+
+    def denormalize(self, y: Tensor) -> Tensor:
+        x = (y.clamp(-1.0, 1.0) + 1) / 2 * (self.hi - self.lo) + self.lo
+        return torch.where(self.log_mask, torch.exp(x), x)
+
+
+SAMPLE_FLAGS = A.PF_FLAG_SANITIZE_CTX | A.PF_FLAG_CLAMP | A.PF_FLAG_WRAP | A.PF_FLAG_DENORMALIZE
+
+
+def sample_fused(flow: NSFPosteriorFlow, scaler: ParamScaler, ctx_full: Tensor, n_samples: int,
+                 z: Optional[Tensor] = None, seed: int = 0, flags: int = SAMPLE_FLAGS):
+    """lean_npe.py:326-332 in one C-ABI call: (theta [E, n, D] physical, logdet [E*n], railed [E*n]).
+    The context is NOT repeated: row e of `ctx_full` serves samples [e*n, (e+1)*n)."""
+    fh = flow.handle()
+    with torch.no_grad():
+        return torch.ops.posteriflow.nsf_sample_fused(ctx_full, z, int(seed), int(n_samples), fh.id, int(flags),
+                                                      scaler.lo, scaler.hi, scaler.log_mask, scaler.circ_mask)
+
+
+class LeanNPE(nn.Module):
+    """encoder (caller's PyTorch module) + rank embedding + B200 flow (lean_npe.py:255-338).
+
+    `encoder(strain[, asd_bands]) -> [B, context_dim]`.  `encoder=None` builds a flow head that must be
+    given `context=` explicitly (cached-context training, frozen_context_heads.py)."""
+
+    def __init__(self, param_names: List[str] = PARAM_NAMES, context_dim: int = 256, rank_dim: int = 32,
+                 max_signals: int = 5, flow_layers: int = 10, flow_hidden: int = 256, flow_bins: int = 16,
+                 premerger: bool = False, psd_cond: bool = False, encoder: Optional[nn.Module] = None,
+                 tier: str = "fp32"):
+        super().__init__()
+        self.param_names, self.max_signals, self.context_dim = param_names, max_signals, context_dim
+        self.psd_cond = psd_cond
+        self.scaler = ParamScaler(param_names, premerger=premerger)
+        self.encoder = encoder
+        self.rank_embed = nn.Embedding(max_signals, rank_dim)
+        self.flow = NSFPosteriorFlow(features=len(param_names), context_features=context_dim + rank_dim,
+                                     hidden_features=flow_hidden, num_layers=flow_layers, num_bins=flow_bins,
+                                     tail_bound=5.0, dropout=0.0, temperature_scale=1.0, use_masked_context=False,
+                                     tier=tier)
+        self.flow.temperature.requires_grad_(False)
+        self.sample_seed = 0
+
+    def _full_context(self, context: Tensor, rank: Tensor) -> Tensor:
+        return torch.cat([context, self.rank_embed(rank)], dim=1)
+
+    def encode(self, strain: Tensor, asd_bands: Optional[Tensor] = None) -> Tensor:
+        if self.encoder is None:
+            raise RuntimeError("this LeanNPE was built without an encoder: pass context= explicitly")
+        return self.encoder(strain, asd_bands) if self.psd_cond else self.encoder(strain)
+
+    def nll(self, strain: Optional[Tensor], params_phys: Tensor, rank: Tensor, context: Optional[Tensor] = None,
+            asd_bands: Optional[Tensor] = None) -> Tensor:
+        if context is None:
+            context = self.encode(strain, asd_bands)
+        ctx = self._full_context(context, rank)
+        y = self.scaler.normalize(params_phys)
+        return self.flow.compute_psd_aware_nll(y, ctx, None)
+
+    @torch.no_grad()
+    def sample_posterior(self, strain: Optional[Tensor], rank: int = 0, n_samples: int = 256,
+                         asd_bands: Optional[Tensor] = None, context: Optional[Tensor] = None,
+                         z: Optional[Tensor] = None) -> Tensor:
+        """[B, n_samples, D] physical samples, event-major.  `z` ([B*n, D]) fixes the base noise (parity);
+        otherwise it is drawn in-kernel (Philox keyed by an internal counter seeded from torch's RNG)."""
+        if context is None:
+            context = self.encode(strain, asd_bands)
+        B = context.shape[0]
+        r = torch.full((B,), rank, dtype=torch.long, device=context.device)
+        ctx = self._full_context(context, r)
+        if z is None:
+            seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        else:
+            seed = 0
+        theta, _, _ = sample_fused(self.flow, self.scaler, ctx, n_samples, z=z, seed=seed)
+        return theta
+
+    def to(self, *args, **kwargs):
+        out = super().to(*args, **kwargs)
+        self.scaler.to(next(self.parameters()).device)
+        return out
+
+
+def accelerate(model: nn.Module, tier: str = "fp32") -> nn.Module:
+    """Convert a *reference* `ahsd.models.lean_npe.LeanNPE` in place: its nflows-backed `flow` is
+    replaced by the B200 flow holding the same weights (strict state-dict load) and `sample_posterior`
+    is rebound to the fused, context-broadcasting path.  Every other attribute (encoder, rank_embed,
+    scaler, nll, encode) is untouched, so all reference call sites keep working."""
+    old = model.flow
+    dev = next(old.parameters()).device
+    new = NSFPosteriorFlow(features=old.features, context_features=old.context_features,
+                           hidden_features=old.transform._transforms[1].autoregressive_net.final_layer.weight.shape[1],
+                           num_layers=old.num_layers,
+                           num_bins=(old.transform._transforms[1].autoregressive_net.final_layer.weight.shape[0]
+                                     // old.features + 1) // 3,
+                           tail_bound=float(old.tail_bounds_list[0]), dropout=0.0,
+                           temperature_scale=float(old.temperature.detach()), use_masked_context=False, tier=tier)
+    new.load_state_dict(old.state_dict(), strict=True)
+    new.temperature.requires_grad_(old.temperature.requires_grad)
+    model.flow = new.to(dev)
+
+    @torch.no_grad()
+    def sample_posterior(self, strain, rank: int = 0, n_samples: int = 256, asd_bands=None, z=None):
+        context = self.encode(strain, asd_bands)
+        B = context.shape[0]
+        r = torch.full((B,), rank, dtype=torch.long, device=context.device)
+        ctx = self._full_context(context, r)
+        seed = 0 if z is not None else int(torch.randint(0, 2 ** 62, (1,)).item())
+        return sample_fused(self.flow, self.scaler, ctx, n_samples, z=z, seed=seed)[0]
+
+    model.sample_posterior = types.MethodType(sample_posterior, model)
+    return model

@@ -1,0 +1,330 @@
+"""torch.library custom ops `posteriflow::*` over the C-ABI.
+
+PyTorch is plumbing here: it owns device memory and the current CUDA stream; every op body is one
+call into libposteriflow_b200.so.  There is no eager / CPU fallback: CPU tensors raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import weakref
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+from torch import Tensor
+
+from . import _cabi as A
+
+# per-layer tensor order of the flat `weights` list handed to the ops (nflows state-dict names,
+# relative to `transform._transforms.{2l+1}.autoregressive_net.`)
+LAYER_KEYS = [
+    "initial_layer.weight", "initial_layer.bias",
+    "context_layer.weight", "context_layer.bias",
+    "blocks.0.context_layer.weight", "blocks.0.context_layer.bias",
+    "blocks.1.context_layer.weight", "blocks.1.context_layer.bias",
+    "blocks.0.linear_layers.0.weight", "blocks.0.linear_layers.0.bias",
+    "blocks.0.linear_layers.1.weight", "blocks.0.linear_layers.1.bias",
+    "blocks.1.linear_layers.0.weight", "blocks.1.linear_layers.0.bias",
+    "blocks.1.linear_layers.1.weight", "blocks.1.linear_layers.1.bias",
+    "final_layer.weight", "final_layer.bias",
+]
+NW = len(LAYER_KEYS)
+
+_HANDLES: Dict[int, "FlowHandle"] = {}
+_NEXT_ID = [1]
+
+
+def _ptr(t: Optional[Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _require_cuda(*ts: Tensor) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("posteriflow_b200 ops run on CUDA (sm_100a) only; there is no CPU fallback")
+
+
+def _f32c(t: Tensor) -> Tensor:
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t if t.is_contiguous() else t.contiguous()
+
+
+class FlowHandle:
+    """Owns one `pf_flow*` (packed weights of one NSFPosteriorFlow on one device)."""
+
+    def __init__(self, features: int, context_features: int, hidden_features: int, num_layers: int,
+                 num_bins: int, tail_bound: float, clamp_bound: float, tier: int, device: torch.device):
+        self.lib = A.load_library()
+        if device.type != "cuda":
+            raise RuntimeError("posteriflow_b200 needs a CUDA device; there is no CPU fallback")
+        self.device = device
+        self.index = device.index if device.index is not None else torch.cuda.current_device()
+        self.shape = (features, context_features, hidden_features, num_layers, num_bins)
+        self.tier = tier
+        desc = A.FlowDesc(features, context_features, hidden_features, num_layers, num_bins, 2,
+                          float(tail_bound), float(clamp_bound), tier, self.index)
+        h = C.c_void_p()
+        A.check(self.lib.pf_flow_create(C.byref(desc), C.byref(h)), "pf_flow_create")
+        self.h = h
+        self.pack_key = None
+        self.id = _NEXT_ID[0]
+        _NEXT_ID[0] += 1
+        _HANDLES[self.id] = self
+        self.launches = 0
+        weakref.finalize(self, FlowHandle._destroy, self.lib, h, self.id)
+
+    @staticmethod
+    def _destroy(lib, h, hid):
+        _HANDLES.pop(hid, None)
+        try:
+            lib.pf_flow_destroy(h)
+        except Exception:
+            pass
+
+    # -- packing ---------------------------------------------------------------------------------
+    def ensure_packed(self, weights: Sequence[Tensor]) -> None:
+        key = tuple((w.data_ptr(), w._version) for w in weights)
+        if key == self.pack_key:
+            return
+        self.pack(weights)
+        self.pack_key = key
+
+    def pack(self, weights: Sequence[Tensor], masks: Optional[Sequence[Dict[str, Tensor]]] = None) -> None:
+        L = self.shape[3]
+        if len(weights) != NW * L:
+            raise ValueError(f"expected {NW * L} weight tensors, got {len(weights)}")
+        keep = [_f32c(w.detach()) for w in weights]
+        _require_cuda(*keep)
+        arr = (A.LayerPtrs * L)()
+        for l in range(L):
+            w = keep[l * NW:(l + 1) * NW]
+            p = arr[l]
+            p.initial_w, p.initial_b, p.ctx_w, p.ctx_b = _ptr(w[0]), _ptr(w[1]), _ptr(w[2]), _ptr(w[3])
+            p.blk_ctx_w[0], p.blk_ctx_b[0], p.blk_ctx_w[1], p.blk_ctx_b[1] = (_ptr(w[4]), _ptr(w[5]), _ptr(w[6]),
+                                                                              _ptr(w[7]))
+            for k in range(2):
+                for j in range(2):
+                    p.blk_lin_w[k][j] = _ptr(w[8 + 4 * k + 2 * j])
+                    p.blk_lin_b[k][j] = _ptr(w[9 + 4 * k + 2 * j])
+            p.final_w, p.final_b = _ptr(w[16]), _ptr(w[17])
+            if masks is not None:
+                m = masks[l]
+                mk = {k: _f32c(v) for k, v in m.items()}
+                keep.extend(mk.values())
+                p.initial_mask = _ptr(mk.get("initial"))
+                p.final_mask = _ptr(mk.get("final"))
+                for k in range(2):
+                    for j in range(2):
+                        p.blk_lin_mask[k][j] = _ptr(mk.get(f"hidden{k}{j}"))
+        with torch.cuda.device(self.index):
+            A.check(self.lib.pf_flow_pack(self.h, arr, _stream()), "pf_flow_pack")
+        self._note_launches()
+
+    def _note_launches(self) -> None:
+        self.launches += int(self.lib.pf_flow_last_launch_count(self.h))
+
+    def hidden_perm(self) -> List[int]:
+        buf = (C.c_int32 * self.shape[2])()
+        A.check(self.lib.pf_flow_hidden_perm(self.h, buf), "pf_flow_hidden_perm")
+        return list(buf)
+
+    def workspace(self, op: int, R: int, E: int) -> Tensor:
+        n = int(self.lib.pf_flow_workspace_bytes(self.h, op, R, E))
+        return torch.empty(max(n, 256), dtype=torch.uint8, device=self.device)
+
+    def saved_bytes(self, R: int, E: int) -> int:
+        return int(self.lib.pf_flow_saved_bytes(self.h, R, E))
+
+
+def get_handle(hid: int) -> FlowHandle:
+    try:
+        return _HANDLES[hid]
+    except KeyError:
+        raise RuntimeError(f"posteriflow_b200: unknown flow handle {hid}") from None
+
+
+def _rows(x: Tensor, ctx: Tensor, n_per_ctx: int) -> Tuple[int, int]:
+    R, E = x.shape[0], ctx.shape[0]
+    if n_per_ctx < 1 or (R > 0 and (R - 1) // n_per_ctx >= E):
+        raise ValueError(f"context rows ({E}) do not cover {R} flow rows at {n_per_ctx} rows per context")
+    return R, E
+
+
+# ------------------------------------------------------------------------------------------------
+# density direction
+# ------------------------------------------------------------------------------------------------
+@torch.library.custom_op("posteriflow::nsf_forward", mutates_args=())
+def nsf_forward(x: Tensor, ctx: Tensor, weights: Sequence[Tensor], handle: int, n_per_ctx: int,
+                save: bool) -> Tuple[Tensor, Tensor, Tensor]:
+    """NSFPosteriorFlow.forward (flows.py:610-618): (z [R,D], logdet [R], saved activations)."""
+    _require_cuda(x, ctx)
+    fh = get_handle(handle)
+    x, ctx = _f32c(x), _f32c(ctx)
+    R, E = _rows(x, ctx, n_per_ctx)
+    z = torch.empty_like(x)
+    logdet = torch.empty(R, dtype=torch.float32, device=x.device)
+    saved = torch.empty(fh.saved_bytes(R, E) if save else 0, dtype=torch.uint8, device=x.device)
+    ws = fh.workspace(A.PF_OP_FORWARD, R, E)
+    with torch.cuda.device(fh.index):
+        A.check(fh.lib.pf_flow_forward(fh.h, x.data_ptr(), ctx.data_ptr(), None, n_per_ctx, R, E, z.data_ptr(),
+                                       logdet.data_ptr(), None, None, 0, saved.data_ptr() if save else None,
+                                       ws.data_ptr(), ws.numel(), _stream()), "pf_flow_forward")
+    fh._note_launches()
+    return z, logdet, saved
+
+
+@nsf_forward.register_fake
+def _(x, ctx, weights, handle, n_per_ctx, save):
+    return torch.empty_like(x), x.new_empty(x.shape[0]), x.new_empty(0, dtype=torch.uint8)
+
+
+@torch.library.custom_op("posteriflow::nsf_backward", mutates_args=())
+def nsf_backward(saved: Tensor, ctx: Tensor, gz: Tensor, glogdet: Tensor, weights: Sequence[Tensor], handle: int,
+                 n_per_ctx: int) -> List[Tensor]:
+    """Backward of nsf_forward: [gx, gctx, *gweights] (weights in the nflows layout, masked entries zero)."""
+    _require_cuda(saved, ctx, gz, glogdet)
+    fh = get_handle(handle)
+    ctx, gz, glogdet = _f32c(ctx), _f32c(gz), _f32c(glogdet)
+    R, E = _rows(gz, ctx, n_per_ctx)
+    L = fh.shape[3]
+    gx = torch.zeros_like(gz)
+    gctx = torch.zeros_like(ctx)
+    gws = [torch.zeros(w.shape, dtype=torch.float32, device=gz.device) for w in weights]
+    arr = (A.LayerGrads * L)()
+    for l in range(L):
+        g = gws[l * NW:(l + 1) * NW]
+        p = arr[l]
+        p.initial_w, p.initial_b, p.ctx_w, p.ctx_b = _ptr(g[0]), _ptr(g[1]), _ptr(g[2]), _ptr(g[3])
+        p.blk_ctx_w[0], p.blk_ctx_b[0], p.blk_ctx_w[1], p.blk_ctx_b[1] = _ptr(g[4]), _ptr(g[5]), _ptr(g[6]), _ptr(g[7])
+        for k in range(2):
+            for j in range(2):
+                p.blk_lin_w[k][j] = _ptr(g[8 + 4 * k + 2 * j])
+                p.blk_lin_b[k][j] = _ptr(g[9 + 4 * k + 2 * j])
+        p.final_w, p.final_b = _ptr(g[16]), _ptr(g[17])
+    ws = fh.workspace(A.PF_OP_BACKWARD, R, E)
+    with torch.cuda.device(fh.index):
+        A.check(fh.lib.pf_flow_backward(fh.h, saved.data_ptr(), ctx.data_ptr(), None, n_per_ctx, R, E, gz.data_ptr(),
+                                        glogdet.data_ptr(), gx.data_ptr(), gctx.data_ptr(), arr, ws.data_ptr(),
+                                        ws.numel(), _stream()), "pf_flow_backward")
+    fh._note_launches()
+    return [gx, gctx] + gws
+
+
+@nsf_backward.register_fake
+def _(saved, ctx, gz, glogdet, weights, handle, n_per_ctx):
+    return [torch.empty_like(gz), torch.empty_like(ctx)] + [torch.empty_like(w) for w in weights]
+
+
+def _fwd_setup(ctx, inputs, output):
+    x, c, weights, handle, n_per_ctx, save = inputs
+    _, _, saved = output
+    if not save:
+        raise RuntimeError("nsf_forward was called with save=False but a gradient is required")
+    ctx.save_for_backward(saved, c, *weights)
+    ctx.handle, ctx.n_per_ctx = handle, n_per_ctx
+
+
+def _fwd_backward(ctx, gz, glogdet, gsaved):
+    saved, c, *weights = ctx.saved_tensors
+    outs = torch.ops.posteriflow.nsf_backward(saved, c, gz, glogdet, weights, ctx.handle, ctx.n_per_ctx)
+    return outs[0], outs[1], list(outs[2:]), None, None, None
+
+
+nsf_forward.register_autograd(_fwd_backward, setup_context=_fwd_setup)
+
+
+@torch.library.custom_op("posteriflow::nsf_nll", mutates_args=())
+def nsf_nll(x: Tensor, ctx: Tensor, log_sigma: Optional[Tensor], handle: int, n_per_ctx: int) -> Tensor:
+    """compute_psd_aware_nll (flows.py:727-779) fused, inference only (no autograd)."""
+    _require_cuda(x, ctx)
+    fh = get_handle(handle)
+    x, ctx = _f32c(x), _f32c(ctx)
+    ls = _f32c(log_sigma) if log_sigma is not None else None
+    R, E = _rows(x, ctx, n_per_ctx)
+    nll = torch.empty(R, dtype=torch.float32, device=x.device)
+    ws = fh.workspace(A.PF_OP_FORWARD, R, E)
+    with torch.cuda.device(fh.index):
+        A.check(fh.lib.pf_flow_forward(fh.h, x.data_ptr(), ctx.data_ptr(), None, n_per_ctx, R, E, None, None,
+                                       nll.data_ptr(), _ptr(ls), 0, None, ws.data_ptr(), ws.numel(), _stream()),
+                "pf_flow_forward(nll)")
+    fh._note_launches()
+    return nll
+
+
+@nsf_nll.register_fake
+def _(x, ctx, log_sigma, handle, n_per_ctx):
+    return x.new_empty(x.shape[0])
+
+
+# ------------------------------------------------------------------------------------------------
+# sampling direction
+# ------------------------------------------------------------------------------------------------
+def _scaler_struct(lo, hi, log_mask, circ_mask):
+    if lo is None:
+        return None, []
+    keep = [_f32c(lo), _f32c(hi), log_mask.to(torch.uint8).contiguous(), circ_mask.to(torch.uint8).contiguous()]
+    _require_cuda(*keep)
+    return A.Scaler(*[t.data_ptr() for t in keep]), keep
+
+
+@torch.library.custom_op("posteriflow::nsf_inverse", mutates_args=())
+def nsf_inverse(z: Tensor, ctx: Tensor, handle: int, n_per_ctx: int, flags: int, lo: Optional[Tensor],
+                hi: Optional[Tensor], log_mask: Optional[Tensor], circ_mask: Optional[Tensor]
+                ) -> Tuple[Tensor, Tensor]:
+    """NSFPosteriorFlow.inverse (flows.py:620-655), optionally fused with ParamScaler.wrap/denormalize."""
+    _require_cuda(z, ctx)
+    fh = get_handle(handle)
+    z, ctx = _f32c(z), _f32c(ctx)
+    R, E = _rows(z, ctx, n_per_ctx)
+    x = torch.empty_like(z)
+    logdet = torch.empty(R, dtype=torch.float32, device=z.device)
+    sc, keep = _scaler_struct(lo, hi, log_mask, circ_mask)
+    ws = fh.workspace(A.PF_OP_INVERSE, R, E)
+    with torch.cuda.device(fh.index):
+        A.check(fh.lib.pf_flow_inverse(fh.h, z.data_ptr(), ctx.data_ptr(), None, n_per_ctx, R, E, x.data_ptr(),
+                                       logdet.data_ptr(), flags, C.byref(sc) if sc is not None else None,
+                                       ws.data_ptr(), ws.numel(), _stream()), "pf_flow_inverse")
+    fh._note_launches()
+    return x, logdet
+
+
+@nsf_inverse.register_fake
+def _(z, ctx, handle, n_per_ctx, flags, lo, hi, log_mask, circ_mask):
+    return torch.empty_like(z), z.new_empty(z.shape[0])
+
+
+@torch.library.custom_op("posteriflow::nsf_sample_fused", mutates_args=())
+def nsf_sample_fused(ctx: Tensor, z: Optional[Tensor], seed: int, n: int, handle: int, flags: int, lo: Tensor,
+                     hi: Tensor, log_mask: Tensor, circ_mask: Tensor) -> Tuple[Tensor, Tensor, Tensor]:
+    """LeanNPE.sample_posterior after the encoder (lean_npe.py:326-332): theta [E, n, D], logdet [E*n],
+    railed [E*n] (pipeline.py:177).  z=None draws the base noise in-kernel (Philox keyed by `seed`)."""
+    _require_cuda(ctx, z)
+    fh = get_handle(handle)
+    ctx = _f32c(ctx)
+    E, D = ctx.shape[0], fh.shape[0]
+    R = E * n
+    if z is not None:
+        z = _f32c(z)
+        if z.shape[0] != R:
+            raise ValueError(f"z has {z.shape[0]} rows, expected {R}")
+    theta = torch.empty(E, n, D, dtype=torch.float32, device=ctx.device)
+    logdet = torch.empty(R, dtype=torch.float32, device=ctx.device)
+    railed = torch.empty(R, dtype=torch.uint8, device=ctx.device)
+    sc, keep = _scaler_struct(lo, hi, log_mask, circ_mask)
+    ws = fh.workspace(A.PF_OP_SAMPLE, R, E)
+    with torch.cuda.device(fh.index):
+        A.check(fh.lib.pf_sample_fused(fh.h, ctx.data_ptr(), C.byref(sc), _ptr(z), seed & (2 ** 64 - 1), E, n,
+                                       theta.data_ptr(), logdet.data_ptr(), railed.data_ptr(), flags, ws.data_ptr(),
+                                       ws.numel(), _stream()), "pf_sample_fused")
+    fh._note_launches()
+    return theta, logdet, railed
+
+
+@nsf_sample_fused.register_fake
+def _(ctx, z, seed, n, handle, flags, lo, hi, log_mask, circ_mask):
+    E = ctx.shape[0]
+    return (ctx.new_empty(E, n, lo.shape[0]), ctx.new_empty(E * n), ctx.new_empty(E * n, dtype=torch.uint8))

@@ -1,0 +1,43 @@
+"""Shared helpers for the parity tests (test infrastructure; may import oracle/)."""
+import os
+
+import numpy as np
+import torch
+
+import nsf_oracle as O
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load_golden(name):
+    g = dict(np.load(os.path.join(GOLDEN, name + ".npz"), allow_pickle=False))
+    s = g["spec"]
+    spec = O.FlowSpec(int(s[0]), int(s[1]), int(s[2]), int(s[3]), int(s[4]), float(s[5]), int(s[6]))
+    if any(k.startswith("w:") for k in g):
+        w = {k[2:]: torch.from_numpy(v) for k, v in g.items() if k.startswith("w:")}
+    else:
+        w = O.init_weights(spec, seed=int(g["seed"]), stress=bool(g["stress"]))
+    assert abs(O.weights_checksum(w) - float(g["weights_checksum"])) <= 1e-9 * abs(float(g["weights_checksum"])), \
+        "regenerated weights differ from the ones the golden fixture was made with"
+    return spec, w, g
+
+
+def t(a, device="cpu"):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(device)
+
+
+def make_flow(spec, w, device, tier="fp32"):
+    """posteriflow_b200.NSFPosteriorFlow holding the oracle weight set `w` (strict state-dict load)."""
+    import posteriflow_b200 as P
+    flow = P.NSFPosteriorFlow(features=spec.features, context_features=spec.context_features,
+                              hidden_features=spec.hidden_features, num_layers=spec.num_layers,
+                              num_bins=spec.num_bins, tail_bound=spec.tail_bound, dropout=0.0,
+                              temperature_scale=1.0, use_masked_context=False, tier=tier)
+    flow.load_state_dict(O.full_state_dict(spec, w), strict=True)
+    return flow.to(device)
+
+
+def rel_err(a, ref):
+    """max |a - ref| / max(1, |ref|) -- the tolerance form of SURVEY.md 8c / BASELINE north_star."""
+    a, ref = np.asarray(a, dtype=np.float64), np.asarray(ref, dtype=np.float64)
+    return float(np.max(np.abs(a - ref) / np.maximum(1.0, np.abs(ref)))) if a.size else 0.0
