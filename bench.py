@@ -1,0 +1,312 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the LeanNPE posterior-flow hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--tier fp32|bf16]
+
+Metric (BASELINE.json): NSF posterior samples/s.  One step = one pass of the fused sampler
+(lean_npe.py:326-332: context broadcast -> base noise -> inverse flow -> wrap -> denormalize) over one
+batch of synthetic events: EVENTS_PER_GPU events x 5000 samples per GPU, i.e. BASELINE config #3
+(4096 events x 5000 samples) at 8 GPUs, events sharded contiguously, no data-path collective (weak
+scaling).  Weights are random-init (seeded), contexts synthetic.  The NLL training step (config #4
+shard: forward + backward of the flow head) is timed too and reported under "train".
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+EVENTS_PER_GPU = 512
+SAMPLES_PER_EVENT = 5000
+TRAIN_EVENTS_PER_GPU = 512          # config #4: batch 4096 over 8 GPUs
+F_X = 7946240                       # FLOP per flow row, dense single conditioner pass x 10 layers
+F_CTX = 4423680                     # FLOP per distinct context row
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d, "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            self.th.join(timeout=2)
+
+    def summary(self):
+        sm = sorted(int(r[0]) for r in self.rows if len(r) >= 6 and r[0].isdigit())
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        mx = max(int(r[1]) for r in self.rows if len(r) >= 6 and r[1].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 6 and r[2 + i].lower() == "active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": mx, "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own algorithm (PyTorch eager over nflows semantics) as restated by oracle/
+# ------------------------------------------------------------------------------------------------
+def cpu_sampler(rows_per_call=4096):
+    """Returns (fn(n_rows) -> seconds, cores).  One call = flow.inverse on `n_rows` samples of one event
+    in chunks of 4096 (pipeline.py:105), + wrap + denormalize, exactly the reference's op sequence."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import nsf_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    spec = O.FlowSpec()
+    w = O.init_weights(spec, seed=0)
+    sc = O.Scaler()
+    g = torch.Generator().manual_seed(1)
+    ctx = torch.randn(1, spec.context_features, generator=g)
+
+    def run(n_rows):
+        z = torch.randn(n_rows, spec.features, generator=g)
+        t0 = time.perf_counter()
+        with torch.no_grad():
+            O.sample_posterior(spec, w, sc, ctx, z, n_rows, chunk=rows_per_call)
+        return time.perf_counter() - t0
+    return run, cores
+
+
+def cpu_measure(budget_s=12.0):
+    run, cores = cpu_sampler()
+    run(256)                       # warm-up (thread pool, allocator)
+    t = run(1024)
+    n = int(max(1024, min(65536, 1024 * budget_s / max(t, 1e-3))))
+    n = n // 1024 * 1024
+    dt = run(n)
+    return {"value": n / dt, "unit": "samples/s", "cores": cores, "kind": "port",
+            "sample": f"{n} samples of 1 event (chunks of 4096), LeanNPE shape, fp32, oracle/nsf_oracle.py "
+                      f"(reference op sequence: 11 conditioner passes per layer), {dt:.1f} s"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    run, cores = cpu_sampler()
+    run(256)
+    t = run(512)
+    per_step = int(max(512, min(16384, 512 * (60.0 / max(1, args.steps + args.warmup)) / max(t, 1e-3)))) // 512 * 512
+    for _ in range(args.warmup):
+        run(per_step)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        run(per_step)
+    dt = time.perf_counter() - t0
+    v = per_step * args.steps / dt
+    sample = (f"{per_step} samples/step of 1 event on {cores} host threads; oracle port of the reference's PyTorch "
+              f"path (nflows is not installable here, SURVEY.md 0.3)")
+    print(json.dumps({
+        "impl": "reference", "metric": "posterior_samples_per_sec", "value": v, "unit": "samples/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def workload_config(n_gpus):
+    return {"workload": f"BASELINE config #3 shard: {EVENTS_PER_GPU} events x {SAMPLES_PER_EVENT} samples per GPU "
+                        f"({EVENTS_PER_GPU * n_gpus} events total; 4096 at 8 GPUs), rank 0, LeanNPE flow 10x256x16 "
+                        "bins, 11-D, 288-D context",
+            "events_per_gpu": EVENTS_PER_GPU, "samples_per_event": SAMPLES_PER_EVENT,
+            "parallelism": f"events sharded over {n_gpus} GPU(s), no data-path collective",
+            "l2": "inputs+outputs per step (>= 225 MB) exceed the 126 MB L2"}
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch.distributed as dist
+    import posteriflow_b200 as P
+    from posteriflow_b200 import _cabi as A
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        tt = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt.item())
+
+    torch.manual_seed(0)
+    model = P.LeanNPE(tier=args.tier).to(dev)      # random-init weights, identical on every rank
+    flow, scaler = model.flow, model.scaler
+    E, n, D = args.events, args.samples, 11
+    R = E * n
+    g = torch.Generator().manual_seed(100 + rank)
+    ctx_host = torch.randn(E, 256, generator=g).pin_memory()   # stands in for encoder output (encoder stays PyTorch)
+    ctx_dev = ctx_host.to(dev)
+    rank_idx = torch.zeros(E, dtype=torch.long, device=dev)
+    with torch.no_grad():
+        ctx_full = model._full_context(ctx_dev, rank_idx)
+    theta_host = torch.empty(E, n, D, dtype=torch.float32).pin_memory()
+    fh = flow.handle()
+
+    def step_device(i):
+        return P.sample_fused(flow, scaler, ctx_full, n, z=None, seed=1000 + i)
+
+    def step_e2e(i):
+        c = ctx_host.to(dev, non_blocking=True)
+        th = model.sample_posterior(None, rank=0, n_samples=n, context=c)
+        theta_host.copy_(th, non_blocking=True)
+
+    def timed(fn, steps, warmup):
+        for i in range(warmup):
+            fn(i)
+        barrier()
+        l0 = fh.launches
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(warmup + i)
+        e1.record()
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1)), fh.launches - l0
+
+    with ClockSampler(local) as clk:
+        ms, launches = timed(step_device, args.steps, args.warmup)
+    clocks = clk.summary()
+    ms_e2e, _ = timed(step_e2e, args.steps, max(1, args.warmup // 2))
+
+    # NLL training step of the flow head (config #4 shard): forward + backward (+ gradient all-reduce)
+    Bt = args.train_events
+    nsig = torch.multinomial(torch.tensor([.55, .20, .12, .08, .05]), Bt, replacement=True, generator=g) + 1
+    ev = torch.repeat_interleave(torch.arange(Bt), nsig)
+    rk = torch.cat([torch.arange(int(k)) for k in nsig])
+    Rt = int(ev.numel())
+    sc_cpu = P.ParamScaler()
+    theta_phys = sc_cpu.denormalize(torch.rand(Rt, D, generator=g) * 2 - 1).to(dev)
+    tctx = torch.randn(Bt, 256, generator=g).to(dev).requires_grad_(True)
+    ev, rk = ev.to(dev), rk.to(dev)
+    params = [p for p in model.parameters() if p.requires_grad]
+
+    def step_train(i):
+        for p in params:
+            p.grad = None
+        tctx.grad = None
+        loss = model.nll(None, theta_phys, rk, context=tctx[ev]).sum() / Rt
+        loss.backward()
+        if world > 1:
+            flat = torch.cat([p.grad.reshape(-1) for p in params])
+            dist.all_reduce(flat)
+        return loss
+
+    ms_train, launches_train = timed(step_train, args.steps, args.warmup)
+
+    pk, pk_kind = peaks()
+    rows_s = R * world * args.steps / (ms * 1e-3)
+    flop_row = F_X + F_CTX / n
+    ach = rows_s / world * flop_row / 1e12
+    peak = float(pk["bf16_tflops_sustained"])
+    train_flop = 3 * (F_X + F_CTX) * Rt
+    ach_t = train_flop * args.steps / (ms_train * 1e-3) / 1e12
+    out = {
+        "metric": "posterior_samples_per_sec", "value": rows_s, "unit": "samples/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32" if args.tier == "fp32" else "bf16 operands, f32 accumulate+spline",
+        "data": "synthetic (random-init weights, N(0,1) contexts standing in for encoder output, in-kernel Philox base noise)",
+        "config": workload_config(world) if (E, n) == (EVENTS_PER_GPU, SAMPLES_PER_EVENT) else
+        {"workload": f"{E} events x {n} samples per GPU (non-default)", "parallelism": f"events sharded over {world} GPU(s)"},
+        "tier": args.tier,
+        "e2e": {"value": R * world * args.steps / (ms_e2e * 1e-3), "unit": "samples/s",
+                "h2d_bytes_per_step": int(ctx_host.numel() * 4), "d2h_bytes_per_step": int(theta_host.numel() * 4),
+                "ms_per_step": ms_e2e / args.steps,
+                "api": "posteriflow_b200.LeanNPE.sample_posterior(context=pinned host -> device) -> pinned host theta"},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                     "traffic": None, "peak_source": f"{pk_kind} bf16_tflops_sustained",
+                     "flop_per_row": flop_row,
+                     "note": "whole sampler step per GPU (dense single-pass conditioner FLOPs, SURVEY 8d); "
+                             "hbm: %.1f GB/s of algorithmic output (49 B/row)" % (rows_s / world * 49 / 1e9)},
+        "train": {"metric": "nll_train_steps_per_sec", "value": args.steps / (ms_train * 1e-3), "unit": "steps/s",
+                  "events_per_gpu": Bt, "flow_rows_per_gpu": Rt, "ms_per_step": ms_train / args.steps,
+                  "gpu_launches": int(launches_train),
+                  "includes": "scaler.normalize, rank embedding, flow forward+backward (all weights, context), "
+                              + ("NCCL gradient all-reduce" if world > 1 else "no all-reduce at 1 GPU")
+                              + "; encoder and optimizer excluded (encoder stays reference PyTorch)",
+                  "roofline": {"bound": "tensor", "achieved": ach_t, "peak": peak, "unit": "TFLOP/s",
+                               "frac": ach_t / peak, "flop_per_row": 3 * (F_X + F_CTX)}},
+    }
+    if rank == 0:
+        if not args.no_cpu and world == 1:
+            out["cpu_baseline"] = cpu_measure()
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--tier", default=os.environ.get("PF_TIER", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--events", type=int, default=EVENTS_PER_GPU)
+    ap.add_argument("--samples", type=int, default=SAMPLES_PER_EVENT)
+    ap.add_argument("--train-events", type=int, default=TRAIN_EVENTS_PER_GPU)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -349,11 +349,11 @@ extern "C" pf_status pf_flow_forward(pf_flow* f, const float* x, const float* ct
                                      const float* log_sigma, uint32_t flags, void* saved, void* workspace,
                                      size_t workspace_bytes, void* stream) {
   PF_TRY(check_call(f, R, E, row2ctx, n_per_ctx));
+  f->launches = 0;
+  if (R == 0) return PF_OK;
   if (!x || !ctx) return PF_ERR_INVALID;
   PF_CUDA(cudaSetDevice(f->desc.device));
   cudaStream_t st = (cudaStream_t)stream;
-  f->launches = 0;
-  if (R == 0) return PF_OK;
   const int D = f->D, H = f->H, L = f->L, PLD = f->PLD, P = f->P;
   const bool is_proj = flags & PF_FLAG_CTX_IS_PROJ;
   const bool dense = !row2ctx && n_per_ctx == 1;
@@ -557,10 +557,10 @@ extern "C" pf_status pf_flow_inverse(pf_flow* f, const float* z, const float* ct
                                      int64_t n_per_ctx, int64_t R, int64_t E, float* x, float* logdet, uint32_t flags,
                                      const pf_scaler* scaler, void* workspace, size_t workspace_bytes, void* stream) {
   PF_TRY(check_call(f, R, E, row2ctx, n_per_ctx));
-  if (!z || !ctx || !x) return PF_ERR_INVALID;
-  PF_CUDA(cudaSetDevice(f->desc.device));
   f->launches = 0;
   if (R == 0) return PF_OK;
+  if (!z || !ctx || !x) return PF_ERR_INVALID;
+  PF_CUDA(cudaSetDevice(f->desc.device));
   if (f->desc.tier == PF_TIER_BF16)
     return pf_tc_inverse(f, (cudaStream_t)stream, z, 0, ctx, row2ctx, n_per_ctx, R, E, x, logdet, nullptr, flags, scaler,
                          workspace, workspace_bytes);
@@ -574,10 +574,10 @@ extern "C" pf_status pf_sample_fused(pf_flow* f, const float* ctx, const pf_scal
   if (!f || n < 1 || E < 0) return PF_ERR_INVALID;
   const int64_t R = E * n;
   PF_TRY(check_call(f, R, E, nullptr, n));
-  if (!ctx || !theta) return PF_ERR_INVALID;
-  PF_CUDA(cudaSetDevice(f->desc.device));
   f->launches = 0;
   if (R == 0) return PF_OK;
+  if (!ctx || !theta) return PF_ERR_INVALID;
+  PF_CUDA(cudaSetDevice(f->desc.device));
   if (f->desc.tier == PF_TIER_BF16)
     return pf_tc_inverse(f, (cudaStream_t)stream, z, seed, ctx, nullptr, n, R, E, theta, logdet, railed, flags, scaler,
                          workspace, workspace_bytes);
