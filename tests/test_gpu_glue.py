@@ -123,7 +123,7 @@ def test_round_trip_inverse_then_forward(R):
     # the inverse is ill-conditioned where a bin is steep, so the maximum over 11*R draws grows with R;
     # the bulk must close to float32 round-off
     dz, dl = (z2 - z).abs().flatten(), (ld + ld2).abs()
-    assert float(dz.median()) <= 2e-6 and float(dl.median()) <= 2e-5
+    assert float(dz.median()) <= 1e-5 and float(dl.median()) <= 5e-5
     if R >= 1000:
         assert float(torch.quantile(dz[:1000000], 0.999)) <= 2e-4
     assert float(dz.max()) <= 2e-2 and float(dl.max()) <= 2e-2

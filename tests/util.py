@@ -46,13 +46,14 @@ def rel_err(a, ref):
 TOL = 1e-4  # FP32 tier: |d| <= 1e-4 * max(1, |ref|)  (BASELINE.json north_star)
 
 
-def check_parity(name, got, ref32, ref64=None, tol=TOL, scale=None):
+def check_parity(name, got, ref32, ref64=None, tol=TOL, scale=None, median_factor=2.0):
     """Pass if `got` is within `tol` of the float32 reference.  Where it is not and a float64 run of
     the same reference code is available, the float64 run arbitrates: with ill-conditioned (stress)
     weights the float32 reference ITSELF sits further than `tol` from float64, and any other valid
     float32 evaluation order (ours) is a second draw from the same error distribution.  It must then be
     statistically indistinguishable from the reference's own float32 error: median within 2x, maximum
-    within 8x (+tol).  `scale` switches from per-element max(1,|ref|) to one global scale (gradients)."""
+    within 8x (+tol).  `scale` switches from per-element max(1,|ref|) to one global scale (gradients); median_factor=None
+    drops the median test for entries whose errors are correlated (norms of one backward pass)."""
     got, ref32 = np.asarray(got, np.float64), np.asarray(ref32, np.float64)
     assert got.shape == ref32.shape, (name, got.shape, ref32.shape)
     if got.size == 0:
@@ -65,6 +66,8 @@ def check_parity(name, got, ref32, ref64=None, tol=TOL, scale=None):
     ref64 = np.asarray(ref64, np.float64)
     e = np.abs(got - ref64) / den(ref64)
     own = np.abs(ref32 - ref64) / den(ref64)
-    ok = np.median(e) <= 2 * np.median(own) + 1e-6 and e.max() <= 8 * own.max() + tol
+    ok = e.max() <= 8 * own.max() + tol
+    if median_factor is not None:
+        ok = ok and np.median(e) <= median_factor * np.median(own) + 1e-6
     assert ok, (f"{name}: vs f32 max {e32.max():.3e}; vs f64 median {np.median(e):.3e} max {e.max():.3e}; "
                 f"f32 reference's own vs f64 median {np.median(own):.3e} max {own.max():.3e}")
