@@ -98,9 +98,8 @@ struct pf_flow {
   float *WfT;            // [L][H][PLD]
   float *WctxT;          // [C][L*3H]   (all layers side by side: one GEMM for d(ctx))
   float* W0T;            // [L][DP][H]  (d(x) through the initial layer)
-  // bf16 tensor-core tier (pf_tc.cu): per-layer streamed weight image, built by pf_flow_pack
-  void* tc_image;        // device, NULL when tier != PF_TIER_BF16
-  size_t tc_image_bytes;
+  // bf16 tensor-core tier (pf_tc.cu): opaque state (weight image + padded side arrays), built by pf_flow_pack
+  void* tc;              // NULL when tier != PF_TIER_BF16
   int UF;                // padded per-dim parameter count (MULT rounded up to 4)
 };
 
@@ -110,5 +109,6 @@ pf_status pf_tc_inverse(pf_flow* f, cudaStream_t st, const float* z, uint64_t se
                         const int64_t* row2ctx, int64_t n_per_ctx, int64_t R, int64_t E, float* x, float* logdet,
                         uint8_t* railed, uint32_t flags, const pf_scaler* scaler, void* workspace,
                         size_t workspace_bytes);
+pf_status pf_tc_ctxproj(pf_flow* f, cudaStream_t st, const float* ctx, int64_t E, uint32_t flags, float* proj);
 size_t pf_tc_workspace_bytes(const pf_flow* f, int64_t R, int64_t E);
 void pf_tc_destroy(pf_flow* f);

@@ -15,6 +15,7 @@
 #include "pf_common.cuh"
 #include "pf_gemm.cuh"
 #include "pf_spline.cuh"
+#include "pf_tail.cuh"
 
 namespace pf {
 
@@ -161,42 +162,13 @@ __global__ void copy_rows_kernel(const float* __restrict__ src, float* __restric
   if (i < n) dst[i] = src[i];
 }
 
-// Philox4x32-10 (Salmon et al. 2011) keyed by the call's seed; counter = (row, quad index).
-__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
-                                              uint32_t k1, uint32_t out[4]) {
-#pragma unroll
-  for (int i = 0; i < 10; ++i) {
-    uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-    uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-    uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
-    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
-    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
-  }
-  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
-}
-__device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& n0, float& n1) {
-  float u1 = ((float)a + 1.f) * 2.3283064365386963e-10f;  // (0, 1]
-  float u2 = (float)b * 2.3283064365386963e-10f;
-  float rad = sqrtf(-2.f * logf(u1));
-  float s, c;
-  sincospif(2.f * u2, &s, &c);
-  n0 = rad * c; n1 = rad * s;
-}
 __global__ void philox_normal_kernel(float* __restrict__ Z, int D, int R, int64_t row0, uint64_t seed) {
   int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= R) return;
-  uint64_t gr = (uint64_t)(row0 + r);
-  for (int q = 0; q * 4 < D; ++q) {
-    uint32_t o[4];
-    philox4x32_10((uint32_t)gr, (uint32_t)(gr >> 32), (uint32_t)q, 0u, (uint32_t)seed, (uint32_t)(seed >> 32), o);
-    float n[4];
-    box_muller(o[0], o[1], n[0], n[1]);
-    box_muller(o[2], o[3], n[2], n[3]);
-    for (int i = 0; i < 4 && q * 4 + i < D; ++i) Z[(int64_t)r * D + q * 4 + i] = n[i];
-  }
+  float n[PF_MAX_D];
+  philox_normal_row((uint64_t)(row0 + r), seed, D, n);
+  for (int j = 0; j < D; ++j) Z[(int64_t)r * D + j] = n[j];
 }
-
-struct ScalerDev { const float* lo; const float* hi; const uint8_t* log_mask; const uint8_t* circ_mask; };
 
 // Tail of NSFPosteriorFlow.inverse (flows.py:648-654) + ParamScaler.wrap / denormalize
 // (lean_npe.py:100-114) + rail mask (pipeline.py:177) + m1>=m2 ordering (pipeline.py:184-186).
@@ -206,35 +178,9 @@ __global__ void finish_inverse_kernel(const float* __restrict__ U, int D, int R,
   int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= R) return;
   float v[PF_MAX_D];
-  bool rail = false;
 #pragma unroll
-  for (int j = 0; j < PF_MAX_D; ++j) {
-    if (j >= D) break;
-    float x = U[(int64_t)r * D + (D - 1 - j)];
-    if (flags & PF_FLAG_CLAMP) {
-      if (x != x) x = 0.f;
-      else if (isinf(x)) x = x > 0.f ? 1.f : -1.f;
-      x = fminf(fmaxf(x, -clamp_bound), clamp_bound);
-    }
-    if (flags & PF_FLAG_WRAP) {
-      if (sc.circ_mask[j]) {
-        float m = fmodf(x + 1.f, 2.f);  // torch.remainder: sign follows the divisor
-        if (m != 0.f && m < 0.f) m += 2.f;
-        x = m - 1.f;
-      } else {
-        x = fminf(fmaxf(x, -1.f), 1.f);
-        rail = rail || fabsf(x) > 0.999f;
-      }
-    }
-    if (flags & PF_FLAG_DENORMALIZE) {
-      float y = fminf(fmaxf(x, -1.f), 1.f);
-      float lo = sc.lo[j], hi = sc.hi[j];
-      x = (y + 1.f) / 2.f * (hi - lo) + lo;
-      if (sc.log_mask[j]) x = expf(x);
-    }
-    v[j] = x;
-  }
-  if ((flags & PF_FLAG_SORT_MASSES) && D >= 2 && v[1] > v[0]) { float t = v[0]; v[0] = v[1]; v[1] = t; }
+  for (int j = 0; j < PF_MAX_D; ++j) v[j] = j < D ? U[(int64_t)r * D + (D - 1 - j)] : 0.f;
+  bool rail = finish_row(v, D, flags, clamp_bound, sc);
 #pragma unroll
   for (int j = 0; j < PF_MAX_D; ++j) {
     if (j >= D) break;
@@ -284,6 +230,7 @@ extern "C" pf_status pf_flow_ctxproj(pf_flow* f, const float* ctx, int64_t E, ui
   if (!f->packed) return PF_ERR_NOT_PACKED;
   PF_CUDA(cudaSetDevice(f->desc.device));
   f->launches = 0;
+  if (f->desc.tier == PF_TIER_BF16) return pf_tc_ctxproj(f, (cudaStream_t)stream, ctx, E, flags, proj);
   return ctxproj_impl(f, (cudaStream_t)stream, ctx, E, flags, proj);
 }
 

@@ -133,6 +133,7 @@ extern "C" pf_status pf_flow_create(const pf_flow_desc* d, pf_flow** out) {
 
 extern "C" void pf_flow_destroy(pf_flow* f) {
   if (!f) return;
+  pf_tc_destroy(f);
   if (f->arena) cudaFree(f->arena);
   if (f->d_perm) cudaFree(f->d_perm);
   if (f->d_flag) cudaFree(f->d_flag);
@@ -194,6 +195,7 @@ extern "C" pf_status pf_flow_pack(pf_flow* f, const pf_layer_ptrs* layers, void*
     PF_TRY(pack_vector(f, st, f->bf + (size_t)l * PLD, w.final_b, P, nullptr));
 
   }
+  PF_TRY(pf_tc_pack(f, st));
   int flag = 0;
   PF_CUDA(cudaMemcpyAsync(&flag, f->d_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
   PF_CUDA(cudaStreamSynchronize(st));

@@ -1,10 +1,728 @@
-// bf16 tensor-core tier (PF_TIER_BF16): tcgen05 sampler.  Placeholder until the kernel lands.
-#include "pf_common.cuh"
+// Tensor-core tier (PF_TIER_BF16) of the sampling direction: ONE persistent kernel per call runs the whole
+// incremental autoregressive inverse of NSFPosteriorFlow.inverse (flows.py:620-655) + the LeanNPE epilogue
+// (lean_npe.py:326-332) for tiles of 128 flow rows, with every conditioner matrix product on tcgen05.mma
+// (bf16 operands, fp32 accumulation in tensor memory) and the rational-quadratic spline in fp32 registers.
+//
+// Per CTA (one per SM, 192 threads):
+//   warps 0-3  "row" warps: thread t owns flow row t of the tile = TMEM lane t.  They read accumulators with
+//              tcgen05.ld, apply bias / context / GLU / residual / relu or the spline inverse, and write the
+//              next stage's A operand (bf16) back to tensor memory (tcgen05.st) or shared memory.
+//   warp 4     lane 0 issues every tcgen05.mma + tcgen05.commit; the warp also owns the TMEM allocation.
+//   warp 5     lane 0 streams the pre-laid-out bf16 weight blobs (UMMA canonical K-major layout, built by
+//              pf_tc_pack) from L2 into a shared-memory ring with cp.async.bulk + mbarrier complete_tx.
+//
+// Hidden units are sorted by autoregressive degree and every degree group is padded to GSP (even) slots, so
+// a masked matrix restricted to "rows of degree d" is a dense [GSP x GSP*d] block: step d of a layer needs
+// five skinny MMAs (N = 32, K = GSP*d) for the hidden group of degree d and one (N = 48, K = GSP*(d-1)) for
+// the 3K-1 spline parameters of dimension d -- one conditioner pass of work per layer in total instead of
+// nflows' D passes.  The five activation arrays a step must keep for later steps
+// (relu(h0), relu(u1), relu(h1), relu(u2), h2: 5 x [128, 260] bf16) do not fit in shared memory, so three
+// of them live in tensor memory and are fed to the MMA as the TMEM A operand; two live in shared memory.
+#include <stdlib.h>
 
-pf_status pf_tc_pack(pf_flow*, cudaStream_t) { return PF_OK; }
-pf_status pf_tc_inverse(pf_flow*, cudaStream_t, const float*, uint64_t, const float*, const int64_t*, int64_t, int64_t,
-                        int64_t, float*, float*, uint8_t*, uint32_t, const pf_scaler*, void*, size_t) {
-  return PF_ERR_UNSUPPORTED;
+#include <vector>
+
+#include "pf_common.cuh"
+#include "pf_gemm.cuh"
+#include "pf_sm100.cuh"
+#include "pf_spline.cuh"
+#include "pf_tail.cuh"
+
+namespace pf {
+using namespace pf::sm100;
+
+constexpr int TC_ROWS = 128;      // rows per tile = UMMA M = TMEM lanes
+constexpr int TC_NSLOT = 4;       // weight ring depth
+constexpr int TC_THREADS = 192;
+
+// stage order inside step d of a layer (d = 1..D; the hidden stages exist for d < D)
+enum { ST_F = 0, ST_I = 1, ST_A1 = 2, ST_B1 = 3, ST_A2 = 4, ST_B2 = 5, ST_COUNT = 6 };
+
+struct TcShape {
+  int D, G, GSP, KTOT, KA, MULT, NF, L, PLD;
+  int pc_f;              // K=16 chunks per ring item of the final-layer blobs
+  uint32_t slot_bytes;   // ring slot size
+  uint32_t layer_bytes;  // weight image bytes per layer
+  int off[PF_MAX_D + 1]; // off[g] = #hidden units of degree <= g (unpadded, degree-sorted order)
+};
+__host__ __device__ inline int tc_nchunks(const TcShape& s, int d, int st) {
+  if (st == ST_F) return (s.GSP * (d - 1) + 15) / 16;
+  if (st == ST_I) return 2;
+  return (s.GSP * d + 15) / 16;
 }
-size_t pf_tc_workspace_bytes(const pf_flow*, int64_t, int64_t) { return 0; }
-void pf_tc_destroy(pf_flow*) {}
+__host__ __device__ inline int tc_n(const TcShape& s, int st) { return st == ST_F ? s.NF : 32; }
+__host__ __device__ inline int tc_piece(const TcShape& s, int st, int nch) { return st == ST_F ? s.pc_f : nch; }
+
+struct TcItem { int d, st, c0, nc, N; uint32_t off; };
+
+struct TcState {
+  TcShape shape;
+  uint8_t* image;        // [L][layer_bytes] bf16 blobs in program order
+  float* arena;          // padded-order fp32 side arrays
+  float *b0p, *bap, *bbp;   // [L][KTOT], [L][2][KTOT], [L][2][KTOT]
+  float *Wctxp, *bctxp;     // [L*3*KTOT][C], [L*3*KTOT]
+  int* err;              // device error flag (protocol timeouts)
+  TcItem* d_items; int n_items;
+  int kernel_smem;
+  bool debug_sync;
+};
+
+// ------------------------------------------------------------------------------------------------
+// packing
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int tc_slot_to_sorted(const TcShape& s, int slot) {
+  int g = slot / s.GSP, i = slot % s.GSP;  // g = degree - 1
+  if (g >= s.G) return -1;
+  int n = s.off[g + 1] - s.off[g];
+  return i < n ? s.off[g] + i : -1;
+}
+
+__global__ void tc_pack_image_kernel(TcShape s, const TcItem* __restrict__ items, uint8_t* __restrict__ image,
+                                     const float* __restrict__ W0, int DP, const float* __restrict__ Wa,
+                                     const float* __restrict__ Wb, const float* __restrict__ Wf, int H) {
+  const TcItem it = items[blockIdx.x];
+  const int l = blockIdx.y;
+  __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(image + (size_t)l * s.layer_bytes + it.off);
+  const int K = it.nc * 16, N = it.N;
+  const int gsz = it.d <= s.G ? s.off[it.d] - s.off[it.d - 1] : 0;
+  for (int e = threadIdx.x; e < N * K; e += blockDim.x) {
+    int n = e / K, k = e % K;
+    float v = 0.f;
+    if (it.st == ST_F) {
+      int col = tc_slot_to_sorted(s, it.c0 * 16 + k);
+      if (n < s.MULT && col >= 0) v = Wf[((size_t)l * s.PLD + (size_t)(it.d - 1) * s.MULT + n) * H + col];
+    } else if (it.st == ST_I) {
+      int j = k < 16 ? k : k - 16;  // columns 16.. multiply the low-order bf16 half of x
+      if (n < gsz && j < s.D) v = W0[((size_t)l * H + s.off[it.d - 1] + n) * DP + j];
+    } else {
+      int blk = (it.st - ST_A1) / 2;
+      const float* W = ((it.st - ST_A1) & 1) ? Wb : Wa;
+      int col = tc_slot_to_sorted(s, it.c0 * 16 + k);
+      if (n < gsz && col >= 0) v = W[(((size_t)l * 2 + blk) * H + s.off[it.d - 1] + n) * H + col];
+    }
+    dst[(k / 8) * (N * 8) + (n / 8) * 64 + (n % 8) * 8 + (k % 8)] = __float2bfloat16(v);
+  }
+}
+
+// padded-order side arrays: dst[row][slot] = src[row][sorted(slot)] or 0
+__global__ void tc_pad_vec_kernel(TcShape s, const float* __restrict__ src, int H, float* __restrict__ dst, int rows) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= rows * s.KTOT) return;
+  int row = i / s.KTOT, col = tc_slot_to_sorted(s, i % s.KTOT);
+  dst[i] = col >= 0 ? src[(size_t)row * H + col] : 0.f;
+}
+// dst[(sec*KTOT + slot)][c] = src[(sec*H + sorted(slot))][c]
+__global__ void tc_pad_rows_kernel(TcShape s, const float* __restrict__ src, int H, int C, float* __restrict__ dst,
+                                   int sections) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)sections * s.KTOT * C) return;
+  int c = (int)(i % C);
+  int64_t rs = i / C;
+  int sec = (int)(rs / s.KTOT), col = tc_slot_to_sorted(s, (int)(rs % s.KTOT));
+  dst[i] = col >= 0 ? src[((size_t)sec * H + col) * C + c] : 0.f;
+}
+
+// ------------------------------------------------------------------------------------------------
+// the sampler kernel
+// ------------------------------------------------------------------------------------------------
+struct TcArgs {
+  TcShape s;
+  const uint8_t* image;
+  const float *b0p, *bap, *bbp, *bf;
+  const float* proj;   // [ctx rows][L*3*KTOT] padded order: relu(c0) | sigmoid gate 1 | sigmoid gate 2
+  int64_t ldproj;
+  CtxMap cm;
+  const float* z;      // [R, D] or NULL -> Philox
+  uint64_t seed;
+  int64_t R;
+  int64_t row_base;    // global index of local row 0 (Philox counter)
+  int n_tiles;
+  float* x; float* logdet; uint8_t* railed;
+  uint32_t flags; float tail, clamp;
+  ScalerDev sc;
+  int* err;
+  int dbg_stop;        // >= 0: leave after this many MMA stages (bring-up aid, PF_TC_STOP)
+};
+
+// TMEM column map (512 columns allocated)
+template <int GSP>
+struct TcTmem {
+  static constexpr int NW = GSP / 2;         // 32-bit columns per group
+  // columns per activation array (G <= 10 groups).  The TMEM A operand of tcgen05.mma must start at a
+  // multiple of 4 columns (measured: tests/tmem_align_probe.cu), tcgen05.ld/st accept any column.
+  static constexpr int ARR = (10 * NW + 3) / 4 * 4;
+  static constexpr int A0 = 0, A1 = ARR, A2 = 2 * ARR, PAD = 3 * ARR;
+  static constexpr int ACC_F = (PAD + 8 + 15) / 16 * 16;  // >= 8 zero columns after the last array
+  static constexpr int ACC_H = ACC_F + 48;
+  static constexpr int ACC_I = ACC_H + 32;
+  static_assert(ACC_I + 32 <= 512, "TMEM budget");
+};
+
+__device__ __forceinline__ float finite_clamp(float v) { return fminf(fmaxf(v, -3.0e38f), 3.0e38f); }  // NaN -> -3e38
+__device__ __forceinline__ float relu_finite(float v) { return fminf(fmaxf(v, 0.f), 3.0e38f); }       // NaN -> 0
+
+template <int NW>
+__device__ __forceinline__ void tmem_store_words(uint32_t dst, const uint32_t* w) {
+  static_assert(NW == 13 || NW == 10, "instantiated group widths");
+  tmem_st8(dst, w);
+  if (NW == 13) {
+    tmem_st4(dst + 8, w + 8);
+    tmem_st1(dst + 12, w + 12);
+  } else {
+    tmem_st2(dst + 8, w + 8);
+  }
+  tmem_wait_st();
+}
+
+struct RegQ {
+  const float* q;
+  __device__ __forceinline__ float operator()(int i) const { return q[i]; }
+};
+
+template <int NB, int GSP>
+__global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs a) {
+  using TM = TcTmem<GSP>;
+  constexpr int NW = GSP / 2;
+  constexpr int MULT = 3 * NB - 1;
+  static_assert(MULT <= 48 && GSP <= 32 && GSP % 2 == 0, "shape limits of this kernel");
+  const TcShape& s = a.s;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int KA = s.KA, D = s.D;
+  uint8_t* sA3 = smem;
+  uint8_t* sA4 = sA3 + (size_t)KA * 256;
+  uint8_t* sX = sA4 + (size_t)KA * 256;
+  uint8_t* ring = sX + 8192;
+  float* ybuf = reinterpret_cast<float*>(ring + (size_t)TC_NSLOT * s.slot_bytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ybuf + 2 * TC_ROWS * D + ((2 * TC_ROWS * D) & 1));
+  uint64_t* full = bars;                 // [NSLOT] weights landed
+  uint64_t* empty = bars + TC_NSLOT;     // [NSLOT] MMAs reading the slot completed
+  uint64_t* acc_bar = bars + 2 * TC_NSLOT;      // accumulator of the current stage complete
+  uint64_t* op_bar = bars + 2 * TC_NSLOT + 1;   // operands of the next stage written (4 warp arrivals)
+  volatile int* abort_s = reinterpret_cast<volatile int*>(bars + 2 * TC_NSLOT + 2);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_NSLOT + 3);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) {
+    for (int i = 0; i < TC_NSLOT; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(acc_bar, 1);
+    mbar_init(op_bar, 4);
+    *abort_s = 0;
+    fence_mbar_init();
+  }
+  if (warp == 4) tmem_alloc(tmem_slot, 512);
+  // zero the shared-memory operand arrays (stale columns are multiplied by zero weights: must be finite)
+  for (int i = tid; i < (2 * KA * 256 + 8192) / 16; i += TC_THREADS) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  // bounded wait; on timeout raise the CTA-wide abort flag so every role leaves its loops
+  auto wait = [&](uint64_t* bar, uint32_t parity, int code) -> bool {
+    for (uint32_t i = 0; i < (1u << 21); ++i) {
+      if (mbar_try_wait(bar, parity)) return true;
+      if ((i & 255) == 255 && *abort_s) return false;
+    }
+    *abort_s = 1;
+    atomicExch(a.err, code);
+    return false;
+  };
+
+  if (warp < 4) {
+    // ============================ row warps ============================
+    const int r = tid;
+    const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16);   // this warp's TMEM lane window
+    {  // zero the TMEM activation arrays + pad columns
+      uint32_t zz[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) zz[i] = 0u;
+      for (int c = 0; c < TM::ACC_F; c += 16) tmem_st16(tl + c, zz);
+      tmem_wait_st();
+    }
+    uint32_t acc_par = 0;
+    const uint32_t rowoff = (uint32_t)(r / 8) * 128 + (uint32_t)(r % 8) * 16;
+    bool ok = true;
+    for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
+      const int64_t grow = (int64_t)tile * TC_ROWS + r;
+      const bool valid = grow < a.R;
+      float* y0 = ybuf + r * D;                 // ybuf[0][r][:]
+      float* y1 = ybuf + TC_ROWS * D + r * D;   // ybuf[1][r][:]
+      {
+        float zr[PF_MAX_D];
+#pragma unroll
+        for (int j = 0; j < PF_MAX_D; ++j) zr[j] = 0.f;
+        if (valid) {
+          if (a.z) {
+            for (int j = 0; j < D; ++j) zr[j] = a.z[grow * D + j];
+          } else {
+            philox_normal_row((uint64_t)(a.row_base + grow), a.seed, D, zr);
+          }
+        }
+        for (int j = 0; j < D; ++j) y0[j] = zr[j];
+      }
+      const float* projr = a.proj + (valid ? a.cm(grow) : 0) * a.ldproj;
+      float ld_acc = 0.f;
+      bool bad = false;
+      float* yin = y0;
+      float* yout = y1;
+      for (int l = s.L - 1; l >= 0 && ok; --l) {
+        const bool reversed = (l != s.L - 1);
+        const float* pl = projr + (size_t)l * 3 * s.KTOT;
+        for (int d = 1; d <= D && ok; ++d) {
+          const int j = d - 1;
+          // ---------------- F(d): spline parameters of dim d -> inverse spline ----------------
+          {
+            float q[48];
+            const float* bfl = a.bf + (size_t)l * s.PLD + (size_t)j * MULT;
+#pragma unroll
+            for (int i = 0; i < MULT; ++i) q[i] = __ldg(bfl + i);
+            q[47] = 0.f;
+            const float y = yin[reversed ? D - 1 - j : j];
+            if (d > 1) {
+              if (!(ok = wait(acc_bar, acc_par, 10))) break;
+              acc_par ^= 1;
+              tc_fence_after();
+              uint32_t v[48];
+              tmem_ld32(tl + TM::ACC_F, v);
+              tmem_ld16(tl + TM::ACC_F + 32, v + 32);
+              tmem_wait_ld();
+#pragma unroll
+              for (int i = 0; i < MULT; ++i) q[i] += __uint_as_float(v[i]);
+            }
+            float lad;
+            const float xo = rqs_apply<NB, true>(RegQ{q}, y, a.tail, lad);
+            ld_acc += lad;
+            yout[j] = xo;
+            bad = bad || !(fabsf(xo) <= 3.0e38f);
+            const float xc = finite_clamp(xo);
+            const __nv_bfloat16 hi = __float2bfloat16(xc);
+            const __nv_bfloat16 lo = __float2bfloat16(xc - __bfloat162float(hi));
+            *reinterpret_cast<__nv_bfloat16*>(sX + (j / 8) * 2048 + rowoff + (j % 8) * 2) = hi;
+            *reinterpret_cast<__nv_bfloat16*>(sX + (2 + j / 8) * 2048 + rowoff + (j % 8) * 2) = lo;
+          }
+          if (d == D) break;  // last dim: no hidden group follows, and the next stage (F(1)) has no MMA
+          fence_proxy_async_smem();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(op_bar);
+
+          const int slot0 = j * GSP;   // first padded slot of the degree-d group
+          float h[GSP];
+          // ---------------- I(d): h0 = W0 x + b0 + relu(Wc0 ctx + b) ----------------
+          {
+            float t[GSP];
+            const float* b = a.b0p + (size_t)l * s.KTOT + slot0;
+#pragma unroll
+            for (int i = 0; i < GSP; ++i) t[i] = __ldg(b + i) + __ldg(pl + slot0 + i);
+            if (!(ok = wait(acc_bar, acc_par, 11))) break;
+            acc_par ^= 1;
+            tc_fence_after();
+            uint32_t v[32];
+            tmem_ld32(tl + TM::ACC_I, v);
+            tmem_wait_ld();
+            uint32_t w[NW];
+#pragma unroll
+            for (int i = 0; i < GSP; ++i) h[i] = __uint_as_float(v[i]) + t[i];
+#pragma unroll
+            for (int i = 0; i < NW; ++i) w[i] = pack_bf16(relu_finite(h[2 * i]), relu_finite(h[2 * i + 1]));
+            tmem_store_words<NW>(tl + TM::A0 + j * NW, w);
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(op_bar);
+          // ---------------- residual blocks ----------------
+#pragma unroll
+          for (int blk = 0; blk < 2; ++blk) {
+            {  // A: u = Wa relu(h) + ba -> relu(u)
+              float t[GSP];
+              const float* b = a.bap + ((size_t)l * 2 + blk) * s.KTOT + slot0;
+#pragma unroll
+              for (int i = 0; i < GSP; ++i) t[i] = __ldg(b + i);
+              if (!(ok = wait(acc_bar, acc_par, 12 + blk))) break;
+              acc_par ^= 1;
+              tc_fence_after();
+              uint32_t v[32];
+              tmem_ld32(tl + TM::ACC_H, v);
+              tmem_wait_ld();
+              uint32_t w[NW];
+#pragma unroll
+              for (int i = 0; i < NW; ++i)
+                w[i] = pack_bf16(relu_finite(__uint_as_float(v[2 * i]) + t[2 * i]),
+                                 relu_finite(__uint_as_float(v[2 * i + 1]) + t[2 * i + 1]));
+              if (blk == 0) {
+                tmem_store_words<NW>(tl + TM::A1 + j * NW, w);
+              } else {
+                const uint32_t b0 = (uint32_t)slot0 * 2;
+#pragma unroll
+                for (int i = 0; i < NW; ++i) {
+                  uint32_t bo = b0 + 4 * i;
+                  *reinterpret_cast<uint32_t*>(sA3 + (bo >> 4) * 2048 + rowoff + (bo & 15)) = w[i];
+                }
+                fence_proxy_async_smem();
+              }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(op_bar);
+            {  // B: h += gate * (Wb relu(u) + bb)
+              float t[GSP], g[GSP];
+              const float* b = a.bbp + ((size_t)l * 2 + blk) * s.KTOT + slot0;
+              const float* gp = pl + (size_t)(blk + 1) * s.KTOT + slot0;
+#pragma unroll
+              for (int i = 0; i < GSP; ++i) { t[i] = __ldg(b + i); g[i] = __ldg(gp + i); }
+              if (!(ok = wait(acc_bar, acc_par, 14 + blk))) break;
+              acc_par ^= 1;
+              tc_fence_after();
+              uint32_t v[32];
+              tmem_ld32(tl + TM::ACC_H, v);
+              tmem_wait_ld();
+#pragma unroll
+              for (int i = 0; i < GSP; ++i) h[i] = fmaf(g[i], __uint_as_float(v[i]) + t[i], h[i]);
+              uint32_t w[NW];
+              if (blk == 0) {
+#pragma unroll
+                for (int i = 0; i < NW; ++i) w[i] = pack_bf16(relu_finite(h[2 * i]), relu_finite(h[2 * i + 1]));
+                tmem_store_words<NW>(tl + TM::A2 + j * NW, w);
+              } else {
+#pragma unroll
+                for (int i = 0; i < NW; ++i) w[i] = pack_bf16(finite_clamp(h[2 * i]), finite_clamp(h[2 * i + 1]));
+                const uint32_t b0 = (uint32_t)slot0 * 2;
+#pragma unroll
+                for (int i = 0; i < NW; ++i) {
+                  uint32_t bo = b0 + 4 * i;
+                  *reinterpret_cast<uint32_t*>(sA4 + (bo >> 4) * 2048 + rowoff + (bo & 15)) = w[i];
+                }
+                fence_proxy_async_smem();
+              }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(op_bar);
+          }
+        }
+        float* tsw = yin; yin = yout; yout = tsw;
+      }
+      if (!ok) break;
+      // ---------------- tail of inverse + ParamScaler (shared with the FP32 tier) ----------------
+      if (valid) {
+        float v[PF_MAX_D];
+#pragma unroll
+        for (int jj = 0; jj < PF_MAX_D; ++jj) v[jj] = jj < D ? yin[D - 1 - jj] : 0.f;
+        if (bad) {  // a non-finite value entered the conditioner: the reference turns the row into NaN
+          for (int jj = 0; jj < D; ++jj) v[jj] = __int_as_float(0x7fc00000);
+          ld_acc = __int_as_float(0x7fc00000);
+        }
+        const bool rail = finish_row(v, D, a.flags, a.clamp, a.sc);
+        for (int jj = 0; jj < D; ++jj) a.x[grow * D + jj] = v[jj];
+        if (a.logdet) a.logdet[grow] = ld_acc;
+        if (a.railed) a.railed[grow] = rail ? 1 : 0;
+      }
+    }
+  } else if (warp == 4) {
+    // ============================ MMA issuer ============================
+    if (lane == 0) {
+      uint32_t op_par = 0, slot = 0, full_par = 0;
+      int nstage = 0;
+      const uint32_t idesc_h = umma_idesc_bf16(TC_ROWS, 32), idesc_f = umma_idesc_bf16(TC_ROWS, s.NF);
+      const uint32_t aX = smem_u32(sX), aA3 = smem_u32(sA3), aA4 = smem_u32(sA4), aRing = smem_u32(ring);
+      bool ok = true;
+      for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
+        for (int l = s.L - 1; l >= 0 && ok; --l) {
+          for (int d = 1; d <= D && ok; ++d) {
+            for (int st = 0; st < ST_COUNT && ok; ++st) {
+              if (st > 0 && d == D) break;
+              const int nch = tc_nchunks(s, d, st);
+              if (nch == 0) continue;                   // F(1): bias only
+              if (nstage++ == a.dbg_stop) { *abort_s = 1; ok = false; break; }
+              if (!(ok = wait(op_bar, op_par, 20 + st))) break;
+              op_par ^= 1;
+              tc_fence_after();
+              const int N = tc_n(s, st);
+              const uint32_t idesc = st == ST_F ? idesc_f : idesc_h;
+              const uint32_t acc = tmem + (st == ST_F ? TM::ACC_F : (st == ST_I ? TM::ACC_I : TM::ACC_H));
+              const int pc = tc_piece(s, st, nch);
+              for (int c0 = 0; c0 < nch && ok; c0 += pc) {
+                const int nc = min(pc, nch - c0);
+                if (!(ok = wait(&full[slot], full_par, 30))) break;
+                tc_fence_after();
+                const uint32_t bbase = aRing + slot * s.slot_bytes;
+                for (int i = 0; i < nc; ++i) {
+                  const uint64_t bd = umma_smem_desc(bbase + (uint32_t)i * 2u * (uint32_t)(N * 16), N * 16, 128);
+                  const int c = c0 + i;
+                  if (st == ST_F || st == ST_I || st == ST_B2) {
+                    const uint32_t abase = st == ST_F ? aA4 : (st == ST_I ? aX : aA3);
+                    const uint64_t ad = umma_smem_desc(abase + (uint32_t)c * 4096u, 2048, 128);
+                    umma_ss(acc, ad, bd, idesc, c > 0);
+                  } else {
+                    const uint32_t at = tmem + (st == ST_A1 ? TM::A0 : (st == ST_B1 ? TM::A1 : TM::A2)) + c * 8;
+                    umma_ts(acc, at, bd, idesc, c > 0);
+                  }
+                }
+                umma_commit(&empty[slot]);
+                if (++slot == TC_NSLOT) { slot = 0; full_par ^= 1; }
+              }
+              if (ok) umma_commit(acc_bar);
+            }
+          }
+        }
+      }
+    }
+  } else {
+    // ============================ weight loader ============================
+    if (lane == 0) {
+      uint32_t slot = 0, empty_par = 1;   // a fresh barrier passes a wait on parity 1
+      bool ok = true;
+      for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
+        for (int l = s.L - 1; l >= 0 && ok; --l) {
+          const uint8_t* src = a.image + (size_t)l * s.layer_bytes;
+          for (int d = 1; d <= D && ok; ++d) {
+            for (int st = 0; st < ST_COUNT && ok; ++st) {
+              if (st > 0 && d == D) break;
+              const int nch = tc_nchunks(s, d, st);
+              if (nch == 0) continue;
+              const int N = tc_n(s, st);
+              const int pc = tc_piece(s, st, nch);
+              for (int c0 = 0; c0 < nch; c0 += pc) {
+                const uint32_t bytes = (uint32_t)min(pc, nch - c0) * (uint32_t)N * 32u;
+                if (!(ok = wait(&empty[slot], empty_par, 40))) break;
+                mbar_arrive_expect_tx(&full[slot], bytes);
+                bulk_g2s(ring + (size_t)slot * s.slot_bytes, src, bytes, &full[slot]);
+                src += bytes;
+                if (++slot == TC_NSLOT) { slot = 0; empty_par ^= 1; }
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) tmem_dealloc(tmem, 512);
+}
+
+}  // namespace pf
+using namespace pf;
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+static bool tc_plan(const pf_flow* f, TcShape& s, std::vector<TcItem>& items) {
+  memset(&s, 0, sizeof(s));
+  s.D = f->D; s.G = f->G; s.L = f->L; s.MULT = f->MULT; s.PLD = f->PLD;
+  if (f->NB != 16 || f->D > 16 || f->G > 10 || f->desc.num_blocks != 2) return false;
+  int gsp = (f->max_group + 1) / 2 * 2;
+  if (gsp != 26 && gsp != 20) return false;   // instantiated group sizes (H=256 | 192 at D=11)
+  s.GSP = gsp;
+  s.KTOT = s.G * gsp;
+  s.KA = round_up(s.KTOT, 16);
+  s.NF = round_up(s.MULT, 16);
+  for (int g = 0; g <= PF_MAX_D; ++g) s.off[g] = f->off[g];
+  s.slot_bytes = 32u * (uint32_t)s.KA * 2u;
+  s.pc_f = (int)(s.slot_bytes / ((uint32_t)s.NF * 32u));
+  uint32_t off = 0;
+  items.clear();
+  for (int d = 1; d <= s.D; ++d)
+    for (int st = 0; st < ST_COUNT; ++st) {
+      if (st > 0 && d == s.D) break;
+      int nch = tc_nchunks(s, d, st);
+      if (nch == 0) continue;
+      int pc = tc_piece(s, st, nch), N = tc_n(s, st);
+      for (int c0 = 0; c0 < nch; c0 += pc) {
+        int nc = std::min(pc, nch - c0);
+        items.push_back(TcItem{d, st, c0, nc, N, off});
+        off += (uint32_t)nc * N * 32u;
+      }
+    }
+  s.layer_bytes = off;
+  return true;
+}
+
+static int tc_smem_bytes(const TcShape& s) {
+  size_t y = (size_t)2 * TC_ROWS * s.D;
+  y += y & 1;
+  return (int)((size_t)2 * s.KA * 256 + 8192 + (size_t)TC_NSLOT * s.slot_bytes + y * 4 + (2 * TC_NSLOT + 4) * 8);
+}
+
+template <int NB, int GSP>
+static pf_status tc_launch(pf_flow* f, cudaStream_t st, const TcArgs& a, int smem) {
+  static bool attr_done[64] = {};
+  int dev = f->desc.device;
+  if (dev < 64 && !attr_done[dev]) {
+    PF_CUDA(cudaFuncSetAttribute(tc_sampler_kernel<NB, GSP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_done[dev] = true;
+  }
+  int grid = a.n_tiles < f->sm_count ? a.n_tiles : f->sm_count;
+  tc_sampler_kernel<NB, GSP><<<grid, TC_THREADS, smem, st>>>(a);
+  PF_LAUNCH_CHECK(f);
+  return PF_OK;
+}
+
+pf_status pf_tc_pack(pf_flow* f, cudaStream_t st) {
+  if (f->desc.tier != PF_TIER_BF16) return PF_OK;
+  TcShape s;
+  std::vector<TcItem> items;
+  if (!tc_plan(f, s, items)) return PF_ERR_UNSUPPORTED;
+  TcState* t = reinterpret_cast<TcState*>(f->tc);
+  const size_t L = f->L, KT = s.KTOT, C = f->C;
+  if (!t) {
+    t = new TcState();
+    memset(t, 0, sizeof(*t));
+    t->shape = s;
+    t->n_items = (int)items.size();
+    t->kernel_smem = tc_smem_bytes(s);
+    const char* dbg = getenv("PF_TC_DEBUG");
+    t->debug_sync = dbg && dbg[0] == '1';
+    size_t nf = L * KT + 2 * (L * 2 * KT) + L * 3 * KT * C + L * 3 * KT;
+    cudaError_t e = cudaMalloc(&t->image, L * s.layer_bytes);
+    if (e == cudaSuccess) e = cudaMalloc(&t->arena, nf * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&t->err, sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc(&t->d_items, items.size() * sizeof(TcItem));
+    if (e == cudaSuccess) e = cudaMemcpy(t->d_items, items.data(), items.size() * sizeof(TcItem), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemset(t->err, 0, sizeof(int));
+    if (e != cudaSuccess) {
+      if (t->image) cudaFree(t->image);
+      if (t->arena) cudaFree(t->arena);
+      if (t->err) cudaFree(t->err);
+      if (t->d_items) cudaFree(t->d_items);
+      delete t;
+      return cuda_fail(e, "tensor-core tier allocation", __FILE__, __LINE__);
+    }
+    float* p = t->arena;
+    t->b0p = p; p += L * KT;
+    t->bap = p; p += L * 2 * KT;
+    t->bbp = p; p += L * 2 * KT;
+    t->Wctxp = p; p += L * 3 * KT * C;
+    t->bctxp = p;
+    f->tc = t;
+  }
+  dim3 grid(t->n_items, f->L);
+  tc_pack_image_kernel<<<grid, 256, 0, st>>>(s, t->d_items, t->image, f->W0, f->DP, f->Wa, f->Wb, f->Wf, f->H);
+  PF_LAUNCH_CHECK(f);
+  auto padvec = [&](const float* src, float* dst, int rows) -> pf_status {
+    int n = rows * s.KTOT;
+    tc_pad_vec_kernel<<<(n + 255) / 256, 256, 0, st>>>(s, src, f->H, dst, rows);
+    PF_LAUNCH_CHECK(f);
+    return PF_OK;
+  };
+  PF_TRY(padvec(f->b0, t->b0p, f->L));
+  PF_TRY(padvec(f->ba, t->bap, f->L * 2));
+  PF_TRY(padvec(f->bb, t->bbp, f->L * 2));
+  PF_TRY(padvec(f->bctx, t->bctxp, f->L * 3));
+  {
+    int64_t n = (int64_t)f->L * 3 * s.KTOT * f->C;
+    tc_pad_rows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(s, f->Wctx, f->H, f->C, t->Wctxp, f->L * 3);
+    PF_LAUNCH_CHECK(f);
+  }
+  return PF_OK;
+}
+
+void pf_tc_destroy(pf_flow* f) {
+  TcState* t = reinterpret_cast<TcState*>(f->tc);
+  if (!t) return;
+  cudaFree(t->image); cudaFree(t->arena); cudaFree(t->err); cudaFree(t->d_items);
+  delete t;
+  f->tc = nullptr;
+}
+
+// proj[e, (l*3 + sec)*KTOT + slot] in the padded slot order of this tier
+struct EpiCtxProjPad {
+  float* out; int ld; const float* bias; int KT;
+  __device__ __forceinline__ void operator()(int m, int n, float acc) const {
+    float v = acc + bias[n];
+    int sec = (n / KT) % 3;
+    out[(int64_t)m * ld + n] = sec == 0 ? fmaxf(v, 0.f) : 1.f / (1.f + expf(-v));
+  }
+};
+
+pf_status pf_tc_ctxproj(pf_flow* f, cudaStream_t st, const float* ctx, int64_t E, uint32_t flags, float* proj) {
+  TcState* t = reinterpret_cast<TcState*>(f->tc);
+  if (!t) return PF_ERR_NOT_PACKED;
+  const int N = f->L * 3 * t->shape.KTOT;
+  EpiCtxProjPad epi{proj, N, t->bctxp, t->shape.KTOT};
+  if (flags & PF_FLAG_SANITIZE_CTX)
+    return sgemm_nt<EpiCtxProjPad, A_SANITIZE, 64>(f, st, ctx, f->C, t->Wctxp, f->C, (int)E, N, f->C, epi);
+  return sgemm_nt<EpiCtxProjPad, A_PLAIN, 64>(f, st, ctx, f->C, t->Wctxp, f->C, (int)E, N, f->C, epi);
+}
+
+size_t pf_tc_workspace_bytes(const pf_flow* f, int64_t R, int64_t E) {
+  const TcState* t = reinterpret_cast<const TcState*>(f->tc);
+  int KT = t ? t->shape.KTOT : f->G * 32;
+  const int64_t chunk = R < PF_ROW_CHUNK ? R : PF_ROW_CHUNK;
+  const int64_t prow = E > chunk ? E : chunk;
+  return (size_t)prow * f->L * 3 * KT * sizeof(float) + 512;
+}
+
+pf_status pf_tc_inverse(pf_flow* f, cudaStream_t st, const float* z, uint64_t seed, const float* ctx,
+                        const int64_t* row2ctx, int64_t n_per_ctx, int64_t R, int64_t E, float* x, float* logdet,
+                        uint8_t* railed, uint32_t flags, const pf_scaler* scaler, void* workspace,
+                        size_t workspace_bytes) {
+  TcState* t = reinterpret_cast<TcState*>(f->tc);
+  if (!t) return PF_ERR_NOT_PACKED;
+  const TcShape& s = t->shape;
+  const bool is_proj = flags & PF_FLAG_CTX_IS_PROJ;
+  const bool dense = !row2ctx && n_per_ctx == 1;
+  const int64_t ldproj = (int64_t)f->L * 3 * s.KTOT;
+  const int64_t chunk = dense ? (R < PF_ROW_CHUNK ? R : PF_ROW_CHUNK) : R;
+  const int64_t prow = is_proj ? 0 : (dense ? chunk : E);
+  if ((size_t)prow * ldproj * sizeof(float) > workspace_bytes || (prow && !workspace)) return PF_ERR_WORKSPACE;
+  float* wproj = reinterpret_cast<float*>(workspace);
+  ScalerDev sc{nullptr, nullptr, nullptr, nullptr};
+  if (flags & (PF_FLAG_WRAP | PF_FLAG_DENORMALIZE)) {
+    if (!scaler || !scaler->lo || !scaler->hi || !scaler->log_mask || !scaler->circ_mask) return PF_ERR_INVALID;
+    sc = ScalerDev{scaler->lo, scaler->hi, scaler->log_mask, scaler->circ_mask};
+  }
+  const float* proj_all = nullptr;
+  if (is_proj) proj_all = ctx;
+  else if (!dense) {
+    PF_TRY(pf_tc_ctxproj(f, st, ctx, E, flags, wproj));
+    proj_all = wproj;
+  }
+  for (int64_t r0 = 0; r0 < R; r0 += chunk) {
+    const int64_t rows = (R - r0) < chunk ? (R - r0) : chunk;
+    TcArgs a;
+    memset(&a, 0, sizeof(a));
+    a.s = s;
+    a.image = t->image;
+    a.b0p = t->b0p; a.bap = t->bap; a.bbp = t->bbp; a.bf = f->bf;
+    a.ldproj = ldproj;
+    if (proj_all) {
+      a.proj = proj_all;
+      a.cm = CtxMap{row2ctx, n_per_ctx, r0};
+    } else {
+      PF_TRY(pf_tc_ctxproj(f, st, ctx + r0 * f->C, rows, flags, wproj));
+      a.proj = wproj;
+      a.cm = CtxMap{nullptr, 1, 0};
+    }
+    a.z = z ? z + r0 * s.D : nullptr;
+    a.seed = seed;
+    a.R = rows;
+    a.row_base = r0;
+    a.n_tiles = (int)((rows + TC_ROWS - 1) / TC_ROWS);
+    a.x = x + r0 * s.D;
+    a.logdet = logdet ? logdet + r0 : nullptr;
+    a.railed = railed ? railed + r0 : nullptr;
+    a.flags = flags; a.tail = f->desc.tail_bound; a.clamp = f->desc.clamp_bound;
+    a.sc = sc;
+    a.err = t->err;
+    {
+      const char* stop = getenv("PF_TC_STOP");
+      a.dbg_stop = stop ? atoi(stop) : -1;
+    }
+    if (s.GSP == 26) PF_TRY((tc_launch<16, 26>(f, st, a, t->kernel_smem)));
+    else PF_TRY((tc_launch<16, 20>(f, st, a, t->kernel_smem)));
+  }
+  if (t->debug_sync) {
+    int herr = 0;
+    PF_CUDA(cudaStreamSynchronize(st));
+    PF_CUDA(cudaMemcpy(&herr, t->err, sizeof(int), cudaMemcpyDeviceToHost));
+    if (herr) {
+      snprintf(g_cuda_err, sizeof(g_cuda_err), "tensor-core sampler: barrier timeout, code %d", herr);
+      cudaMemset(t->err, 0, sizeof(int));
+      return PF_ERR_CUDA;
+    }
+  }
+  return PF_OK;
+}

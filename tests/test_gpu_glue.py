@@ -122,7 +122,8 @@ def test_round_trip_inverse_then_forward(R):
         z2, ld2 = flow.forward(x, ctx, n_per_ctx=R)
     # the inverse is ill-conditioned where a bin is steep, so the maximum over 11*R draws grows with R;
     # the bulk must close to float32 round-off
-    dz, dl = (z2 - z).abs().flatten(), (ld + ld2).abs()
+    # (log-dets are sums of 110 terms of magnitude O(1): compare relative to max(1, |logdet|))
+    dz, dl = (z2 - z).abs().flatten(), (ld + ld2).abs() / ld.abs().clamp_min(1.0)
     assert float(dz.median()) <= 1e-5 and float(dl.median()) <= 5e-5
     if R >= 1000:
         assert float(torch.quantile(dz[:1000000], 0.999)) <= 2e-4
