@@ -65,6 +65,7 @@ struct TcState {
   TcItem* d_items; int n_items;
   int kernel_smem;
   bool debug_sync;
+  long long* prof;       // device, 16 counters (PF_TC_PROF=1)
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -142,6 +143,7 @@ struct TcArgs {
   ScalerDev sc;
   int* err;
   int dbg_stop;        // >= 0: leave after this many MMA stages (bring-up aid, PF_TC_STOP)
+  long long* prof;     // NULL, or 16 cycle counters filled by CTA 0 (PF_TC_PROF=1)
 };
 
 // TMEM column map (512 columns allocated)
@@ -152,7 +154,8 @@ struct TcTmem {
   // multiple of 4 columns (measured: tests/tmem_align_probe.cu), tcgen05.ld/st accept any column.
   static constexpr int ARR = (10 * NW + 3) / 4 * 4;
   static constexpr int A0 = 0, A1 = ARR, A2 = 2 * ARR, PAD = 3 * ARR;
-  static constexpr int ACC_F = (PAD + 8 + 15) / 16 * 16;  // >= 8 zero columns after the last array
+  static constexpr int KCOLS = (10 * GSP + 15) / 16 * 8;  // columns the widest K loop reads from one array
+  static constexpr int ACC_F = (A2 + KCOLS + 15) / 16 * 16;  // zero pad columns between the last array and ACC_F
   static constexpr int ACC_H = ACC_F + 48;
   static constexpr int ACC_I = ACC_H + 32;
   static_assert(ACC_I + 32 <= 512, "TMEM budget");
@@ -201,7 +204,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
   volatile int* abort_s = reinterpret_cast<volatile int*>(bars + 2 * TC_NSLOT + 2);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_NSLOT + 3);
 
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // provably warp-uniform role index
 
   if (tid == 0) {
     for (int i = 0; i < TC_NSLOT; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
@@ -230,7 +234,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
     return false;
   };
 
-  if (warp < 4) {
+  const int lvl = a.dbg_stop;
+  if (warp < 4 && lvl != -11) {
     // ============================ row warps ============================
     const int r = tid;
     const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16);   // this warp's TMEM lane window
@@ -242,8 +247,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
       tmem_wait_st();
     }
     uint32_t acc_par = 0;
+    const bool prof = a.prof && blockIdx.x == 0 && tid == 0;
+    long long pw[6] = {0, 0, 0, 0, 0, 0}, pc[6] = {0, 0, 0, 0, 0, 0};
+    long long tmark = clock64();
+    const long long t_begin = tmark;
+    // account the time since the last mark to "compute of stage a" / "wait of stage b"
+    auto mark_c = [&](int st) { if (prof) { long long n = clock64(); pc[st] += n - tmark; tmark = n; } };
+    auto mark_w = [&](int st) { if (prof) { long long n = clock64(); pw[st] += n - tmark; tmark = n; } };
     const uint32_t rowoff = (uint32_t)(r / 8) * 128 + (uint32_t)(r % 8) * 16;
-    bool ok = true;
+    bool ok = !(lvl == -12 || lvl == -13);
     for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
       const int64_t grow = (int64_t)tile * TC_ROWS + r;
       const bool valid = grow < a.R;
@@ -281,7 +293,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
             q[47] = 0.f;
             const float y = yin[reversed ? D - 1 - j : j];
             if (d > 1) {
+              mark_c(ST_F);
               if (!(ok = wait(acc_bar, acc_par, 10))) break;
+              mark_w(ST_F);
               acc_par ^= 1;
               tc_fence_after();
               uint32_t v[48];
@@ -302,6 +316,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
             *reinterpret_cast<__nv_bfloat16*>(sX + (j / 8) * 2048 + rowoff + (j % 8) * 2) = hi;
             *reinterpret_cast<__nv_bfloat16*>(sX + (2 + j / 8) * 2048 + rowoff + (j % 8) * 2) = lo;
           }
+          mark_c(ST_F);
           if (d == D) break;  // last dim: no hidden group follows, and the next stage (F(1)) has no MMA
           fence_proxy_async_smem();
           tc_fence_before();
@@ -316,7 +331,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
             const float* b = a.b0p + (size_t)l * s.KTOT + slot0;
 #pragma unroll
             for (int i = 0; i < GSP; ++i) t[i] = __ldg(b + i) + __ldg(pl + slot0 + i);
+            mark_c(ST_I);
             if (!(ok = wait(acc_bar, acc_par, 11))) break;
+            mark_w(ST_I);
             acc_par ^= 1;
             tc_fence_after();
             uint32_t v[32];
@@ -340,7 +357,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
               const float* b = a.bap + ((size_t)l * 2 + blk) * s.KTOT + slot0;
 #pragma unroll
               for (int i = 0; i < GSP; ++i) t[i] = __ldg(b + i);
+              mark_c(ST_A1 + 2 * blk);
               if (!(ok = wait(acc_bar, acc_par, 12 + blk))) break;
+              mark_w(ST_A1 + 2 * blk);
               acc_par ^= 1;
               tc_fence_after();
               uint32_t v[32];
@@ -372,7 +391,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
               const float* gp = pl + (size_t)(blk + 1) * s.KTOT + slot0;
 #pragma unroll
               for (int i = 0; i < GSP; ++i) { t[i] = __ldg(b + i); g[i] = __ldg(gp + i); }
+              mark_c(ST_B1 + 2 * blk);
               if (!(ok = wait(acc_bar, acc_par, 14 + blk))) break;
+              mark_w(ST_B1 + 2 * blk);
               acc_par ^= 1;
               tc_fence_after();
               uint32_t v[32];
@@ -420,11 +441,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
         if (a.railed) a.railed[grow] = rail ? 1 : 0;
       }
     }
+    if (prof) {
+      for (int i = 0; i < 6; ++i) { a.prof[i] = pw[i]; a.prof[6 + i] = pc[i]; }
+      a.prof[15] = clock64() - t_begin;
+    }
   } else if (warp == 4) {
     // ============================ MMA issuer ============================
-    if (lane == 0) {
+    // the whole warp runs the (warp-uniform) loops; one elected lane issues tcgen05.mma / commit
+    if (lvl <= -13) *abort_s = 1;
+    if (lvl > -11) {
       uint32_t op_par = 0, slot = 0, full_par = 0;
       int nstage = 0;
+      const bool mprof = a.prof && blockIdx.x == 0;
+      long long m_op = 0, m_full = 0, m_issue = 0;
       const uint32_t idesc_h = umma_idesc_bf16(TC_ROWS, 32), idesc_f = umma_idesc_bf16(TC_ROWS, s.NF);
       const uint32_t aX = smem_u32(sX), aA3 = smem_u32(sA3), aA4 = smem_u32(sA4), aRing = smem_u32(ring);
       bool ok = true;
@@ -436,7 +465,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
               const int nch = tc_nchunks(s, d, st);
               if (nch == 0) continue;                   // F(1): bias only
               if (nstage++ == a.dbg_stop) { *abort_s = 1; ok = false; break; }
+              long long t0 = mprof ? clock64() : 0;
               if (!(ok = wait(op_bar, op_par, 20 + st))) break;
+              if (mprof) { long long n = clock64(); m_op += n - t0; t0 = n; }
               op_par ^= 1;
               tc_fence_after();
               const int N = tc_n(s, st);
@@ -445,33 +476,42 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
               const int pc = tc_piece(s, st, nch);
               for (int c0 = 0; c0 < nch && ok; c0 += pc) {
                 const int nc = min(pc, nch - c0);
+                long long t1 = mprof ? clock64() : 0;
                 if (!(ok = wait(&full[slot], full_par, 30))) break;
+                if (mprof) m_full += clock64() - t1;
                 tc_fence_after();
                 const uint32_t bbase = aRing + slot * s.slot_bytes;
-                for (int i = 0; i < nc; ++i) {
-                  const uint64_t bd = umma_smem_desc(bbase + (uint32_t)i * 2u * (uint32_t)(N * 16), N * 16, 128);
-                  const int c = c0 + i;
+                if (elect_one_sync()) {
                   if (st == ST_F || st == ST_I || st == ST_B2) {
                     const uint32_t abase = st == ST_F ? aA4 : (st == ST_I ? aX : aA3);
-                    const uint64_t ad = umma_smem_desc(abase + (uint32_t)c * 4096u, 2048, 128);
-                    umma_ss(acc, ad, bd, idesc, c > 0);
+                    for (int i = 0; i < nc; ++i) {
+                      const uint64_t bd = umma_smem_desc(bbase + (uint32_t)i * 2u * (uint32_t)(N * 16), N * 16, 128);
+                      const uint64_t ad = umma_smem_desc(abase + (uint32_t)(c0 + i) * 4096u, 2048, 128);
+                      umma_ss(acc, ad, bd, idesc, (c0 + i) > 0);
+                    }
                   } else {
-                    const uint32_t at = tmem + (st == ST_A1 ? TM::A0 : (st == ST_B1 ? TM::A1 : TM::A2)) + c * 8;
-                    umma_ts(acc, at, bd, idesc, c > 0);
+                    const uint32_t at = tmem + (st == ST_A1 ? TM::A0 : (st == ST_B1 ? TM::A1 : TM::A2));
+                    for (int i = 0; i < nc; ++i) {
+                      const uint64_t bd = umma_smem_desc(bbase + (uint32_t)i * 2u * (uint32_t)(N * 16), N * 16, 128);
+                      umma_ts(acc, at + (c0 + i) * 8, bd, idesc, (c0 + i) > 0);
+                    }
                   }
+                  umma_commit(&empty[slot]);
+                  if (c0 + nc >= nch) umma_commit(acc_bar);
                 }
-                umma_commit(&empty[slot]);
+                __syncwarp();
                 if (++slot == TC_NSLOT) { slot = 0; full_par ^= 1; }
               }
-              if (ok) umma_commit(acc_bar);
+              if (mprof) m_issue += clock64() - t0;
             }
           }
         }
       }
+      if (mprof && lane == 0) { a.prof[12] = m_op; a.prof[13] = m_full; a.prof[14] = m_issue; }
     }
   } else {
     // ============================ weight loader ============================
-    if (lane == 0) {
+    if (lvl != -11 && lvl != -12) {
       uint32_t slot = 0, empty_par = 1;   // a fresh barrier passes a wait on parity 1
       bool ok = true;
       for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
@@ -487,8 +527,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
               for (int c0 = 0; c0 < nch; c0 += pc) {
                 const uint32_t bytes = (uint32_t)min(pc, nch - c0) * (uint32_t)N * 32u;
                 if (!(ok = wait(&empty[slot], empty_par, 40))) break;
-                mbar_arrive_expect_tx(&full[slot], bytes);
-                bulk_g2s(ring + (size_t)slot * s.slot_bytes, src, bytes, &full[slot]);
+                if (elect_one_sync()) {
+                  mbar_arrive_expect_tx(&full[slot], bytes);
+                  bulk_g2s(ring + (size_t)slot * s.slot_bytes, src, bytes, &full[slot]);
+                }
+                __syncwarp();
                 src += bytes;
                 if (++slot == TC_NSLOT) { slot = 0; empty_par ^= 1; }
               }
@@ -575,6 +618,8 @@ pf_status pf_tc_pack(pf_flow* f, cudaStream_t st) {
     t->kernel_smem = tc_smem_bytes(s);
     const char* dbg = getenv("PF_TC_DEBUG");
     t->debug_sync = dbg && dbg[0] == '1';
+    const char* pr = getenv("PF_TC_PROF");
+    if (pr && pr[0] == '1' && cudaMalloc(&t->prof, 16 * sizeof(long long)) != cudaSuccess) t->prof = nullptr;
     size_t nf = L * KT + 2 * (L * 2 * KT) + L * 3 * KT * C + L * 3 * KT;
     cudaError_t e = cudaMalloc(&t->image, L * s.layer_bytes);
     if (e == cudaSuccess) e = cudaMalloc(&t->arena, nf * sizeof(float));
@@ -623,6 +668,7 @@ void pf_tc_destroy(pf_flow* f) {
   TcState* t = reinterpret_cast<TcState*>(f->tc);
   if (!t) return;
   cudaFree(t->image); cudaFree(t->arena); cudaFree(t->err); cudaFree(t->d_items);
+  if (t->prof) cudaFree(t->prof);
   delete t;
   f->tc = nullptr;
 }
@@ -661,6 +707,13 @@ pf_status pf_tc_inverse(pf_flow* f, cudaStream_t st, const float* z, uint64_t se
                         size_t workspace_bytes) {
   TcState* t = reinterpret_cast<TcState*>(f->tc);
   if (!t) return PF_ERR_NOT_PACKED;
+  if (t->debug_sync) {
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) {
+      snprintf(g_cuda_err, sizeof(g_cuda_err), "error pending on entry of inverse: %s", cudaGetErrorString(e));
+      return PF_ERR_CUDA;
+    }
+  }
   const TcShape& s = t->shape;
   const bool is_proj = flags & PF_FLAG_CTX_IS_PROJ;
   const bool dense = !row2ctx && n_per_ctx == 1;
@@ -679,6 +732,14 @@ pf_status pf_tc_inverse(pf_flow* f, cudaStream_t st, const float* z, uint64_t se
   else if (!dense) {
     PF_TRY(pf_tc_ctxproj(f, st, ctx, E, flags, wproj));
     proj_all = wproj;
+    if (t->debug_sync) {
+      cudaError_t e = cudaStreamSynchronize(st);
+      if (e != cudaSuccess) {
+        snprintf(g_cuda_err, sizeof(g_cuda_err), "ctxproj in inverse: %s (ctx %p E %lld wproj %p)", cudaGetErrorString(e),
+                 (const void*)ctx, (long long)E, (void*)wproj);
+        return PF_ERR_CUDA;
+      }
+    }
   }
   for (int64_t r0 = 0; r0 < R; r0 += chunk) {
     const int64_t rows = (R - r0) < chunk ? (R - r0) : chunk;
@@ -707,12 +768,24 @@ pf_status pf_tc_inverse(pf_flow* f, cudaStream_t st, const float* z, uint64_t se
     a.flags = flags; a.tail = f->desc.tail_bound; a.clamp = f->desc.clamp_bound;
     a.sc = sc;
     a.err = t->err;
+    a.prof = t->prof;
     {
       const char* stop = getenv("PF_TC_STOP");
       a.dbg_stop = stop ? atoi(stop) : -1;
     }
+    if (a.dbg_stop == -10) continue;
     if (s.GSP == 26) PF_TRY((tc_launch<16, 26>(f, st, a, t->kernel_smem)));
     else PF_TRY((tc_launch<16, 20>(f, st, a, t->kernel_smem)));
+  }
+  if (t->prof) {
+    long long h[16];
+    PF_CUDA(cudaStreamSynchronize(st));
+    PF_CUDA(cudaMemcpy(h, t->prof, sizeof(h), cudaMemcpyDeviceToHost));
+    const char* nm[6] = {"F", "I", "A1", "B1", "A2", "B2"};
+    fprintf(stderr, "[pf_tc prof] CTA0 rows: total %lld cycles\n", h[15]);
+    for (int i = 0; i < 6; ++i) fprintf(stderr, "[pf_tc prof]   stage %-2s wait %10lld  compute %10lld\n", nm[i], h[i], h[6 + i]);
+    fprintf(stderr, "[pf_tc prof] MMA thread: wait-operands %lld  wait-weights %lld  stage total (incl. waits) %lld\n", h[12],
+            h[13], h[14]);
   }
   if (t->debug_sync) {
     int herr = 0;
