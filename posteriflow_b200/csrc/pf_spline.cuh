@@ -266,4 +266,85 @@ PF_HD float rqs_forward_backward(const P& prm, float x, float B, float gy, float
   return gx;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Tensor-core tier variant of the inverse map (same formulas, Appendix A.5-A.7) built for a lone warp per
+// scheduler: hardware ex2 / lg2 / rcp approximations (about 2^-21 relative, far below that tier's bf16
+// operand rounding), one logarithm for the log-determinant, and the two softmax/cumsum chains written
+// side by side so their dependent instruction chains interleave.  q[0,NB) widths, [NB,2NB) heights,
+// [2NB,3NB-1) interior knot derivatives (unnormalised).
+#ifdef __CUDACC__
+// single-instruction MUFU forms (flush-to-zero, no range fix-up code around them)
+__device__ __forceinline__ float fx_ex2(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float fx_lg2(float x) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float fx_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float fx_sqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float fx_exp(float x) { return fx_ex2(x * 1.4426950408889634f); }
+__device__ __forceinline__ float fx_log(float x) { return fx_lg2(x) * 0.6931471805599453f; }
+
+template <int NB>
+__device__ __forceinline__ float rqs_inverse_fast(const float* q, float y, float B, float& lad) {
+  if (!(y >= -B && y <= B)) {
+    lad = 0.f;
+    return y;
+  }
+  float mw = q[0], mh = q[NB];
+#pragma unroll
+  for (int i = 1; i < NB; ++i) {
+    mw = fmaxf(mw, q[i]);
+    mh = fmaxf(mh, q[NB + i]);
+  }
+  float ew[NB], eh[NB];
+  float sw0 = 0.f, sw1 = 0.f, sh0 = 0.f, sh1 = 0.f;
+#pragma unroll
+  for (int i = 0; i < NB; i += 2) {
+    ew[i] = fx_ex2((q[i] - mw) * 1.4426950408889634f);
+    ew[i + 1] = fx_exp(q[i + 1] - mw);
+    eh[i] = fx_exp(q[NB + i] - mh);
+    eh[i + 1] = fx_exp(q[NB + i + 1] - mh);
+    sw0 += ew[i]; sw1 += ew[i + 1];
+    sh0 += eh[i]; sh1 += eh[i + 1];
+  }
+  const float scale = 1.f - kMinBin * NB;
+  const float cw = (2.f * B) * scale * fx_rcp(sw0 + sw1);   // knot spacing contributed by e_i
+  const float ch = (2.f * B) * scale * fx_rcp(sh0 + sh1);
+  const float base = (2.f * B) * kMinBin;
+  // walk both knot sequences; the bin is found on the height axis, the width axis is gathered at it
+  int k = 0;
+  float yk = -B, hk = 0.f, xk = -B, wk = 0.f;
+  float py = -B, px = -B, cy = 0.f, cx = 0.f;
+#pragma unroll
+  for (int i = 0; i < NB; ++i) {
+    cy += fmaf(ch, eh[i], base);
+    cx += fmaf(cw, ew[i], base);
+    const float ny = (i == NB - 1) ? B : cy - B;
+    const float nx = (i == NB - 1) ? B : cx - B;
+    if (i == 0 || y >= py) { k = i; yk = py; hk = ny - py; xk = px; wk = nx - px; }
+    py = ny; px = nx;
+  }
+  float u0 = kEdgeLogit, u1 = kEdgeLogit;
+#pragma unroll
+  for (int i = 0; i < NB - 1; ++i) {
+    const float u = q[2 * NB + i];
+    if (i + 1 == k) u0 = u;
+    if (i == k) u1 = u;
+  }
+  const float dk = kMinDeriv + (u0 > 20.f ? u0 : fx_log(1.f + fx_exp(u0)));
+  const float dk1 = kMinDeriv + (u1 > 20.f ? u1 : fx_log(1.f + fx_exp(u1)));
+  const float s = hk * fx_rcp(wk);
+  const float dy = y - yk;
+  const float t = dk + dk1 - 2.f * s;
+  const float qa = fmaf(dy, t, hk * (s - dk));
+  const float qb = fmaf(hk, dk, -dy * t);
+  const float qc = -s * dy;
+  const float disc = fmaxf(fmaf(qb, qb, -4.f * qa * qc), 0.f);
+  const float root = 2.f * qc * fx_rcp(-qb - fx_sqrt(disc));
+  const float tt = root * (1.f - root);
+  const float den = fmaf(t, tt, s);
+  const float omr = 1.f - root;
+  const float dnum = s * s * (dk1 * root * root + 2.f * s * tt + dk * omr * omr);
+  lad = -fx_log(dnum * fx_rcp(den * den));
+  return fmaf(root, wk, xk);
+}
+#endif
+
 }  // namespace pf

@@ -32,8 +32,11 @@ namespace pf {
 using namespace pf::sm100;
 
 constexpr int TC_ROWS = 128;      // rows per tile = UMMA M = TMEM lanes
-constexpr int TC_NSLOT = 4;       // weight ring depth
-constexpr int TC_THREADS = 192;
+constexpr int TC_NSLOT = 3;       // weight ring depth
+constexpr int TC_THREADS = 224;   // 4 row warps + MMA warp + weight-loader warp + constants-stager warp
+constexpr int TC_CB_BF = 48;      // per-step constants buffer (floats): bf[48] | 5 bias groups | 2 events x 3 ctx groups
+__host__ __device__ constexpr int tc_gs4(int gsp) { return (gsp + 3) / 4 * 4; }
+__host__ __device__ constexpr int tc_cb_floats(int gsp) { return TC_CB_BF + 11 * tc_gs4(gsp); }
 
 // stage order inside step d of a layer (d = 1..D; the hidden stages exist for d < D)
 enum { ST_F = 0, ST_I = 1, ST_A1 = 2, ST_B1 = 3, ST_A2 = 4, ST_B2 = 5, ST_COUNT = 6 };
@@ -196,13 +199,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
   uint8_t* sX = sA4 + (size_t)KA * 256;
   uint8_t* ring = sX + 8192;
   float* ybuf = reinterpret_cast<float*>(ring + (size_t)TC_NSLOT * s.slot_bytes);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(ybuf + 2 * TC_ROWS * D + ((2 * TC_ROWS * D) & 1));
+  constexpr int GS4 = tc_gs4(GSP), CBF = tc_cb_floats(GSP);
+  float* cbuf = ybuf + (2 * TC_ROWS * D + 3) / 4 * 4;   // [2][CBF] per-step constants, staged by warp 6
+  uint64_t* bars = reinterpret_cast<uint64_t*>(cbuf + 2 * CBF);
   uint64_t* full = bars;                 // [NSLOT] weights landed
   uint64_t* empty = bars + TC_NSLOT;     // [NSLOT] MMAs reading the slot completed
   uint64_t* acc_bar = bars + 2 * TC_NSLOT;      // accumulator of the current stage complete
   uint64_t* op_bar = bars + 2 * TC_NSLOT + 1;   // operands of the next stage written (4 warp arrivals)
-  volatile int* abort_s = reinterpret_cast<volatile int*>(bars + 2 * TC_NSLOT + 2);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_NSLOT + 3);
+  uint64_t* cfull = bars + 2 * TC_NSLOT + 2;    // [2] constants of a step staged
+  uint64_t* cempty = bars + 2 * TC_NSLOT + 4;   // [2] constants of a step consumed (4 warp arrivals)
+  volatile int* abort_s = reinterpret_cast<volatile int*>(bars + 2 * TC_NSLOT + 6);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_NSLOT + 7);
 
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // provably warp-uniform role index
@@ -211,6 +218,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
     for (int i = 0; i < TC_NSLOT; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     mbar_init(acc_bar, 1);
     mbar_init(op_bar, 4);
+    for (int i = 0; i < 2; ++i) { mbar_init(&cfull[i], 1); mbar_init(&cempty[i], 4); }
     *abort_s = 0;
     fence_mbar_init();
   }
@@ -246,14 +254,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
       for (int c = 0; c < TM::ACC_F; c += 16) tmem_st16(tl + c, zz);
       tmem_wait_st();
     }
-    uint32_t acc_par = 0;
+    uint32_t acc_par = 0, stepc = 0;
     const bool prof = a.prof && blockIdx.x == 0 && tid == 0;
     long long pw[6] = {0, 0, 0, 0, 0, 0}, pc[6] = {0, 0, 0, 0, 0, 0};
     long long tmark = clock64();
     const long long t_begin = tmark;
     // account the time since the last mark to "compute of stage a" / "wait of stage b"
-    auto mark_c = [&](int st) { if (prof) { long long n = clock64(); pc[st] += n - tmark; tmark = n; } };
-    auto mark_w = [&](int st) { if (prof) { long long n = clock64(); pw[st] += n - tmark; tmark = n; } };
+    int pcur = ST_F;   // stage whose epilogue is running
+    auto mark_c = [&](int) { if (prof) { long long n = clock64(); pc[pcur] += n - tmark; tmark = n; } };
+    auto mark_w = [&](int st) { if (prof) { long long n = clock64(); pw[st] += n - tmark; tmark = n; pcur = st; } };
     const uint32_t rowoff = (uint32_t)(r / 8) * 128 + (uint32_t)(r % 8) * 16;
     bool ok = !(lvl == -12 || lvl == -13);
     for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
@@ -274,7 +283,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
         }
         for (int j = 0; j < D; ++j) y0[j] = zr[j];
       }
-      const float* projr = a.proj + (valid ? a.cm(grow) : 0) * a.ldproj;
+      // context constants: staged in shared memory for the (at most two) events of this tile when rows map
+      // to contexts in contiguous runs of >= 128; otherwise each row reads its own projection from L2
+      const bool ctx_staged = !a.cm.row2ctx && a.cm.n_per_ctx >= TC_ROWS;
+      const int64_t cidx = valid ? a.cm(grow) : a.cm((int64_t)tile * TC_ROWS);
+      const int esel = (ctx_staged && cidx != a.cm((int64_t)tile * TC_ROWS)) ? 1 : 0;
+      const float* projr = a.proj + cidx * a.ldproj;
       float ld_acc = 0.f;
       bool bad = false;
       float* yin = y0;
@@ -284,13 +298,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
         const float* pl = projr + (size_t)l * 3 * s.KTOT;
         for (int d = 1; d <= D && ok; ++d) {
           const int j = d - 1;
+          // this step's constants (biases, context gates), staged by warp 6 one step ahead
+          const float* cb = cbuf + (stepc & 1) * CBF;
+          if (!(ok = wait(&cfull[stepc & 1], (stepc >> 1) & 1, 16))) break;
+          const float* cbb = cb + TC_CB_BF;                      // 5 bias groups of GS4 floats
+          const float* cbc = cbb + 5 * GS4 + esel * 3 * GS4;      // 3 context groups of this row's event
           // ---------------- F(d): spline parameters of dim d -> inverse spline ----------------
           {
+            if (d == 1) { mark_c(0); pcur = ST_F; }
             float q[48];
-            const float* bfl = a.bf + (size_t)l * s.PLD + (size_t)j * MULT;
 #pragma unroll
-            for (int i = 0; i < MULT; ++i) q[i] = __ldg(bfl + i);
-            q[47] = 0.f;
+            for (int i = 0; i < 48; i += 4) {
+              const float4 v4 = *reinterpret_cast<const float4*>(cb + i);
+              q[i] = v4.x; q[i + 1] = v4.y; q[i + 2] = v4.z; q[i + 3] = v4.w;
+            }
             const float y = yin[reversed ? D - 1 - j : j];
             if (d > 1) {
               mark_c(ST_F);
@@ -306,7 +327,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
               for (int i = 0; i < MULT; ++i) q[i] += __uint_as_float(v[i]);
             }
             float lad;
-            const float xo = rqs_apply<NB, true>(RegQ{q}, y, a.tail, lad);
+            const float xo = rqs_inverse_fast<NB>(q, y, a.tail, lad);
             ld_acc += lad;
             yout[j] = xo;
             bad = bad || !(fabsf(xo) <= 3.0e38f);
@@ -317,7 +338,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
             *reinterpret_cast<__nv_bfloat16*>(sX + (2 + j / 8) * 2048 + rowoff + (j % 8) * 2) = lo;
           }
           mark_c(ST_F);
-          if (d == D) break;  // last dim: no hidden group follows, and the next stage (F(1)) has no MMA
+          if (d == D) {       // last dim: no hidden group follows, and the next stage (F(1)) has no MMA
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&cempty[stepc & 1]);
+            ++stepc;
+            break;
+          }
           fence_proxy_async_smem();
           tc_fence_before();
           __syncwarp();
@@ -327,10 +353,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
           float h[GSP];
           // ---------------- I(d): h0 = W0 x + b0 + relu(Wc0 ctx + b) ----------------
           {
-            float t[GSP];
-            const float* b = a.b0p + (size_t)l * s.KTOT + slot0;
+            float t[GS4];
 #pragma unroll
-            for (int i = 0; i < GSP; ++i) t[i] = __ldg(b + i) + __ldg(pl + slot0 + i);
+            for (int i = 0; i < GS4; i += 4) {
+              const float4 b4 = *reinterpret_cast<const float4*>(cbb + i);
+              t[i] = b4.x; t[i + 1] = b4.y; t[i + 2] = b4.z; t[i + 3] = b4.w;
+            }
+            if (ctx_staged) {
+#pragma unroll
+              for (int i = 0; i < GS4; i += 4) {
+                const float4 c4 = *reinterpret_cast<const float4*>(cbc + i);
+                t[i] += c4.x; t[i + 1] += c4.y; t[i + 2] += c4.z; t[i + 3] += c4.w;
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < GSP; ++i) t[i] += __ldg(pl + slot0 + i);
+            }
             mark_c(ST_I);
             if (!(ok = wait(acc_bar, acc_par, 11))) break;
             mark_w(ST_I);
@@ -353,10 +391,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
 #pragma unroll
           for (int blk = 0; blk < 2; ++blk) {
             {  // A: u = Wa relu(h) + ba -> relu(u)
-              float t[GSP];
-              const float* b = a.bap + ((size_t)l * 2 + blk) * s.KTOT + slot0;
+              float t[GS4];
 #pragma unroll
-              for (int i = 0; i < GSP; ++i) t[i] = __ldg(b + i);
+              for (int i = 0; i < GS4; i += 4) {
+                const float4 b4 = *reinterpret_cast<const float4*>(cbb + (1 + 2 * blk) * GS4 + i);
+                t[i] = b4.x; t[i + 1] = b4.y; t[i + 2] = b4.z; t[i + 3] = b4.w;
+              }
               mark_c(ST_A1 + 2 * blk);
               if (!(ok = wait(acc_bar, acc_par, 12 + blk))) break;
               mark_w(ST_A1 + 2 * blk);
@@ -386,11 +426,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
             __syncwarp();
             if (lane == 0) mbar_arrive(op_bar);
             {  // B: h += gate * (Wb relu(u) + bb)
-              float t[GSP], g[GSP];
-              const float* b = a.bbp + ((size_t)l * 2 + blk) * s.KTOT + slot0;
-              const float* gp = pl + (size_t)(blk + 1) * s.KTOT + slot0;
+              float t[GS4], g[GS4];
 #pragma unroll
-              for (int i = 0; i < GSP; ++i) { t[i] = __ldg(b + i); g[i] = __ldg(gp + i); }
+              for (int i = 0; i < GS4; i += 4) {
+                const float4 b4 = *reinterpret_cast<const float4*>(cbb + (2 + 2 * blk) * GS4 + i);
+                t[i] = b4.x; t[i + 1] = b4.y; t[i + 2] = b4.z; t[i + 3] = b4.w;
+              }
+              if (ctx_staged) {
+#pragma unroll
+                for (int i = 0; i < GS4; i += 4) {
+                  const float4 c4 = *reinterpret_cast<const float4*>(cbc + (blk + 1) * GS4 + i);
+                  g[i] = c4.x; g[i + 1] = c4.y; g[i + 2] = c4.z; g[i + 3] = c4.w;
+                }
+              } else {
+                const float* gp = pl + (size_t)(blk + 1) * s.KTOT + slot0;
+#pragma unroll
+                for (int i = 0; i < GSP; ++i) g[i] = __ldg(gp + i);
+              }
               mark_c(ST_B1 + 2 * blk);
               if (!(ok = wait(acc_bar, acc_par, 14 + blk))) break;
               mark_w(ST_B1 + 2 * blk);
@@ -422,6 +474,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
             __syncwarp();
             if (lane == 0) mbar_arrive(op_bar);
           }
+          if (lane == 0) mbar_arrive(&cempty[stepc & 1]);   // (after the __syncwarp above: all lanes are done reading)
+          ++stepc;
         }
         float* tsw = yin; yin = yout; yout = tsw;
       }
@@ -466,6 +520,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
               if (nch == 0) continue;                   // F(1): bias only
               if (nstage++ == a.dbg_stop) { *abort_s = 1; ok = false; break; }
               long long t0 = mprof ? clock64() : 0;
+              if (!(ok = wait(&full[slot], full_par, 30))) break;   // first piece's weights (prefetched long ago)
               if (!(ok = wait(op_bar, op_par, 20 + st))) break;
               if (mprof) { long long n = clock64(); m_op += n - t0; t0 = n; }
               op_par ^= 1;
@@ -477,7 +532,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
               for (int c0 = 0; c0 < nch && ok; c0 += pc) {
                 const int nc = min(pc, nch - c0);
                 long long t1 = mprof ? clock64() : 0;
-                if (!(ok = wait(&full[slot], full_par, 30))) break;
+                if (c0 > 0 && !(ok = wait(&full[slot], full_par, 30))) break;
                 if (mprof) m_full += clock64() - t1;
                 tc_fence_after();
                 const uint32_t bbase = aRing + slot * s.slot_bytes;
@@ -509,7 +564,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
       }
       if (mprof && lane == 0) { a.prof[12] = m_op; a.prof[13] = m_full; a.prof[14] = m_issue; }
     }
-  } else {
+  } else if (warp == 5) {
     // ============================ weight loader ============================
     if (lvl != -11 && lvl != -12) {
       uint32_t slot = 0, empty_par = 1;   // a fresh barrier passes a wait on parity 1
@@ -536,6 +591,51 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
                 if (++slot == TC_NSLOT) { slot = 0; empty_par ^= 1; }
               }
             }
+          }
+        }
+      }
+    }
+  } else if (warp == 6) {
+    // ============================ constants stager ============================
+    // One step ahead of the row warps: the biases of the step's six stages and the context terms of the
+    // tile's (at most two) events go to shared memory, so no global-load latency sits on the serial chain.
+    if (lvl != -11 && lvl != -12) {
+      uint32_t stepc = 0;
+      bool ok = true;
+      for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
+        const int64_t r_first = (int64_t)tile * TC_ROWS;
+        const int64_t r_last = (r_first + TC_ROWS - 1 < a.R ? r_first + TC_ROWS - 1 : a.R - 1);
+        const bool ctx_staged = !a.cm.row2ctx && a.cm.n_per_ctx >= TC_ROWS;
+        const float* p0 = a.proj + a.cm(r_first) * a.ldproj;
+        const float* p1 = a.proj + a.cm(r_last) * a.ldproj;
+        for (int l = s.L - 1; l >= 0 && ok; --l) {
+          for (int d = 1; d <= D && ok; ++d) {
+            const int buf = stepc & 1;
+            if (!(ok = wait(&cempty[buf], ((stepc >> 1) & 1) ^ 1, 41))) break;
+            float* cb = cbuf + buf * CBF;
+            const int j = d - 1, slot0 = j * GSP;
+            for (int i = lane; i < CBF; i += 32) {
+              float v = 0.f;
+              if (i < TC_CB_BF) {
+                if (i < MULT) v = __ldg(a.bf + (size_t)l * s.PLD + (size_t)j * MULT + i);
+              } else if (d < D) {
+                const int k = i - TC_CB_BF, grp = k / GS4, e = k % GS4;
+                if (e < GSP) {
+                  if (grp == 0) v = __ldg(a.b0p + (size_t)l * s.KTOT + slot0 + e);
+                  else if (grp < 5) {
+                    const float* bp = ((grp - 1) & 1) ? a.bbp : a.bap;
+                    v = __ldg(bp + ((size_t)l * 2 + (grp - 1) / 2) * s.KTOT + slot0 + e);
+                  } else if (ctx_staged) {
+                    const int ev = (grp - 5) / 3, sec = (grp - 5) % 3;
+                    v = __ldg((ev ? p1 : p0) + ((size_t)l * 3 + sec) * s.KTOT + slot0 + e);
+                  }
+                }
+              }
+              cb[i] = v;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&cfull[buf]);
+            ++stepc;
           }
         }
       }
@@ -584,9 +684,8 @@ static bool tc_plan(const pf_flow* f, TcShape& s, std::vector<TcItem>& items) {
 }
 
 static int tc_smem_bytes(const TcShape& s) {
-  size_t y = (size_t)2 * TC_ROWS * s.D;
-  y += y & 1;
-  return (int)((size_t)2 * s.KA * 256 + 8192 + (size_t)TC_NSLOT * s.slot_bytes + y * 4 + (2 * TC_NSLOT + 4) * 8);
+  size_t y = ((size_t)2 * TC_ROWS * s.D + 3) / 4 * 4 + 2 * (size_t)tc_cb_floats(s.GSP);
+  return (int)((size_t)2 * s.KA * 256 + 8192 + (size_t)TC_NSLOT * s.slot_bytes + y * 4 + (2 * TC_NSLOT + 8) * 8);
 }
 
 template <int NB, int GSP>
