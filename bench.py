@@ -148,7 +148,8 @@ def workload_config(n_gpus):
                         "bins, 11-D, 288-D context",
             "events_per_gpu": EVENTS_PER_GPU, "samples_per_event": SAMPLES_PER_EVENT,
             "parallelism": f"events sharded over {n_gpus} GPU(s), no data-path collective",
-            "l2": "inputs+outputs per step (>= 225 MB) exceed the 126 MB L2"}
+            "l2": "L2 flushed (256 MB write) between timed steps; each step also streams 126 MB of outputs; the "
+                  "5.5 MB bf16 weight image is re-read from L2 by design"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -158,6 +159,7 @@ def run_ours(args):
     import torch.distributed as dist
     import posteriflow_b200 as P
     from posteriflow_b200 import _cabi as A
+    from posteriflow_b200.dist import allreduce_gradients
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -203,18 +205,25 @@ def run_ours(args):
         th = model.sample_posterior(None, rank=0, n_samples=n, context=c)
         theta_host.copy_(th, non_blocking=True)
 
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
     def timed(fn, steps, warmup):
+        """Device time of exactly `steps` steps: one CUDA-event pair per step on the launching stream, L2
+        flushed (256 MB write) between steps outside the pairs, barrier + synchronize on both sides."""
         for i in range(warmup):
             fn(i)
         barrier()
         l0 = fh.launches
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
+        pairs = []
         for i in range(steps):
+            flush_buf.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
             fn(warmup + i)
-        e1.record()
+            e1.record()
+            pairs.append((e0, e1))
         barrier()
-        return max_over_ranks(e0.elapsed_time(e1)), fh.launches - l0
+        return max_over_ranks(sum(a.elapsed_time(b) for a, b in pairs)), fh.launches - l0
 
     with ClockSampler(local) as clk:
         ms, launches = timed(step_device, args.steps, args.warmup)
@@ -240,8 +249,7 @@ def run_ours(args):
         loss = model.nll(None, theta_phys, rk, context=tctx[ev]).sum() / Rt
         loss.backward()
         if world > 1:
-            flat = torch.cat([p.grad.reshape(-1) for p in params])
-            dist.all_reduce(flat)
+            allreduce_gradients(params)
         return loss
 
     ms_train, launches_train = timed(step_train, args.steps, args.warmup)
@@ -260,7 +268,8 @@ def run_ours(args):
         "data": "synthetic (random-init weights, N(0,1) contexts standing in for encoder output, in-kernel Philox base noise)",
         "config": workload_config(world) if (E, n) == (EVENTS_PER_GPU, SAMPLES_PER_EVENT) else
         {"workload": f"{E} events x {n} samples per GPU (non-default)", "parallelism": f"events sharded over {world} GPU(s)"},
-        "tier": args.tier,
+        "tier": args.tier + (" (sampler: tcgen05 bf16 operands, fp32 accumulate + fp32 spline; training step: FP32 kernels)"
+                             if args.tier == "bf16" else ""),
         "e2e": {"value": R * world * args.steps / (ms_e2e * 1e-3), "unit": "samples/s",
                 "h2d_bytes_per_step": int(ctx_host.numel() * 4), "d2h_bytes_per_step": int(theta_host.numel() * 4),
                 "ms_per_step": ms_e2e / args.steps,
@@ -295,7 +304,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--tier", default=os.environ.get("PF_TIER", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--tier", default=os.environ.get("PF_TIER", "bf16"), choices=["fp32", "bf16"])
     ap.add_argument("--events", type=int, default=EVENTS_PER_GPU)
     ap.add_argument("--samples", type=int, default=SAMPLES_PER_EVENT)
     ap.add_argument("--train-events", type=int, default=TRAIN_EVENTS_PER_GPU)
