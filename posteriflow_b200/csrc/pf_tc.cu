@@ -34,9 +34,10 @@ using namespace pf::sm100;
 constexpr int TC_ROWS = 128;      // rows per tile = UMMA M = TMEM lanes
 constexpr int TC_NSLOT = 3;       // weight ring depth
 constexpr int TC_THREADS = 224;   // 4 row warps + MMA warp + weight-loader warp + constants-stager warp
-constexpr int TC_CB_BF = 48;      // per-step constants buffer (floats): bf[48] | 5 bias groups | 2 events x 3 ctx groups
+constexpr int TC_CB_BF = 48;      // per-step constants buffer (floats): bf[48] | 5 bias groups | W0[:, d-1] | 2 events x 3 ctx groups
 __host__ __device__ constexpr int tc_gs4(int gsp) { return (gsp + 3) / 4 * 4; }
-__host__ __device__ constexpr int tc_cb_floats(int gsp) { return TC_CB_BF + 11 * tc_gs4(gsp); }
+__host__ __device__ constexpr int tc_cb_floats(int gsp) { return TC_CB_BF + 12 * tc_gs4(gsp); }
+constexpr int TC_NCB = 4;         // constants buffers in flight (the stager runs up to 3 steps ahead)
 
 // stage order inside step d of a layer (d = 1..D; the hidden stages exist for d < D)
 enum { ST_F = 0, ST_I = 1, ST_A1 = 2, ST_B1 = 3, ST_A2 = 4, ST_B2 = 5, ST_COUNT = 6 };
@@ -50,7 +51,7 @@ struct TcShape {
 };
 __host__ __device__ inline int tc_nchunks(const TcShape& s, int d, int st) {
   if (st == ST_F) return (s.GSP * (d - 1) + 15) / 16;
-  if (st == ST_I) return 2;
+  if (st == ST_I) return (d >= 2 && d <= s.G) ? 2 : 0;   // I(1) has no MMA: its only input x_1 is added in fp32
   return (s.GSP * d + 15) / 16;
 }
 __host__ __device__ inline int tc_n(const TcShape& s, int st) { return st == ST_F ? s.NF : 32; }
@@ -97,7 +98,8 @@ __global__ void tc_pack_image_kernel(TcShape s, const TcItem* __restrict__ items
       if (n < s.MULT && col >= 0) v = Wf[((size_t)l * s.PLD + (size_t)(it.d - 1) * s.MULT + n) * H + col];
     } else if (it.st == ST_I) {
       int j = k < 16 ? k : k - 16;  // columns 16.. multiply the low-order bf16 half of x
-      if (n < gsz && j < s.D) v = W0[((size_t)l * H + s.off[it.d - 1] + n) * DP + j];
+      // column d-1 (x_d itself) is left out: the epilogue adds W0[g, d-1] * x_d in fp32 (hoisted I stage)
+      if (n < gsz && j < s.D && j != it.d - 1) v = W0[((size_t)l * H + s.off[it.d - 1] + n) * DP + j];
     } else {
       int blk = (it.st - ST_A1) / 2;
       const float* W = ((it.st - ST_A1) & 1) ? Wb : Wa;
@@ -133,6 +135,7 @@ struct TcArgs {
   TcShape s;
   const uint8_t* image;
   const float *b0p, *bap, *bbp, *bf;
+  const float* W0; int DP, H;   // fp32 initial-layer weights [L][H sorted][DP] (x_d column of the hoisted I stage)
   const float* proj;   // [ctx rows][L*3*KTOT] padded order: relu(c0) | sigmoid gate 1 | sigmoid gate 2
   int64_t ldproj;
   CtxMap cm;
@@ -200,16 +203,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
   uint8_t* ring = sX + 8192;
   float* ybuf = reinterpret_cast<float*>(ring + (size_t)TC_NSLOT * s.slot_bytes);
   constexpr int GS4 = tc_gs4(GSP), CBF = tc_cb_floats(GSP);
-  float* cbuf = ybuf + (2 * TC_ROWS * D + 3) / 4 * 4;   // [2][CBF] per-step constants, staged by warp 6
-  uint64_t* bars = reinterpret_cast<uint64_t*>(cbuf + 2 * CBF);
+  float* cbuf = ybuf + (2 * TC_ROWS * D + 3) / 4 * 4;   // [TC_NCB][CBF] per-step constants, staged by warp 6
+  uint64_t* bars = reinterpret_cast<uint64_t*>(cbuf + TC_NCB * CBF);
   uint64_t* full = bars;                 // [NSLOT] weights landed
   uint64_t* empty = bars + TC_NSLOT;     // [NSLOT] MMAs reading the slot completed
   uint64_t* acc_bar = bars + 2 * TC_NSLOT;      // accumulator of the current stage complete
   uint64_t* op_bar = bars + 2 * TC_NSLOT + 1;   // operands of the next stage written (4 warp arrivals)
-  uint64_t* cfull = bars + 2 * TC_NSLOT + 2;    // [2] constants of a step staged
-  uint64_t* cempty = bars + 2 * TC_NSLOT + 4;   // [2] constants of a step consumed (4 warp arrivals)
-  volatile int* abort_s = reinterpret_cast<volatile int*>(bars + 2 * TC_NSLOT + 6);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_NSLOT + 7);
+  uint64_t* cfull = bars + 2 * TC_NSLOT + 2;              // [TC_NCB] constants of a step staged
+  uint64_t* cempty = bars + 2 * TC_NSLOT + 2 + TC_NCB;    // [TC_NCB] constants of a step consumed (4 warp arrivals)
+  volatile int* abort_s = reinterpret_cast<volatile int*>(bars + 2 * TC_NSLOT + 2 + 2 * TC_NCB);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_NSLOT + 3 + 2 * TC_NCB);
 
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // provably warp-uniform role index
@@ -218,7 +221,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
     for (int i = 0; i < TC_NSLOT; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     mbar_init(acc_bar, 1);
     mbar_init(op_bar, 4);
-    for (int i = 0; i < 2; ++i) { mbar_init(&cfull[i], 1); mbar_init(&cempty[i], 4); }
+    for (int i = 0; i < TC_NCB; ++i) { mbar_init(&cfull[i], 1); mbar_init(&cempty[i], 4); }
     *abort_s = 0;
     fence_mbar_init();
   }
@@ -299,10 +302,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
         for (int d = 1; d <= D && ok; ++d) {
           const int j = d - 1;
           // this step's constants (biases, context gates), staged by warp 6 one step ahead
-          const float* cb = cbuf + (stepc & 1) * CBF;
-          if (!(ok = wait(&cfull[stepc & 1], (stepc >> 1) & 1, 16))) break;
+          const int cbi = stepc & (TC_NCB - 1);
+          const float* cb = cbuf + cbi * CBF;
+          if (!(ok = wait(&cfull[cbi], (stepc / TC_NCB) & 1, 16))) break;
           const float* cbb = cb + TC_CB_BF;                      // 5 bias groups of GS4 floats
-          const float* cbc = cbb + 5 * GS4 + esel * 3 * GS4;      // 3 context groups of this row's event
+          const float* cbw = cbb + 5 * GS4;                      // initial-layer weights of x_d for this group
+          const float* cbc = cbw + GS4 + esel * 3 * GS4;          // 3 context groups of this row's event
+          float xd;
           // ---------------- F(d): spline parameters of dim d -> inverse spline ----------------
           {
             if (d == 1) { mark_c(0); pcur = ST_F; }
@@ -336,28 +342,27 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
             const __nv_bfloat16 lo = __float2bfloat16(xc - __bfloat162float(hi));
             *reinterpret_cast<__nv_bfloat16*>(sX + (j / 8) * 2048 + rowoff + (j % 8) * 2) = hi;
             *reinterpret_cast<__nv_bfloat16*>(sX + (2 + j / 8) * 2048 + rowoff + (j % 8) * 2) = lo;
+            xd = xo;
           }
-          mark_c(ST_F);
           if (d == D) {       // last dim: no hidden group follows, and the next stage (F(1)) has no MMA
+            mark_c(ST_F);
             __syncwarp();
-            if (lane == 0) mbar_arrive(&cempty[stepc & 1]);
+            if (lane == 0) mbar_arrive(&cempty[cbi]);
             ++stepc;
             break;
           }
-          fence_proxy_async_smem();
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(op_bar);
-
           const int slot0 = j * GSP;   // first padded slot of the degree-d group
           float h[GSP];
-          // ---------------- I(d): h0 = W0 x + b0 + relu(Wc0 ctx + b) ----------------
+          // ---- I(d), hoisted: W0[g, <d] x[<d] was issued together with F(d) (its x_d column is zero in the
+          // blob); the x_d term is added here in fp32: h0 = acc + W0[g, d] x_d + b0 + relu(Wc0 ctx + b) ----
           {
             float t[GS4];
 #pragma unroll
             for (int i = 0; i < GS4; i += 4) {
               const float4 b4 = *reinterpret_cast<const float4*>(cbb + i);
-              t[i] = b4.x; t[i + 1] = b4.y; t[i + 2] = b4.z; t[i + 3] = b4.w;
+              const float4 w4 = *reinterpret_cast<const float4*>(cbw + i);
+              t[i] = fmaf(w4.x, xd, b4.x); t[i + 1] = fmaf(w4.y, xd, b4.y);
+              t[i + 2] = fmaf(w4.z, xd, b4.z); t[i + 3] = fmaf(w4.w, xd, b4.w);
             }
             if (ctx_staged) {
 #pragma unroll
@@ -369,21 +374,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
 #pragma unroll
               for (int i = 0; i < GSP; ++i) t[i] += __ldg(pl + slot0 + i);
             }
-            mark_c(ST_I);
-            if (!(ok = wait(acc_bar, acc_par, 11))) break;
-            mark_w(ST_I);
-            acc_par ^= 1;
-            tc_fence_after();
-            uint32_t v[32];
-            tmem_ld32(tl + TM::ACC_I, v);
-            tmem_wait_ld();
-            uint32_t w[NW];
+            if (d > 1) {
+              uint32_t v[32];
+              tmem_ld32(tl + TM::ACC_I, v);
+              tmem_wait_ld();
 #pragma unroll
-            for (int i = 0; i < GSP; ++i) h[i] = __uint_as_float(v[i]) + t[i];
+              for (int i = 0; i < GSP; ++i) h[i] = __uint_as_float(v[i]) + t[i];
+            } else {
+#pragma unroll
+              for (int i = 0; i < GSP; ++i) h[i] = t[i];
+            }
+            uint32_t w[NW];
 #pragma unroll
             for (int i = 0; i < NW; ++i) w[i] = pack_bf16(relu_finite(h[2 * i]), relu_finite(h[2 * i + 1]));
             tmem_store_words<NW>(tl + TM::A0 + j * NW, w);
           }
+          fence_proxy_async_smem();
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(op_bar);
@@ -474,7 +480,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
             __syncwarp();
             if (lane == 0) mbar_arrive(op_bar);
           }
-          if (lane == 0) mbar_arrive(&cempty[stepc & 1]);   // (after the __syncwarp above: all lanes are done reading)
+          if (lane == 0) mbar_arrive(&cempty[cbi]);   // (after the __syncwarp above: all lanes are done reading)
           ++stepc;
         }
         float* tsw = yin; yin = yout; yout = tsw;
@@ -507,62 +513,86 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
       uint32_t op_par = 0, slot = 0, full_par = 0;
       int nstage = 0;
       const bool mprof = a.prof && blockIdx.x == 0;
-      long long m_op = 0, m_full = 0, m_issue = 0;
+      long long m_op = 0, m_full = 0, m_issue = 0, m_loop = 0, m_commit = 0;
+      long long n_mma = 0;
       const uint32_t idesc_h = umma_idesc_bf16(TC_ROWS, 32), idesc_f = umma_idesc_bf16(TC_ROWS, s.NF);
       const uint32_t aX = smem_u32(sX), aA3 = smem_u32(sA3), aA4 = smem_u32(sA4), aRing = smem_u32(ring);
       bool ok = true;
       for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
         for (int l = s.L - 1; l >= 0 && ok; --l) {
           for (int d = 1; d <= D && ok; ++d) {
-            for (int st = 0; st < ST_COUNT && ok; ++st) {
-              if (st > 0 && d == D) break;
-              const int nch = tc_nchunks(s, d, st);
-              if (nch == 0) continue;                   // F(1): bias only
+            // MMA stages of step d: [F(d) + I(d)] (one commit), A1, B1, A2, B2
+            for (int ms = 0; ms < 5 && ok; ++ms) {
+              if (ms > 0 && d == D) break;
+              const int st0 = ms == 0 ? ST_F : ms + 1;
+              const int ngrp = ms == 0 ? 2 : 1;            // stage 0 has two item groups: F then I
+              const int n0 = tc_nchunks(s, d, st0), n1 = ms == 0 ? tc_nchunks(s, d, ST_I) : 0;
+              if (n0 + n1 == 0) continue;                 // step 1: bias-only F, fp32-only I
               if (nstage++ == a.dbg_stop) { *abort_s = 1; ok = false; break; }
               long long t0 = mprof ? clock64() : 0;
-              if (!(ok = wait(&full[slot], full_par, 30))) break;   // first piece's weights (prefetched long ago)
-              if (!(ok = wait(op_bar, op_par, 20 + st))) break;
+              if (!(ok = wait(&full[slot], full_par, 30))) break;   // first item's weights (prefetched long ago)
+              if (!(ok = wait(op_bar, op_par, 20 + st0))) break;
               if (mprof) { long long n = clock64(); m_op += n - t0; t0 = n; }
               op_par ^= 1;
               tc_fence_after();
-              const int N = tc_n(s, st);
-              const uint32_t idesc = st == ST_F ? idesc_f : idesc_h;
-              const uint32_t acc = tmem + (st == ST_F ? TM::ACC_F : (st == ST_I ? TM::ACC_I : TM::ACC_H));
-              const int pc = tc_piece(s, st, nch);
-              for (int c0 = 0; c0 < nch && ok; c0 += pc) {
-                const int nc = min(pc, nch - c0);
-                long long t1 = mprof ? clock64() : 0;
-                if (c0 > 0 && !(ok = wait(&full[slot], full_par, 30))) break;
-                if (mprof) m_full += clock64() - t1;
-                tc_fence_after();
-                const uint32_t bbase = aRing + slot * s.slot_bytes;
-                if (elect_one_sync()) {
-                  if (st == ST_F || st == ST_I || st == ST_B2) {
-                    const uint32_t abase = st == ST_F ? aA4 : (st == ST_I ? aX : aA3);
-                    for (int i = 0; i < nc; ++i) {
-                      const uint64_t bd = umma_smem_desc(bbase + (uint32_t)i * 2u * (uint32_t)(N * 16), N * 16, 128);
-                      const uint64_t ad = umma_smem_desc(abase + (uint32_t)(c0 + i) * 4096u, 2048, 128);
-                      umma_ss(acc, ad, bd, idesc, (c0 + i) > 0);
+              bool first_item = true;
+              for (int grp = 0; grp < ngrp && ok; ++grp) {
+                const int st = grp == 0 ? st0 : ST_I;
+                const int nch = grp == 0 ? n0 : n1;
+                if (nch == 0) continue;
+                const bool last_grp = (grp == ngrp - 1) || (grp == 0 && n1 == 0);
+                const int N = tc_n(s, st);
+                const uint32_t idesc = st == ST_F ? idesc_f : idesc_h;
+                const uint32_t acc = tmem + (st == ST_F ? TM::ACC_F : (st == ST_I ? TM::ACC_I : TM::ACC_H));
+                const int pc = tc_piece(s, st, nch);
+                for (int c0 = 0; c0 < nch && ok; c0 += pc) {
+                  const int nc = min(pc, nch - c0);
+                  long long t1 = mprof ? clock64() : 0;
+                  if (!first_item && !(ok = wait(&full[slot], full_par, 30))) break;
+                  first_item = false;
+                  if (mprof) m_full += clock64() - t1;
+                  tc_fence_after();
+                  const uint32_t bbase = aRing + slot * s.slot_bytes;
+                  const long long t2 = mprof ? clock64() : 0;
+                  if (elect_one_sync()) {
+                    // descriptors advance by adding to their low word (start address field, 16-byte units)
+                    uint64_t bd = umma_smem_desc(bbase, N * 16, 128);
+                    const uint64_t bstep = (uint64_t)((2u * (uint32_t)N * 16u) >> 4);
+                    uint32_t accf = c0 > 0 ? 1u : 0u;
+                    if (st == ST_F || st == ST_I || st == ST_B2) {
+                      const uint32_t abase = st == ST_F ? aA4 : (st == ST_I ? aX : aA3);
+                      uint64_t ad = umma_smem_desc(abase + (uint32_t)c0 * 4096u, 2048, 128);
+#pragma unroll 4
+                      for (int i = 0; i < nc; ++i) {
+                        umma_ss(acc, ad, bd, idesc, accf);
+                        accf = 1u; ad += 256u; bd += bstep;
+                      }
+                    } else {
+                      uint32_t at = tmem + (st == ST_A1 ? TM::A0 : (st == ST_B1 ? TM::A1 : TM::A2)) + c0 * 8;
+#pragma unroll 4
+                      for (int i = 0; i < nc; ++i) {
+                        umma_ts(acc, at, bd, idesc, accf);
+                        accf = 1u; at += 8u; bd += bstep;
+                      }
                     }
-                  } else {
-                    const uint32_t at = tmem + (st == ST_A1 ? TM::A0 : (st == ST_B1 ? TM::A1 : TM::A2));
-                    for (int i = 0; i < nc; ++i) {
-                      const uint64_t bd = umma_smem_desc(bbase + (uint32_t)i * 2u * (uint32_t)(N * 16), N * 16, 128);
-                      umma_ts(acc, at + (c0 + i) * 8, bd, idesc, (c0 + i) > 0);
-                    }
+                    const long long t3 = mprof ? clock64() : 0;
+                    umma_commit(&empty[slot]);
+                    if (last_grp && c0 + nc >= nch) umma_commit(acc_bar);
+                    if (mprof) { const long long t4 = clock64(); m_loop += t3 - t2; m_commit += t4 - t3; n_mma += nc; }
                   }
-                  umma_commit(&empty[slot]);
-                  if (c0 + nc >= nch) umma_commit(acc_bar);
+                  __syncwarp();
+                  if (++slot == TC_NSLOT) { slot = 0; full_par ^= 1; }
                 }
-                __syncwarp();
-                if (++slot == TC_NSLOT) { slot = 0; full_par ^= 1; }
               }
               if (mprof) m_issue += clock64() - t0;
             }
           }
         }
       }
-      if (mprof && lane == 0) { a.prof[12] = m_op; a.prof[13] = m_full; a.prof[14] = m_issue; }
+      if (mprof && elect_one_sync()) {
+        a.prof[12] = m_op; a.prof[13] = m_full; a.prof[14] = m_issue;
+        a.prof[16] = m_loop; a.prof[17] = m_commit; a.prof[18] = n_mma;
+      }
     }
   } else if (warp == 5) {
     // ============================ weight loader ============================
@@ -610,29 +640,40 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
         const float* p1 = a.proj + a.cm(r_last) * a.ldproj;
         for (int l = s.L - 1; l >= 0 && ok; --l) {
           for (int d = 1; d <= D && ok; ++d) {
-            const int buf = stepc & 1;
-            if (!(ok = wait(&cempty[buf], ((stepc >> 1) & 1) ^ 1, 41))) break;
+            const int buf = stepc & (TC_NCB - 1);
+            if (!(ok = wait(&cempty[buf], ((stepc / TC_NCB) & 1) ^ 1, 41))) break;
             float* cb = cbuf + buf * CBF;
             const int j = d - 1, slot0 = j * GSP;
-            for (int i = lane; i < CBF; i += 32) {
-              float v = 0.f;
+            // address phase, then all loads in flight together, then the stores
+            constexpr int PER = (CBF + 31) / 32;
+            const float* src[PER];
+#pragma unroll
+            for (int k = 0; k < PER; ++k) {
+              const int i = lane + 32 * k;
+              const float* ptr = nullptr;
               if (i < TC_CB_BF) {
-                if (i < MULT) v = __ldg(a.bf + (size_t)l * s.PLD + (size_t)j * MULT + i);
-              } else if (d < D) {
-                const int k = i - TC_CB_BF, grp = k / GS4, e = k % GS4;
+                if (i < MULT) ptr = a.bf + (size_t)l * s.PLD + (size_t)j * MULT + i;
+              } else if (i < CBF && d < D) {
+                const int kk = i - TC_CB_BF, grp = kk / GS4, e = kk % GS4;
                 if (e < GSP) {
-                  if (grp == 0) v = __ldg(a.b0p + (size_t)l * s.KTOT + slot0 + e);
-                  else if (grp < 5) {
-                    const float* bp = ((grp - 1) & 1) ? a.bbp : a.bap;
-                    v = __ldg(bp + ((size_t)l * 2 + (grp - 1) / 2) * s.KTOT + slot0 + e);
+                  if (grp == 0) ptr = a.b0p + (size_t)l * s.KTOT + slot0 + e;
+                  else if (grp < 5) ptr = (((grp - 1) & 1) ? a.bbp : a.bap) + ((size_t)l * 2 + (grp - 1) / 2) * s.KTOT + slot0 + e;
+                  else if (grp == 5) {
+                    if (e < s.off[d] - s.off[d - 1]) ptr = a.W0 + ((size_t)l * a.H + s.off[d - 1] + e) * a.DP + j;
                   } else if (ctx_staged) {
-                    const int ev = (grp - 5) / 3, sec = (grp - 5) % 3;
-                    v = __ldg((ev ? p1 : p0) + ((size_t)l * 3 + sec) * s.KTOT + slot0 + e);
+                    const int ev = (grp - 6) / 3, sec = (grp - 6) % 3;
+                    ptr = (ev ? p1 : p0) + ((size_t)l * 3 + sec) * s.KTOT + slot0 + e;
                   }
                 }
               }
-              cb[i] = v;
+              src[k] = ptr;
             }
+            float val[PER];
+#pragma unroll
+            for (int k = 0; k < PER; ++k) val[k] = src[k] ? __ldg(src[k]) : 0.f;
+#pragma unroll
+            for (int k = 0; k < PER; ++k)
+              if (lane + 32 * k < CBF) cb[lane + 32 * k] = val[k];
             __syncwarp();
             if (lane == 0) mbar_arrive(&cfull[buf]);
             ++stepc;
@@ -684,8 +725,8 @@ static bool tc_plan(const pf_flow* f, TcShape& s, std::vector<TcItem>& items) {
 }
 
 static int tc_smem_bytes(const TcShape& s) {
-  size_t y = ((size_t)2 * TC_ROWS * s.D + 3) / 4 * 4 + 2 * (size_t)tc_cb_floats(s.GSP);
-  return (int)((size_t)2 * s.KA * 256 + 8192 + (size_t)TC_NSLOT * s.slot_bytes + y * 4 + (2 * TC_NSLOT + 8) * 8);
+  size_t y = ((size_t)2 * TC_ROWS * s.D + 3) / 4 * 4 + TC_NCB * (size_t)tc_cb_floats(s.GSP);
+  return (int)((size_t)2 * s.KA * 256 + 8192 + (size_t)TC_NSLOT * s.slot_bytes + y * 4 + (2 * TC_NSLOT + 2 * TC_NCB + 4) * 8);
 }
 
 template <int NB, int GSP>
@@ -718,7 +759,7 @@ pf_status pf_tc_pack(pf_flow* f, cudaStream_t st) {
     const char* dbg = getenv("PF_TC_DEBUG");
     t->debug_sync = dbg && dbg[0] == '1';
     const char* pr = getenv("PF_TC_PROF");
-    if (pr && pr[0] == '1' && cudaMalloc(&t->prof, 16 * sizeof(long long)) != cudaSuccess) t->prof = nullptr;
+    if (pr && pr[0] == '1' && cudaMalloc(&t->prof, 24 * sizeof(long long)) != cudaSuccess) t->prof = nullptr;
     size_t nf = L * KT + 2 * (L * 2 * KT) + L * 3 * KT * C + L * 3 * KT;
     cudaError_t e = cudaMalloc(&t->image, L * s.layer_bytes);
     if (e == cudaSuccess) e = cudaMalloc(&t->arena, nf * sizeof(float));
@@ -847,6 +888,7 @@ pf_status pf_tc_inverse(pf_flow* f, cudaStream_t st, const float* z, uint64_t se
     a.s = s;
     a.image = t->image;
     a.b0p = t->b0p; a.bap = t->bap; a.bbp = t->bbp; a.bf = f->bf;
+    a.W0 = f->W0; a.DP = f->DP; a.H = f->H;
     a.ldproj = ldproj;
     if (proj_all) {
       a.proj = proj_all;
@@ -877,7 +919,7 @@ pf_status pf_tc_inverse(pf_flow* f, cudaStream_t st, const float* z, uint64_t se
     else PF_TRY((tc_launch<16, 20>(f, st, a, t->kernel_smem)));
   }
   if (t->prof) {
-    long long h[16];
+    long long h[24];
     PF_CUDA(cudaStreamSynchronize(st));
     PF_CUDA(cudaMemcpy(h, t->prof, sizeof(h), cudaMemcpyDeviceToHost));
     const char* nm[6] = {"F", "I", "A1", "B1", "A2", "B2"};
@@ -885,6 +927,7 @@ pf_status pf_tc_inverse(pf_flow* f, cudaStream_t st, const float* z, uint64_t se
     for (int i = 0; i < 6; ++i) fprintf(stderr, "[pf_tc prof]   stage %-2s wait %10lld  compute %10lld\n", nm[i], h[i], h[6 + i]);
     fprintf(stderr, "[pf_tc prof] MMA thread: wait-operands %lld  wait-weights %lld  stage total (incl. waits) %lld\n", h[12],
             h[13], h[14]);
+    fprintf(stderr, "[pf_tc prof] MMA thread: issue loops %lld cycles for %lld MMAs, commits %lld\n", h[16], h[18], h[17]);
   }
   if (t->debug_sync) {
     int herr = 0;
