@@ -33,7 +33,7 @@ using namespace pf::sm100;
 
 constexpr int TC_ROWS = 128;      // rows per tile = UMMA M = TMEM lanes
 constexpr int TC_NSLOT = 3;       // weight ring depth
-constexpr int TC_THREADS = 224;   // 4 row warps + MMA warp + weight-loader warp + constants-stager warp
+constexpr int TC_THREADS = 352;   // 8 row warps (2 threads per row) + MMA warp + weight-loader warp + constants-stager warp
 constexpr int TC_CB_BF = 48;      // per-step constants buffer (floats): bf[48] | 5 bias groups | W0[:, d-1] | 2 events x 3 ctx groups
 __host__ __device__ constexpr int tc_gs4(int gsp) { return (gsp + 3) / 4 * 4; }
 __host__ __device__ constexpr int tc_cb_floats(int gsp) { return TC_CB_BF + 12 * tc_gs4(gsp); }
@@ -204,7 +204,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
   float* ybuf = reinterpret_cast<float*>(ring + (size_t)TC_NSLOT * s.slot_bytes);
   constexpr int GS4 = tc_gs4(GSP), CBF = tc_cb_floats(GSP);
   float* cbuf = ybuf + (2 * TC_ROWS * D + 3) / 4 * 4;   // [TC_NCB][CBF] per-step constants, staged by warp 6
-  uint64_t* bars = reinterpret_cast<uint64_t*>(cbuf + TC_NCB * CBF);
+  float* xwk = cbuf + TC_NCB * CBF;                      // [128][17] width knots, half 1 -> half 0 of a row pair
+  uint64_t* bars = reinterpret_cast<uint64_t*>(xwk + TC_ROWS * 17 + (TC_ROWS * 17 & 1));
   uint64_t* full = bars;                 // [NSLOT] weights landed
   uint64_t* empty = bars + TC_NSLOT;     // [NSLOT] MMAs reading the slot completed
   uint64_t* acc_bar = bars + 2 * TC_NSLOT;      // accumulator of the current stage complete
@@ -220,12 +221,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
   if (tid == 0) {
     for (int i = 0; i < TC_NSLOT; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     mbar_init(acc_bar, 1);
-    mbar_init(op_bar, 4);
-    for (int i = 0; i < TC_NCB; ++i) { mbar_init(&cfull[i], 1); mbar_init(&cempty[i], 4); }
+    mbar_init(op_bar, 8);
+    for (int i = 0; i < TC_NCB; ++i) { mbar_init(&cfull[i], 1); mbar_init(&cempty[i], 8); }
     *abort_s = 0;
     fence_mbar_init();
   }
-  if (warp == 4) tmem_alloc(tmem_slot, 512);
+  if (warp == 8) tmem_alloc(tmem_slot, 512);
   // zero the shared-memory operand arrays (stale columns are multiplied by zero weights: must be finite)
   for (int i = tid; i < (2 * KA * 256 + 8192) / 16; i += TC_THREADS) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
   fence_proxy_async_smem();
@@ -246,11 +247,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
   };
 
   const int lvl = a.dbg_stop;
-  if (warp < 4 && lvl != -11) {
+  if (warp < 8 && lvl != -11) {
     // ============================ row warps ============================
-    const int r = tid;
-    const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16);   // this warp's TMEM lane window
-    {  // zero the TMEM activation arrays + pad columns
+    // Two threads per flow row: warps 0-3 ("half 0") and 4-7 ("half 1") both cover rows 0..127 (TMEM lane
+    // window = warp % 4).  In the hidden stages half 0 owns bf16 words 0..6 of the step's 13-word group and
+    // half 1 words 7..12; in the spline stage half 1 turns the 16 width logits into the 17 width knots while
+    // half 0 does heights, bin search, derivatives and the closing solve.  Two warps per scheduler instead of
+    // one is what hides the dependent-instruction latency of these epilogues.
+    const int half = warp >> 2, q4 = warp & 3;
+    const int r = q4 * 32 + lane;
+    const uint32_t tl = tmem + ((uint32_t)(q4 * 32) << 16);   // this warp's TMEM lane window
+    constexpr int NWH = (NW + 1) / 2;                            // words of half 0 (half 1 has NW - NWH)
+    const int wo = half ? NWH : 0;                               // first word of this thread's share
+    const int nwo = half ? NW - NWH : NWH;
+    if (half == 0) {  // zero the TMEM activation arrays + pad columns
       uint32_t zz[16];
 #pragma unroll
       for (int i = 0; i < 16; ++i) zz[i] = 0u;
@@ -262,18 +272,46 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
     long long pw[6] = {0, 0, 0, 0, 0, 0}, pc[6] = {0, 0, 0, 0, 0, 0};
     long long tmark = clock64();
     const long long t_begin = tmark;
-    // account the time since the last mark to "compute of stage a" / "wait of stage b"
     int pcur = ST_F;   // stage whose epilogue is running
     auto mark_c = [&](int) { if (prof) { long long n = clock64(); pc[pcur] += n - tmark; tmark = n; } };
     auto mark_w = [&](int st) { if (prof) { long long n = clock64(); pw[st] += n - tmark; tmark = n; pcur = st; } };
     const uint32_t rowoff = (uint32_t)(r / 8) * 128 + (uint32_t)(r % 8) * 16;
+    float* xr = xwk + r * 17;                                    // this row's 17 width knots (half 1 -> half 0)
+    // store this thread's words of the group starting at word column `wbase` / element slot `slot0`
+    auto store_tmem = [&](uint32_t wbase, const uint32_t* w) {
+      const uint32_t dst = wbase + wo;
+      tmem_st4(dst, w);
+      if (nwo >= 6) tmem_st2(dst + 4, w + 4);
+      else tmem_st1(dst + 4, w + 4);
+      if (nwo == 7) tmem_st1(dst + 6, w + 6);
+      tmem_wait_st();
+    };
+    auto store_smem = [&](uint8_t* arr, int slot0, const uint32_t* w) {
+      const uint32_t b0 = (uint32_t)slot0 * 2 + 4 * wo;
+#pragma unroll
+      for (int i = 0; i < NWH; ++i) {
+        if (i < nwo) {
+          const uint32_t bo = b0 + 4 * i;
+          *reinterpret_cast<uint32_t*>(arr + (bo >> 4) * 2048 + rowoff + (bo & 15)) = w[i];
+        }
+      }
+      fence_proxy_async_smem();
+    };
+    // 2*NWH constants of this thread's share from group `g` of the step's constants
+    auto load_consts = [&](const float* grp, float* t) {
+#pragma unroll
+      for (int i = 0; i < NWH; ++i) {
+        const float2 c2 = *reinterpret_cast<const float2*>(grp + 2 * wo + 2 * i);
+        t[2 * i] = c2.x; t[2 * i + 1] = c2.y;
+      }
+    };
     bool ok = !(lvl == -12 || lvl == -13);
     for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
       const int64_t grow = (int64_t)tile * TC_ROWS + r;
       const bool valid = grow < a.R;
       float* y0 = ybuf + r * D;                 // ybuf[0][r][:]
       float* y1 = ybuf + TC_ROWS * D + r * D;   // ybuf[1][r][:]
-      {
+      if (half == 0) {
         float zr[PF_MAX_D];
 #pragma unroll
         for (int j = 0; j < PF_MAX_D; ++j) zr[j] = 0.f;
@@ -301,7 +339,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
         const float* pl = projr + (size_t)l * 3 * s.KTOT;
         for (int d = 1; d <= D && ok; ++d) {
           const int j = d - 1;
-          // this step's constants (biases, context gates), staged by warp 6 one step ahead
+          // this step's constants (biases, context gates), staged by the stager warp ahead of time
           const int cbi = stepc & (TC_NCB - 1);
           const float* cb = cbuf + cbi * CBF;
           if (!(ok = wait(&cfull[cbi], (stepc / TC_NCB) & 1, 16))) break;
@@ -309,13 +347,54 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
           const float* cbw = cbb + 5 * GS4;                      // initial-layer weights of x_d for this group
           const float* cbc = cbw + GS4 + esel * 3 * GS4;          // 3 context groups of this row's event
           float xd;
-          // ---------------- F(d): spline parameters of dim d -> inverse spline ----------------
-          {
-            if (d == 1) { mark_c(0); pcur = ST_F; }
-            float q[48];
+          if (d == 1) { mark_c(0); pcur = ST_F; }
+          // ---------------- F(d): spline parameters of dim d -> inverse spline, split over the thread pair -------
+          if (half == 1) {
+            // ---- widths: 16 logits -> 17 knots of the x axis, handed to half 0 through shared memory ----
+            float qw[NB];
 #pragma unroll
-            for (int i = 0; i < 48; i += 4) {
+            for (int i = 0; i < NB; i += 4) {
               const float4 v4 = *reinterpret_cast<const float4*>(cb + i);
+              qw[i] = v4.x; qw[i + 1] = v4.y; qw[i + 2] = v4.z; qw[i + 3] = v4.w;
+            }
+            if (d > 1) {
+              if (!(ok = wait(acc_bar, acc_par, 10))) break;
+              acc_par ^= 1;
+              tc_fence_after();
+              uint32_t v[16];
+              tmem_ld16(tl + TM::ACC_F, v);
+              tmem_wait_ld();
+#pragma unroll
+              for (int i = 0; i < NB; ++i) qw[i] += __uint_as_float(v[i]);
+            }
+            float mw = qw[0];
+#pragma unroll
+            for (int i = 1; i < NB; ++i) mw = fmaxf(mw, qw[i]);
+            float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+            for (int i = 0; i < NB; i += 2) {
+              qw[i] = fx_ex2((qw[i] - mw) * 1.4426950408889634f);
+              qw[i + 1] = fx_ex2((qw[i + 1] - mw) * 1.4426950408889634f);
+              s0 += qw[i]; s1 += qw[i + 1];
+            }
+            const float cwn = (2.f * a.tail) * (1.f - kMinBin * NB) * fx_rcp(s0 + s1);
+            const float base = (2.f * a.tail) * kMinBin;
+            float cx = 0.f;
+            xr[0] = -a.tail;
+#pragma unroll
+            for (int i = 0; i < NB; ++i) {
+              cx += fmaf(cwn, qw[i], base);
+              xr[i + 1] = (i == NB - 1) ? a.tail : cx - a.tail;
+            }
+            bar_arrive(1 + q4, 64);
+            bar_sync(5 + q4, 64);          // half 0 has read the knots and published x_d
+            xd = yout[j];
+          } else {
+            // ---- heights + derivatives: bin search on the y axis, then the closing solve ----
+            float q[32];
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+              const float4 v4 = *reinterpret_cast<const float4*>(cb + NB + i);
               q[i] = v4.x; q[i + 1] = v4.y; q[i + 2] = v4.z; q[i + 3] = v4.w;
             }
             const float y = yin[reversed ? D - 1 - j : j];
@@ -325,16 +404,61 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
               mark_w(ST_F);
               acc_par ^= 1;
               tc_fence_after();
-              uint32_t v[48];
-              tmem_ld32(tl + TM::ACC_F, v);
-              tmem_ld16(tl + TM::ACC_F + 32, v + 32);
+              uint32_t v[32];
+              tmem_ld32(tl + TM::ACC_F + NB, v);
               tmem_wait_ld();
 #pragma unroll
-              for (int i = 0; i < MULT; ++i) q[i] += __uint_as_float(v[i]);
+              for (int i = 0; i < 2 * NB - 1; ++i) q[i] += __uint_as_float(v[i]);
             }
-            float lad;
-            const float xo = rqs_inverse_fast<NB>(q, y, a.tail, lad);
-            ld_acc += lad;
+            const float B = a.tail;
+            float mh = q[0];
+#pragma unroll
+            for (int i = 1; i < NB; ++i) mh = fmaxf(mh, q[i]);
+            float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+            for (int i = 0; i < NB; i += 2) {
+              q[i] = fx_ex2((q[i] - mh) * 1.4426950408889634f);
+              q[i + 1] = fx_ex2((q[i + 1] - mh) * 1.4426950408889634f);
+              s0 += q[i]; s1 += q[i + 1];
+            }
+            const float chn = (2.f * B) * (1.f - kMinBin * NB) * fx_rcp(s0 + s1);
+            const float base = (2.f * B) * kMinBin;
+            int k = 0;
+            float yk = -B, hk = 0.f, py = -B, cy = 0.f;
+#pragma unroll
+            for (int i = 0; i < NB; ++i) {
+              cy += fmaf(chn, q[i], base);
+              const float ny = (i == NB - 1) ? B : cy - B;
+              if (i == 0 || y >= py) { k = i; yk = py; hk = ny - py; }
+              py = ny;
+            }
+            float u0 = kEdgeLogit, u1 = kEdgeLogit;
+#pragma unroll
+            for (int i = 0; i < NB - 1; ++i) {
+              const float u = q[NB + i];
+              if (i + 1 == k) u0 = u;
+              if (i == k) u1 = u;
+            }
+            const float dk = kMinDeriv + (u0 > 20.f ? u0 : fx_log(1.f + fx_exp(u0)));
+            const float dk1 = kMinDeriv + (u1 > 20.f ? u1 : fx_log(1.f + fx_exp(u1)));
+            bar_sync(1 + q4, 64);          // the width knots of this row are in shared memory
+            const float xk = xr[k];
+            const float wk = xr[k + 1] - xk;
+            const float sl = hk * fx_rcp(wk);
+            const float dy = y - yk;
+            const float t = dk + dk1 - 2.f * sl;
+            const float qa = fmaf(dy, t, hk * (sl - dk));
+            const float qb = fmaf(hk, dk, -dy * t);
+            const float qc = -sl * dy;
+            const float disc = fmaxf(fmaf(qb, qb, -4.f * qa * qc), 0.f);
+            const float root = 2.f * qc * fx_rcp(-qb - fx_sqrt(disc));
+            const float tt = root * (1.f - root);
+            const float den = fmaf(t, tt, sl);
+            const float omr = 1.f - root;
+            const float dnum = sl * sl * (dk1 * root * root + 2.f * sl * tt + dk * omr * omr);
+            const bool inside = y >= -B && y <= B;       // outside (or NaN): linear tails, identity
+            const float xo = inside ? fmaf(root, wk, xk) : y;
+            ld_acc += inside ? -fx_log(dnum * fx_rcp(den * den)) : 0.f;
             yout[j] = xo;
             bad = bad || !(fabsf(xo) <= 3.0e38f);
             const float xc = finite_clamp(xo);
@@ -342,6 +466,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
             const __nv_bfloat16 lo = __float2bfloat16(xc - __bfloat162float(hi));
             *reinterpret_cast<__nv_bfloat16*>(sX + (j / 8) * 2048 + rowoff + (j % 8) * 2) = hi;
             *reinterpret_cast<__nv_bfloat16*>(sX + (2 + j / 8) * 2048 + rowoff + (j % 8) * 2) = lo;
+            bar_arrive(5 + q4, 64);
             xd = xo;
           }
           if (d == D) {       // last dim: no hidden group follows, and the next stage (F(1)) has no MMA
@@ -352,42 +477,38 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
             break;
           }
           const int slot0 = j * GSP;   // first padded slot of the degree-d group
-          float h[GSP];
+          float h[2 * NWH];
           // ---- I(d), hoisted: W0[g, <d] x[<d] was issued together with F(d) (its x_d column is zero in the
           // blob); the x_d term is added here in fp32: h0 = acc + W0[g, d] x_d + b0 + relu(Wc0 ctx + b) ----
           {
-            float t[GS4];
+            float t[2 * NWH], wc[2 * NWH];
+            load_consts(cbb, t);
+            load_consts(cbw, wc);
 #pragma unroll
-            for (int i = 0; i < GS4; i += 4) {
-              const float4 b4 = *reinterpret_cast<const float4*>(cbb + i);
-              const float4 w4 = *reinterpret_cast<const float4*>(cbw + i);
-              t[i] = fmaf(w4.x, xd, b4.x); t[i + 1] = fmaf(w4.y, xd, b4.y);
-              t[i + 2] = fmaf(w4.z, xd, b4.z); t[i + 3] = fmaf(w4.w, xd, b4.w);
-            }
+            for (int i = 0; i < 2 * NWH; ++i) t[i] = fmaf(wc[i], xd, t[i]);
             if (ctx_staged) {
+              load_consts(cbc, wc);
 #pragma unroll
-              for (int i = 0; i < GS4; i += 4) {
-                const float4 c4 = *reinterpret_cast<const float4*>(cbc + i);
-                t[i] += c4.x; t[i + 1] += c4.y; t[i + 2] += c4.z; t[i + 3] += c4.w;
-              }
+              for (int i = 0; i < 2 * NWH; ++i) t[i] += wc[i];
             } else {
 #pragma unroll
-              for (int i = 0; i < GSP; ++i) t[i] += __ldg(pl + slot0 + i);
+              for (int i = 0; i < 2 * NWH; ++i)
+                if (i < 2 * nwo) t[i] += __ldg(pl + slot0 + 2 * wo + i);
             }
             if (d > 1) {
-              uint32_t v[32];
-              tmem_ld32(tl + TM::ACC_I, v);
+              uint32_t v[16];
+              tmem_ld16(tl + TM::ACC_I + 2 * wo, v);
               tmem_wait_ld();
 #pragma unroll
-              for (int i = 0; i < GSP; ++i) h[i] = __uint_as_float(v[i]) + t[i];
+              for (int i = 0; i < 2 * NWH; ++i) h[i] = __uint_as_float(v[i]) + t[i];
             } else {
 #pragma unroll
-              for (int i = 0; i < GSP; ++i) h[i] = t[i];
+              for (int i = 0; i < 2 * NWH; ++i) h[i] = t[i];
             }
-            uint32_t w[NW];
+            uint32_t w[NWH];
 #pragma unroll
-            for (int i = 0; i < NW; ++i) w[i] = pack_bf16(relu_finite(h[2 * i]), relu_finite(h[2 * i + 1]));
-            tmem_store_words<NW>(tl + TM::A0 + j * NW, w);
+            for (int i = 0; i < NWH; ++i) w[i] = pack_bf16(relu_finite(h[2 * i]), relu_finite(h[2 * i + 1]));
+            store_tmem(tl + TM::A0 + j * NW, w);
           }
           fence_proxy_async_smem();
           tc_fence_before();
@@ -397,83 +518,56 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
 #pragma unroll
           for (int blk = 0; blk < 2; ++blk) {
             {  // A: u = Wa relu(h) + ba -> relu(u)
-              float t[GS4];
-#pragma unroll
-              for (int i = 0; i < GS4; i += 4) {
-                const float4 b4 = *reinterpret_cast<const float4*>(cbb + (1 + 2 * blk) * GS4 + i);
-                t[i] = b4.x; t[i + 1] = b4.y; t[i + 2] = b4.z; t[i + 3] = b4.w;
-              }
+              float t[2 * NWH];
+              load_consts(cbb + (1 + 2 * blk) * GS4, t);
               mark_c(ST_A1 + 2 * blk);
               if (!(ok = wait(acc_bar, acc_par, 12 + blk))) break;
               mark_w(ST_A1 + 2 * blk);
               acc_par ^= 1;
               tc_fence_after();
-              uint32_t v[32];
-              tmem_ld32(tl + TM::ACC_H, v);
+              uint32_t v[16];
+              tmem_ld16(tl + TM::ACC_H + 2 * wo, v);
               tmem_wait_ld();
-              uint32_t w[NW];
+              uint32_t w[NWH];
 #pragma unroll
-              for (int i = 0; i < NW; ++i)
+              for (int i = 0; i < NWH; ++i)
                 w[i] = pack_bf16(relu_finite(__uint_as_float(v[2 * i]) + t[2 * i]),
                                  relu_finite(__uint_as_float(v[2 * i + 1]) + t[2 * i + 1]));
-              if (blk == 0) {
-                tmem_store_words<NW>(tl + TM::A1 + j * NW, w);
-              } else {
-                const uint32_t b0 = (uint32_t)slot0 * 2;
-#pragma unroll
-                for (int i = 0; i < NW; ++i) {
-                  uint32_t bo = b0 + 4 * i;
-                  *reinterpret_cast<uint32_t*>(sA3 + (bo >> 4) * 2048 + rowoff + (bo & 15)) = w[i];
-                }
-                fence_proxy_async_smem();
-              }
+              if (blk == 0) store_tmem(tl + TM::A1 + j * NW, w);
+              else store_smem(sA3, slot0, w);
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(op_bar);
             {  // B: h += gate * (Wb relu(u) + bb)
-              float t[GS4], g[GS4];
-#pragma unroll
-              for (int i = 0; i < GS4; i += 4) {
-                const float4 b4 = *reinterpret_cast<const float4*>(cbb + (2 + 2 * blk) * GS4 + i);
-                t[i] = b4.x; t[i + 1] = b4.y; t[i + 2] = b4.z; t[i + 3] = b4.w;
-              }
+              float t[2 * NWH], g[2 * NWH];
+              load_consts(cbb + (2 + 2 * blk) * GS4, t);
               if (ctx_staged) {
-#pragma unroll
-                for (int i = 0; i < GS4; i += 4) {
-                  const float4 c4 = *reinterpret_cast<const float4*>(cbc + (blk + 1) * GS4 + i);
-                  g[i] = c4.x; g[i + 1] = c4.y; g[i + 2] = c4.z; g[i + 3] = c4.w;
-                }
+                load_consts(cbc + (blk + 1) * GS4, g);
               } else {
-                const float* gp = pl + (size_t)(blk + 1) * s.KTOT + slot0;
+                const float* gp = pl + (size_t)(blk + 1) * s.KTOT + slot0 + 2 * wo;
 #pragma unroll
-                for (int i = 0; i < GSP; ++i) g[i] = __ldg(gp + i);
+                for (int i = 0; i < 2 * NWH; ++i) g[i] = i < 2 * nwo ? __ldg(gp + i) : 0.f;
               }
               mark_c(ST_B1 + 2 * blk);
               if (!(ok = wait(acc_bar, acc_par, 14 + blk))) break;
               mark_w(ST_B1 + 2 * blk);
               acc_par ^= 1;
               tc_fence_after();
-              uint32_t v[32];
-              tmem_ld32(tl + TM::ACC_H, v);
+              uint32_t v[16];
+              tmem_ld16(tl + TM::ACC_H + 2 * wo, v);
               tmem_wait_ld();
 #pragma unroll
-              for (int i = 0; i < GSP; ++i) h[i] = fmaf(g[i], __uint_as_float(v[i]) + t[i], h[i]);
-              uint32_t w[NW];
+              for (int i = 0; i < 2 * NWH; ++i) h[i] = fmaf(g[i], __uint_as_float(v[i]) + t[i], h[i]);
+              uint32_t w[NWH];
               if (blk == 0) {
 #pragma unroll
-                for (int i = 0; i < NW; ++i) w[i] = pack_bf16(relu_finite(h[2 * i]), relu_finite(h[2 * i + 1]));
-                tmem_store_words<NW>(tl + TM::A2 + j * NW, w);
+                for (int i = 0; i < NWH; ++i) w[i] = pack_bf16(relu_finite(h[2 * i]), relu_finite(h[2 * i + 1]));
+                store_tmem(tl + TM::A2 + j * NW, w);
               } else {
 #pragma unroll
-                for (int i = 0; i < NW; ++i) w[i] = pack_bf16(finite_clamp(h[2 * i]), finite_clamp(h[2 * i + 1]));
-                const uint32_t b0 = (uint32_t)slot0 * 2;
-#pragma unroll
-                for (int i = 0; i < NW; ++i) {
-                  uint32_t bo = b0 + 4 * i;
-                  *reinterpret_cast<uint32_t*>(sA4 + (bo >> 4) * 2048 + rowoff + (bo & 15)) = w[i];
-                }
-                fence_proxy_async_smem();
+                for (int i = 0; i < NWH; ++i) w[i] = pack_bf16(finite_clamp(h[2 * i]), finite_clamp(h[2 * i + 1]));
+                store_smem(sA4, slot0, w);
               }
             }
             tc_fence_before();
@@ -487,7 +581,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
       }
       if (!ok) break;
       // ---------------- tail of inverse + ParamScaler (shared with the FP32 tier) ----------------
-      if (valid) {
+      if (valid && half == 0) {
         float v[PF_MAX_D];
 #pragma unroll
         for (int jj = 0; jj < PF_MAX_D; ++jj) v[jj] = jj < D ? yin[D - 1 - jj] : 0.f;
@@ -505,7 +599,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
       for (int i = 0; i < 6; ++i) { a.prof[i] = pw[i]; a.prof[6 + i] = pc[i]; }
       a.prof[15] = clock64() - t_begin;
     }
-  } else if (warp == 4) {
+  } else if (warp == 8) {
     // ============================ MMA issuer ============================
     // the whole warp runs the (warp-uniform) loops; one elected lane issues tcgen05.mma / commit
     if (lvl <= -13) *abort_s = 1;
@@ -594,7 +688,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
         a.prof[16] = m_loop; a.prof[17] = m_commit; a.prof[18] = n_mma;
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == 9) {
     // ============================ weight loader ============================
     if (lvl != -11 && lvl != -12) {
       uint32_t slot = 0, empty_par = 1;   // a fresh barrier passes a wait on parity 1
@@ -625,7 +719,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
         }
       }
     }
-  } else if (warp == 6) {
+  } else if (warp == 10) {
     // ============================ constants stager ============================
     // One step ahead of the row warps: the biases of the step's six stages and the context terms of the
     // tile's (at most two) events go to shared memory, so no global-load latency sits on the serial chain.
@@ -684,7 +778,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) tmem_dealloc(tmem, 512);
+  if (warp == 8) tmem_dealloc(tmem, 512);
 }
 
 }  // namespace pf
@@ -725,7 +819,7 @@ static bool tc_plan(const pf_flow* f, TcShape& s, std::vector<TcItem>& items) {
 }
 
 static int tc_smem_bytes(const TcShape& s) {
-  size_t y = ((size_t)2 * TC_ROWS * s.D + 3) / 4 * 4 + TC_NCB * (size_t)tc_cb_floats(s.GSP);
+  size_t y = ((size_t)2 * TC_ROWS * s.D + 3) / 4 * 4 + TC_NCB * (size_t)tc_cb_floats(s.GSP) + TC_ROWS * 17;
   return (int)((size_t)2 * s.KA * 256 + 8192 + (size_t)TC_NSLOT * s.slot_bytes + y * 4 + (2 * TC_NSLOT + 2 * TC_NCB + 4) * 8);
 }
 

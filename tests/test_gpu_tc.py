@@ -110,6 +110,23 @@ def test_tc_fused_sampler_philox_and_scaler():
     assert float((a[2] != c[2]).float().mean()) <= 0.02   # rail masks agree on all but boundary cases
 
 
+def test_tc_second_instantiated_shape_8x192x16():
+    """experiments/frozen_context_heads.py:159-163 head shape (groups of 20/19 hidden units, tail bound 3)."""
+    spec, w, g = load_golden("head_8x192x16")
+    f32 = make_flow(spec, w, "cuda", tier="fp32")
+    tc = make_flow(spec, w, "cuda", tier="bf16")
+    z, ctx = t(g["z"], "cuda"), t(g["ctx"], "cuda")
+    x, ld = tc.inverse(z, ctx)
+    ex = _rel(x.cpu().numpy(), g["inv_x_f64"])
+    assert np.median(ex) <= 5e-3 and np.quantile(ex, 0.99) <= 1e-1, (np.median(ex), np.quantile(ex, 0.99))
+    gen = torch.Generator().manual_seed(9)
+    c2 = torch.randn(2, spec.context_features, generator=gen).cuda()
+    z2 = torch.randn(2 * 777, spec.features, generator=gen).cuda()
+    xa, _ = f32.inverse(z2, c2, n_per_ctx=777)
+    xb, _ = tc.inverse(z2, c2, n_per_ctx=777)
+    assert float(((xa - xb).abs() / xa.abs().clamp_min(1)).median()) <= 5e-3
+
+
 def test_tc_unsupported_shape_fails_loudly():
     spec, w, g = load_golden("head_12x384x24")
     with pytest.raises(Exception):
