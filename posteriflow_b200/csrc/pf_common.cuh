@@ -109,6 +109,9 @@ pf_status pf_tc_inverse(pf_flow* f, cudaStream_t st, const float* z, uint64_t se
                         const int64_t* row2ctx, int64_t n_per_ctx, int64_t R, int64_t E, float* x, float* logdet,
                         uint8_t* railed, uint32_t flags, const pf_scaler* scaler, void* workspace,
                         size_t workspace_bytes);
+pf_status pf_tc_forward(pf_flow* f, cudaStream_t st, const float* x, const float* ctx, const int64_t* row2ctx,
+                        int64_t n_per_ctx, int64_t R, int64_t E, float* z, float* logdet, uint32_t flags,
+                        void* workspace, size_t workspace_bytes);
 pf_status pf_tc_ctxproj(pf_flow* f, cudaStream_t st, const float* ctx, int64_t E, uint32_t flags, float* proj);
 size_t pf_tc_workspace_bytes(const pf_flow* f, int64_t R, int64_t E);
 void pf_tc_destroy(pf_flow* f);

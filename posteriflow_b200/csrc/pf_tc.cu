@@ -188,7 +188,11 @@ struct RegQ {
   __device__ __forceinline__ float operator()(int i) const { return q[i]; }
 };
 
-template <int NB, int GSP>
+// INV = true: sampling direction (z -> x, NSFPosteriorFlow.inverse).  INV = false: density direction
+// (x -> z, NSFPosteriorFlow.forward, flows.py:610-618) on the SAME stepwise schedule: with x known, step d
+// evaluates dim d's spline forward and then the hidden group of degree d -- the masks make that identical to one
+// dense MADE pass, and the weight image, staging and barrier protocol are shared between the directions.
+template <int NB, int GSP, bool INV>
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs a) {
   using TM = TcTmem<GSP>;
   constexpr int NW = GSP / 2;
@@ -334,7 +338,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
       bool bad = false;
       float* yin = y0;
       float* yout = y1;
-      for (int l = s.L - 1; l >= 0 && ok; --l) {
+      for (int li = 0; li < s.L && ok; ++li) {
+        const int l = INV ? s.L - 1 - li : li;
         const bool reversed = (l != s.L - 1);
         const float* pl = projr + (size_t)l * 3 * s.KTOT;
         for (int d = 1; d <= D && ok; ++d) {
@@ -350,11 +355,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
           if (d == 1) { mark_c(0); pcur = ST_F; }
           // ---------------- F(d): spline parameters of dim d -> inverse spline, split over the thread pair -------
           if (half == 1) {
-            // ---- widths: 16 logits -> 17 knots of the x axis, handed to half 0 through shared memory ----
+            // ---- the axis that is NOT searched (widths when sampling, heights for the density direction):
+            // 16 logits -> its 17 knots, handed to half 0 through shared memory ----
+            constexpr int OTHER = INV ? 0 : NB;
             float qw[NB];
 #pragma unroll
             for (int i = 0; i < NB; i += 4) {
-              const float4 v4 = *reinterpret_cast<const float4*>(cb + i);
+              const float4 v4 = *reinterpret_cast<const float4*>(cb + OTHER + i);
               qw[i] = v4.x; qw[i + 1] = v4.y; qw[i + 2] = v4.z; qw[i + 3] = v4.w;
             }
             if (d > 1) {
@@ -362,7 +369,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
               acc_par ^= 1;
               tc_fence_after();
               uint32_t v[16];
-              tmem_ld16(tl + TM::ACC_F, v);
+              tmem_ld16(tl + TM::ACC_F + OTHER, v);
               tmem_wait_ld();
 #pragma unroll
               for (int i = 0; i < NB; ++i) qw[i] += __uint_as_float(v[i]);
@@ -388,16 +395,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
             }
             bar_arrive(1 + q4, 64);
             bar_sync(5 + q4, 64);          // half 0 has read the knots and published x_d
-            xd = yout[j];
+            xd = INV ? yout[j] : yin[D - 1 - j];   // the conditioner input of this dimension
           } else {
-            // ---- heights + derivatives: bin search on the y axis, then the closing solve ----
+            // ---- searched axis (heights when sampling, widths for the density direction) + derivatives:
+            // bin search, then the closing solve.  q[0,16) = logits of the searched axis, q[16,31) = derivatives ----
+            constexpr int SEARCH = INV ? NB : 0;
             float q[32];
 #pragma unroll
-            for (int i = 0; i < 32; i += 4) {
-              const float4 v4 = *reinterpret_cast<const float4*>(cb + NB + i);
+            for (int i = 0; i < NB; i += 4) {
+              const float4 v4 = *reinterpret_cast<const float4*>(cb + SEARCH + i);
+              const float4 d4 = *reinterpret_cast<const float4*>(cb + 2 * NB + i);
               q[i] = v4.x; q[i + 1] = v4.y; q[i + 2] = v4.z; q[i + 3] = v4.w;
+              q[NB + i] = d4.x; q[NB + i + 1] = d4.y; q[NB + i + 2] = d4.z; q[NB + i + 3] = d4.w;
             }
-            const float y = yin[reversed ? D - 1 - j : j];
+            const float y = INV ? yin[reversed ? D - 1 - j : j] : yin[D - 1 - j];
             if (d > 1) {
               mark_c(ST_F);
               if (!(ok = wait(acc_bar, acc_par, 10))) break;
@@ -405,7 +416,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
               acc_par ^= 1;
               tc_fence_after();
               uint32_t v[32];
-              tmem_ld32(tl + TM::ACC_F + NB, v);
+              tmem_ld16(tl + TM::ACC_F + SEARCH, v);
+              tmem_ld16(tl + TM::ACC_F + 2 * NB, v + 16);
               tmem_wait_ld();
 #pragma unroll
               for (int i = 0; i < 2 * NB - 1; ++i) q[i] += __uint_as_float(v[i]);
@@ -441,33 +453,52 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
             }
             const float dk = kMinDeriv + (u0 > 20.f ? u0 : fx_log(1.f + fx_exp(u0)));
             const float dk1 = kMinDeriv + (u1 > 20.f ? u1 : fx_log(1.f + fx_exp(u1)));
-            bar_sync(1 + q4, 64);          // the width knots of this row are in shared memory
-            const float xk = xr[k];
-            const float wk = xr[k + 1] - xk;
-            const float sl = hk * fx_rcp(wk);
-            const float dy = y - yk;
-            const float t = dk + dk1 - 2.f * sl;
-            const float qa = fmaf(dy, t, hk * (sl - dk));
-            const float qb = fmaf(hk, dk, -dy * t);
-            const float qc = -sl * dy;
-            const float disc = fmaxf(fmaf(qb, qb, -4.f * qa * qc), 0.f);
-            const float root = 2.f * qc * fx_rcp(-qb - fx_sqrt(disc));
-            const float tt = root * (1.f - root);
-            const float den = fmaf(t, tt, sl);
-            const float omr = 1.f - root;
-            const float dnum = sl * sl * (dk1 * root * root + 2.f * sl * tt + dk * omr * omr);
+            bar_sync(1 + q4, 64);          // the other axis' knots of this row are in shared memory
+            const float ok_ = xr[k];                  // other-axis knot and bin size at the bin found
+            const float os_ = xr[k + 1] - ok_;
             const bool inside = y >= -B && y <= B;       // outside (or NaN): linear tails, identity
-            const float xo = inside ? fmaf(root, wk, xk) : y;
-            ld_acc += inside ? -fx_log(dnum * fx_rcp(den * den)) : 0.f;
+            float res, lad;
+            if (INV) {
+              const float xk = ok_, wk = os_;
+              const float sl = hk * fx_rcp(wk);
+              const float dy = y - yk;
+              const float t = dk + dk1 - 2.f * sl;
+              const float qa = fmaf(dy, t, hk * (sl - dk));
+              const float qb = fmaf(hk, dk, -dy * t);
+              const float qc = -sl * dy;
+              const float disc = fmaxf(fmaf(qb, qb, -4.f * qa * qc), 0.f);
+              const float root = 2.f * qc * fx_rcp(-qb - fx_sqrt(disc));
+              const float tt = root * (1.f - root);
+              const float den = fmaf(t, tt, sl);
+              const float omr = 1.f - root;
+              const float dnum = sl * sl * (dk1 * root * root + 2.f * sl * tt + dk * omr * omr);
+              res = fmaf(root, wk, xk);
+              lad = -fx_log(dnum * fx_rcp(den * den));
+            } else {   // forward map: (yk, hk) here are the searched x-axis knot / width, (ok_, os_) the y axis
+              const float xk = yk, wk = hk, y0k = ok_, h0k = os_;
+              const float rw = fx_rcp(wk);
+              const float sl = h0k * rw;
+              const float th = (y - xk) * rw;
+              const float omt = 1.f - th;
+              const float tt = th * omt;
+              const float den = fmaf(dk + dk1 - 2.f * sl, tt, sl);
+              const float rden = fx_rcp(den);
+              res = fmaf(h0k * (sl * th * th + dk * tt), rden, y0k);
+              const float dnum = sl * sl * (dk1 * th * th + 2.f * sl * tt + dk * omt * omt);
+              lad = fx_log(dnum * rden * rden);
+            }
+            const float xo = inside ? res : y;
+            ld_acc += inside ? lad : 0.f;
             yout[j] = xo;
-            bad = bad || !(fabsf(xo) <= 3.0e38f);
-            const float xc = finite_clamp(xo);
+            const float xin = INV ? xo : y;              // what the conditioner of the later dimensions sees
+            bad = bad || !(fabsf(xin) <= 3.0e38f);
+            const float xc = finite_clamp(xin);
             const __nv_bfloat16 hi = __float2bfloat16(xc);
             const __nv_bfloat16 lo = __float2bfloat16(xc - __bfloat162float(hi));
             *reinterpret_cast<__nv_bfloat16*>(sX + (j / 8) * 2048 + rowoff + (j % 8) * 2) = hi;
             *reinterpret_cast<__nv_bfloat16*>(sX + (2 + j / 8) * 2048 + rowoff + (j % 8) * 2) = lo;
             bar_arrive(5 + q4, 64);
-            xd = xo;
+            xd = xin;
           }
           if (d == D) {       // last dim: no hidden group follows, and the next stage (F(1)) has no MMA
             mark_c(ST_F);
@@ -583,16 +614,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
       // ---------------- tail of inverse + ParamScaler (shared with the FP32 tier) ----------------
       if (valid && half == 0) {
         float v[PF_MAX_D];
+        if (INV) {
 #pragma unroll
-        for (int jj = 0; jj < PF_MAX_D; ++jj) v[jj] = jj < D ? yin[D - 1 - jj] : 0.f;
-        if (bad) {  // a non-finite value entered the conditioner: the reference turns the row into NaN
-          for (int jj = 0; jj < D; ++jj) v[jj] = __int_as_float(0x7fc00000);
-          ld_acc = __int_as_float(0x7fc00000);
+          for (int jj = 0; jj < PF_MAX_D; ++jj) v[jj] = jj < D ? yin[D - 1 - jj] : 0.f;
+          if (bad) {  // a non-finite value entered the conditioner: the reference turns the row into NaN
+            for (int jj = 0; jj < D; ++jj) v[jj] = __int_as_float(0x7fc00000);
+            ld_acc = __int_as_float(0x7fc00000);
+          }
+          const bool rail = finish_row(v, D, a.flags, a.clamp, a.sc);
+          if (a.railed) a.railed[grow] = rail ? 1 : 0;
+        } else {      // density direction: z = output of the last layer as it is (flows.py:615-618)
+#pragma unroll
+          for (int jj = 0; jj < PF_MAX_D; ++jj) v[jj] = jj < D ? yin[jj] : 0.f;
+          if (bad) {
+            for (int jj = 0; jj < D; ++jj) v[jj] = __int_as_float(0x7fc00000);
+            ld_acc = __int_as_float(0x7fc00000);
+          }
         }
-        const bool rail = finish_row(v, D, a.flags, a.clamp, a.sc);
         for (int jj = 0; jj < D; ++jj) a.x[grow * D + jj] = v[jj];
         if (a.logdet) a.logdet[grow] = ld_acc;
-        if (a.railed) a.railed[grow] = rail ? 1 : 0;
       }
     }
     if (prof) {
@@ -613,7 +653,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
       const uint32_t aX = smem_u32(sX), aA3 = smem_u32(sA3), aA4 = smem_u32(sA4), aRing = smem_u32(ring);
       bool ok = true;
       for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
-        for (int l = s.L - 1; l >= 0 && ok; --l) {
+        for (int li = 0; li < s.L && ok; ++li) {
+        const int l = INV ? s.L - 1 - li : li;
           for (int d = 1; d <= D && ok; ++d) {
             // MMA stages of step d: [F(d) + I(d)] (one commit), A1, B1, A2, B2
             for (int ms = 0; ms < 5 && ok; ++ms) {
@@ -694,7 +735,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
       uint32_t slot = 0, empty_par = 1;   // a fresh barrier passes a wait on parity 1
       bool ok = true;
       for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
-        for (int l = s.L - 1; l >= 0 && ok; --l) {
+        for (int li = 0; li < s.L && ok; ++li) {
+        const int l = INV ? s.L - 1 - li : li;
           const uint8_t* src = a.image + (size_t)l * s.layer_bytes;
           for (int d = 1; d <= D && ok; ++d) {
             for (int st = 0; st < ST_COUNT && ok; ++st) {
@@ -732,7 +774,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
         const bool ctx_staged = !a.cm.row2ctx && a.cm.n_per_ctx >= TC_ROWS;
         const float* p0 = a.proj + a.cm(r_first) * a.ldproj;
         const float* p1 = a.proj + a.cm(r_last) * a.ldproj;
-        for (int l = s.L - 1; l >= 0 && ok; --l) {
+        for (int li = 0; li < s.L && ok; ++li) {
+        const int l = INV ? s.L - 1 - li : li;
           for (int d = 1; d <= D && ok; ++d) {
             const int buf = stepc & (TC_NCB - 1);
             if (!(ok = wait(&cempty[buf], ((stepc / TC_NCB) & 1) ^ 1, 41))) break;
@@ -823,16 +866,16 @@ static int tc_smem_bytes(const TcShape& s) {
   return (int)((size_t)2 * s.KA * 256 + 8192 + (size_t)TC_NSLOT * s.slot_bytes + y * 4 + (2 * TC_NSLOT + 2 * TC_NCB + 4) * 8);
 }
 
-template <int NB, int GSP>
+template <int NB, int GSP, bool INV>
 static pf_status tc_launch(pf_flow* f, cudaStream_t st, const TcArgs& a, int smem) {
   static bool attr_done[64] = {};
   int dev = f->desc.device;
   if (dev < 64 && !attr_done[dev]) {
-    PF_CUDA(cudaFuncSetAttribute(tc_sampler_kernel<NB, GSP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    PF_CUDA(cudaFuncSetAttribute(tc_sampler_kernel<NB, GSP, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_done[dev] = true;
   }
   int grid = a.n_tiles < f->sm_count ? a.n_tiles : f->sm_count;
-  tc_sampler_kernel<NB, GSP><<<grid, TC_THREADS, smem, st>>>(a);
+  tc_sampler_kernel<NB, GSP, INV><<<grid, TC_THREADS, smem, st>>>(a);
   PF_LAUNCH_CHECK(f);
   return PF_OK;
 }
@@ -935,7 +978,8 @@ size_t pf_tc_workspace_bytes(const pf_flow* f, int64_t R, int64_t E) {
   return (size_t)prow * f->L * 3 * KT * sizeof(float) + 512;
 }
 
-pf_status pf_tc_inverse(pf_flow* f, cudaStream_t st, const float* z, uint64_t seed, const float* ctx,
+// both directions: `z` = input rows ([R, D]; NULL = Philox noise, sampling direction only), `x` = output rows
+static pf_status tc_run(pf_flow* f, cudaStream_t st, bool inverse, const float* z, uint64_t seed, const float* ctx,
                         const int64_t* row2ctx, int64_t n_per_ctx, int64_t R, int64_t E, float* x, float* logdet,
                         uint8_t* railed, uint32_t flags, const pf_scaler* scaler, void* workspace,
                         size_t workspace_bytes) {
@@ -1009,8 +1053,13 @@ pf_status pf_tc_inverse(pf_flow* f, cudaStream_t st, const float* z, uint64_t se
       a.dbg_stop = stop ? atoi(stop) : -1;
     }
     if (a.dbg_stop == -10) continue;
-    if (s.GSP == 26) PF_TRY((tc_launch<16, 26>(f, st, a, t->kernel_smem)));
-    else PF_TRY((tc_launch<16, 20>(f, st, a, t->kernel_smem)));
+    if (inverse) {
+      if (s.GSP == 26) PF_TRY((tc_launch<16, 26, true>(f, st, a, t->kernel_smem)));
+      else PF_TRY((tc_launch<16, 20, true>(f, st, a, t->kernel_smem)));
+    } else {
+      if (s.GSP == 26) PF_TRY((tc_launch<16, 26, false>(f, st, a, t->kernel_smem)));
+      else PF_TRY((tc_launch<16, 20, false>(f, st, a, t->kernel_smem)));
+    }
   }
   if (t->prof) {
     long long h[24];
@@ -1034,4 +1083,22 @@ pf_status pf_tc_inverse(pf_flow* f, cudaStream_t st, const float* z, uint64_t se
     }
   }
   return PF_OK;
+}
+
+pf_status pf_tc_inverse(pf_flow* f, cudaStream_t st, const float* z, uint64_t seed, const float* ctx,
+                        const int64_t* row2ctx, int64_t n_per_ctx, int64_t R, int64_t E, float* x, float* logdet,
+                        uint8_t* railed, uint32_t flags, const pf_scaler* scaler, void* workspace,
+                        size_t workspace_bytes) {
+  return tc_run(f, st, true, z, seed, ctx, row2ctx, n_per_ctx, R, E, x, logdet, railed, flags, scaler, workspace,
+                workspace_bytes);
+}
+
+// Density direction (NSFPosteriorFlow.forward, flows.py:610-618) without saved activations: x [R, D] -> z, logdet.
+pf_status pf_tc_forward(pf_flow* f, cudaStream_t st, const float* x, const float* ctx, const int64_t* row2ctx,
+                        int64_t n_per_ctx, int64_t R, int64_t E, float* z, float* logdet, uint32_t flags,
+                        void* workspace, size_t workspace_bytes) {
+  if (!x || !z) return PF_ERR_INVALID;
+  const uint32_t fl = flags & (PF_FLAG_SANITIZE_CTX | PF_FLAG_CTX_IS_PROJ);
+  return tc_run(f, st, false, x, 0, ctx, row2ctx, n_per_ctx, R, E, z, logdet, nullptr, fl, nullptr, workspace,
+                workspace_bytes);
 }

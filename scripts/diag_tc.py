@@ -35,6 +35,13 @@ for case in [c for c in sys.argv[1:] if not c.startswith("-")] or ["lean_default
     print("  x   bf16 tier vs f64:", q(np.abs(xb.cpu().numpy() - r64) / den))
     print("  ld  fp32 tier vs f64:", q(np.abs(la.cpu().numpy() - l64) / np.maximum(1, np.abs(l64))))
     print("  ld  bf16 tier vs f64:", q(np.abs(lb.cpu().numpy() - l64) / np.maximum(1, np.abs(l64))))
+    with torch.no_grad():
+        za, fa = f32.forward(t(g["fwd_x"], "cuda"), ctx)
+        zb, fb = tc.forward(t(g["fwd_x"], "cuda"), ctx)
+    z64, f64 = g["fwd_z_f64"], g["fwd_logdet_f64"]
+    print("  fwd z  fp32 tier vs f64:", q(np.abs(za.cpu().numpy() - z64) / np.maximum(1, np.abs(z64))))
+    print("  fwd z  bf16 tier vs f64:", q(np.abs(zb.cpu().numpy() - z64) / np.maximum(1, np.abs(z64))))
+    print("  fwd ld bf16 tier vs f64:", q(np.abs(fb.cpu().numpy() - f64) / np.maximum(1, np.abs(f64))))
     # broadcast form, many tiles, ragged last tile
     gen = torch.Generator().manual_seed(5)
     E, n = 3, 1111
@@ -60,3 +67,13 @@ if "--time" in sys.argv:
             torch.cuda.synchronize()
             dt = time.perf_counter() - t0
             print(f"  {tier}: {E}x{n} samples in {dt*1e3:.1f} ms -> {E*n/dt/1e6:.2f} M samples/s", flush=True)
+        y = th.reshape(-1, spec.features)
+        yn = sc.normalize(y)
+        for it in range(2):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            with torch.no_grad():
+                nll = flow.compute_psd_aware_nll(yn, ctx, None, n_per_ctx=n)
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            print(f"  {tier}: log-prob of {E*n} rows in {dt*1e3:.1f} ms -> {E*n/dt/1e6:.2f} M rows/s", flush=True)

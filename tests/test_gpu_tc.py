@@ -110,6 +110,42 @@ def test_tc_fused_sampler_philox_and_scaler():
     assert float((a[2] != c[2]).float().mean()) <= 0.02   # rail masks agree on all but boundary cases
 
 
+def test_tc_density_direction_matches_float64_reference():
+    """NSFPosteriorFlow.forward / compute_psd_aware_nll of a bf16-tier flow (no gradient needed) run on the same
+    tcgen05 kernel, density direction.  Stated tolerance on the golden inputs (which spread over the whole
+    [-5, 5] spline domain, knots included): z median <= 8e-3, 99th percentile <= 1.5e-1; log-det median <= 5e-2
+    (110 log-terms, each carrying the ~2e-3 relative error of bf16 operands; measured 3.3e-3 / 6.8e-2 / 2.6e-2)."""
+    spec, w, g = load_golden("lean_default")
+    tc = make_flow(spec, w, "cuda", tier="bf16")
+    x, ctx = t(g["fwd_x"], "cuda"), t(g["ctx"], "cuda")
+    with torch.no_grad():
+        z, ld = tc.forward(x, ctx)
+        nll = tc.compute_psd_aware_nll(x, ctx, None)
+    ez = _rel(z.cpu().numpy(), g["fwd_z_f64"])
+    el = _rel(ld.cpu().numpy(), g["fwd_logdet_f64"])
+    assert np.median(ez) <= 8e-3 and np.quantile(ez, 0.99) <= 1.5e-1, (np.median(ez), np.quantile(ez, 0.99))
+    assert np.median(el) <= 5e-2, np.median(el)
+    ref_nll = -(-0.5 * ((z ** 2).sum(1) + spec.features * np.log(2 * np.pi)) + ld)
+    assert torch.allclose(nll, ref_nll, rtol=1e-5, atol=1e-4)
+
+
+@pytest.mark.parametrize("R", [1, 300, 20000])
+def test_tc_round_trip_inverse_then_forward(R):
+    spec, w, g = load_golden("lean_default")
+    tc = make_flow(spec, w, "cuda", tier="bf16")
+    gen = torch.Generator().manual_seed(R)
+    ctx = torch.randn(2, spec.context_features, generator=gen).cuda()
+    z = torch.randn(2 * R, spec.features, generator=gen).cuda()
+    from posteriflow_b200 import _cabi as A
+    fh = tc.handle()
+    x, ld = torch.ops.posteriflow.nsf_inverse(z, ctx, fh.id, R, 0, None, None, None, None)   # no clamp
+    with torch.no_grad():
+        z2, ld2 = tc.forward(x, ctx, n_per_ctx=R)
+    dz = (z2 - z).abs().flatten()
+    dl = (ld + ld2).abs() / ld.abs().clamp_min(1.0)
+    assert float(dz.median()) <= 5e-3 and float(dl.median()) <= 2e-2, (float(dz.median()), float(dl.median()))
+
+
 def test_tc_second_instantiated_shape_8x192x16():
     """experiments/frozen_context_heads.py:159-163 head shape (groups of 20/19 hidden units, tail bound 3)."""
     spec, w, g = load_golden("head_8x192x16")
