@@ -193,6 +193,17 @@ pf_status pf_flow_backward(pf_flow* flow, const void* saved, const float* ctx, c
                            const float* glogdet, float* gx, float* gctx, const pf_layer_grads* grads,
                            void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- serving epilogue ------------------------------------------------------------------------ */
+
+/* Replaces the tail of one iteration of infer()'s sampling loop (inference/pipeline.py:180, 57-76, 184-186):
+ * given wrapped normalised samples y [R, D] and their flow NLL nll [R] (pf_flow_forward(nll != NULL) on y),
+ *   theta[r, :] = ParamScaler.denormalize(y[r, :])                       (lean_npe.py:111-114)
+ *   logq[r]     = -nll[r] + sum_j (log 2 - log(hi_j - lo_j)) - sum_{log dims} log(max(theta_rj, 1e-6))
+ * and, with PF_FLAG_SORT_MASSES, dims 0/1 of theta swapped so that m1 >= m2 (logq is not affected).
+ * No handle: the arithmetic involves the scaler only.  theta / logq may be NULL. */
+pf_status pf_physical_logq(const float* y, const float* nll, const pf_scaler* scaler, int32_t D, int64_t R,
+                           float* theta, float* logq, uint32_t flags, int32_t device, void* stream);
+
 /* ---- sizes / diagnostics -------------------------------------------------------------------- */
 
 size_t pf_flow_workspace_bytes(const pf_flow* flow, int32_t op, int64_t R, int64_t E);

@@ -6,7 +6,7 @@ on first use and there is no CPU fallback (see _cabi.load_library).
 from . import _cabi  # noqa: F401
 from . import ops  # noqa: F401
 from .flow import FLOW_NORM_BOUND, NSFPosteriorFlow  # noqa: F401
-from .lean import LeanNPE, ParamScaler, PARAM_NAMES, accelerate, sample_fused  # noqa: F401
+from .lean import LeanNPE, ParamScaler, PARAM_NAMES, accelerate, posterior_chunk, sample_fused  # noqa: F401
 
 __all__ = ["NSFPosteriorFlow", "LeanNPE", "ParamScaler", "PARAM_NAMES", "FLOW_NORM_BOUND", "accelerate",
-           "sample_fused", "ops"]
+           "sample_fused", "posterior_chunk", "ops"]

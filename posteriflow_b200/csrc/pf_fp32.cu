@@ -831,3 +831,52 @@ extern "C" size_t pf_flow_workspace_bytes(const pf_flow* f, int32_t op, int64_t 
   }
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// serving epilogue: physical-units samples + log-density (pipeline.py:57-76, 180, 184-186)
+// ------------------------------------------------------------------------------------------------
+namespace pf {
+__global__ void physical_logq_kernel(const float* __restrict__ Y, const float* __restrict__ nll, ScalerDev sc, int D,
+                                     int64_t R, float* __restrict__ theta, float* __restrict__ logq, uint32_t flags) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= R) return;
+  float v[PF_MAX_D];
+  float jac = 0.f, slog = 0.f;
+#pragma unroll
+  for (int j = 0; j < PF_MAX_D; ++j) {
+    if (j >= D) break;
+    const float lo = sc.lo[j], hi = sc.hi[j];
+    const float y = fminf(fmaxf(Y[r * D + j], -1.f), 1.f);
+    float x = (y + 1.f) / 2.f * (hi - lo) + lo;
+    if (sc.log_mask[j]) {
+      x = expf(x);
+      slog += logf(fmaxf(x, 1e-6f));
+    }
+    jac += 0.6931471805599453f - logf(hi - lo);
+    v[j] = x;
+  }
+  if (logq) logq[r] = -nll[r] + jac - slog;
+  if (theta) {
+    if ((flags & PF_FLAG_SORT_MASSES) && D >= 2 && v[1] > v[0]) { float t = v[0]; v[0] = v[1]; v[1] = t; }
+#pragma unroll
+    for (int j = 0; j < PF_MAX_D; ++j) {
+      if (j >= D) break;
+      theta[r * D + j] = v[j];
+    }
+  }
+}
+}  // namespace pf
+
+extern "C" pf_status pf_physical_logq(const float* y, const float* nll, const pf_scaler* scaler, int32_t D, int64_t R,
+                                      float* theta, float* logq, uint32_t flags, int32_t device, void* stream) {
+  if (!y || !scaler || !scaler->lo || !scaler->hi || !scaler->log_mask || D < 1 || D > PF_MAX_D || R < 0)
+    return PF_ERR_INVALID;
+  if (logq && !nll) return PF_ERR_INVALID;
+  if (R == 0) return PF_OK;
+  PF_CUDA(cudaSetDevice(device));
+  ScalerDev sc{scaler->lo, scaler->hi, scaler->log_mask, scaler->circ_mask};
+  physical_logq_kernel<<<(unsigned)((R + 255) / 256), 256, 0, (cudaStream_t)stream>>>(y, nll, sc, D, R, theta, logq, flags);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return pf::cuda_fail(e, "physical_logq launch", __FILE__, __LINE__);
+  return PF_OK;
+}

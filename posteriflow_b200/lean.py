@@ -78,6 +78,23 @@ def sample_fused(flow: NSFPosteriorFlow, scaler: ParamScaler, ctx_full: Tensor, 
                                                       scaler.lo, scaler.hi, scaler.log_mask, scaler.circ_mask)
 
 
+def posterior_chunk(flow: NSFPosteriorFlow, scaler: ParamScaler, ctx_full: Tensor, n_samples: int,
+                    z: Optional[Tensor] = None, seed: int = 0, sort_masses: bool = True):
+    """One iteration of the reference's infer() sampling loop (inference/pipeline.py:168-186) for E events
+    at once, everything on the device: base noise -> inverse flow -> wrap -> rail mask -> flow NLL of the wrapped
+    samples -> physical log-density (ParamScaler Jacobian) -> denormalise -> m1 >= m2.
+    Returns (theta [E, n, D] physical, logq [E*n] physical, railed [E*n] uint8).  Four kernels after the two
+    context projections: sampler, density direction, base log-prob, physical epilogue."""
+    wrap_flags = A.PF_FLAG_SANITIZE_CTX | A.PF_FLAG_CLAMP | A.PF_FLAG_WRAP
+    y, _, railed = sample_fused(flow, scaler, ctx_full, n_samples, z=z, seed=seed, flags=wrap_flags)
+    E, n, D = y.shape
+    with torch.no_grad():
+        nll = flow.compute_psd_aware_nll(y.reshape(E * n, D), ctx_full, None, n_per_ctx=n)
+        theta, logq = torch.ops.posteriflow.nsf_physical(y.reshape(E * n, D), nll, bool(sort_masses), scaler.lo,
+                                                         scaler.hi, scaler.log_mask, scaler.circ_mask)
+    return theta.reshape(E, n, D), logq, railed
+
+
 class LeanNPE(nn.Module):
     """encoder (caller's PyTorch module) + rank embedding + B200 flow (lean_npe.py:255-338).
 
@@ -134,6 +151,18 @@ class LeanNPE(nn.Module):
             seed = 0
         theta, _, _ = sample_fused(self.flow, self.scaler, ctx, n_samples, z=z, seed=seed)
         return theta
+
+    @torch.no_grad()
+    def sample_with_log_prob(self, strain: Optional[Tensor], rank: int = 0, n_samples: int = 256,
+                             asd_bands: Optional[Tensor] = None, context: Optional[Tensor] = None,
+                             z: Optional[Tensor] = None, sort_masses: bool = True):
+        """The body of infer()'s loop (pipeline.py:161-186) as one call: (theta, log q physical, railed)."""
+        if context is None:
+            context = self.encode(strain, asd_bands)
+        r = torch.full((context.shape[0],), rank, dtype=torch.long, device=context.device)
+        ctx = self._full_context(context, r)
+        seed = 0 if z is not None else int(torch.randint(0, 2 ** 62, (1,)).item())
+        return posterior_chunk(self.flow, self.scaler, ctx, n_samples, z=z, seed=seed, sort_masses=sort_masses)
 
     def to(self, *args, **kwargs):
         out = super().to(*args, **kwargs)

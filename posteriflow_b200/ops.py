@@ -328,3 +328,26 @@ def nsf_sample_fused(ctx: Tensor, z: Optional[Tensor], seed: int, n: int, handle
 def _(ctx, z, seed, n, handle, flags, lo, hi, log_mask, circ_mask):
     E = ctx.shape[0]
     return (ctx.new_empty(E, n, lo.shape[0]), ctx.new_empty(E * n), ctx.new_empty(E * n, dtype=torch.uint8))
+
+
+@torch.library.custom_op("posteriflow::nsf_physical", mutates_args=())
+def nsf_physical(y: Tensor, nll: Tensor, sort_masses: bool, lo: Tensor, hi: Tensor, log_mask: Tensor,
+                 circ_mask: Tensor) -> Tuple[Tensor, Tensor]:
+    """Tail of infer()'s loop (pipeline.py:57-76, 180, 184-186): (theta physical [R, D], log q physical [R])."""
+    _require_cuda(y, nll)
+    y, nll = _f32c(y), _f32c(nll)
+    R, D = y.shape
+    theta = torch.empty_like(y)
+    logq = torch.empty(R, dtype=torch.float32, device=y.device)
+    sc, keep = _scaler_struct(lo, hi, log_mask, circ_mask)
+    lib = A.load_library()
+    idx = y.device.index if y.device.index is not None else torch.cuda.current_device()
+    with torch.cuda.device(idx):
+        A.check(lib.pf_physical_logq(y.data_ptr(), nll.data_ptr(), C.byref(sc), D, R, theta.data_ptr(), logq.data_ptr(),
+                                     A.PF_FLAG_SORT_MASSES if sort_masses else 0, idx, _stream()), "pf_physical_logq")
+    return theta, logq
+
+
+@nsf_physical.register_fake
+def _(y, nll, sort_masses, lo, hi, log_mask, circ_mask):
+    return torch.empty_like(y), y.new_empty(y.shape[0])

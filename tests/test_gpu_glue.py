@@ -10,9 +10,9 @@ from util import check_parity, load_golden, make_flow, rel_err, t
 pytestmark = pytest.mark.gpu
 
 
-def lean_model(w, g, device="cuda"):
+def lean_model(w, g, device="cuda", tier="fp32"):
     import posteriflow_b200 as P
-    m = P.LeanNPE()
+    m = P.LeanNPE(tier=tier)
     m.flow.load_state_dict(O.full_state_dict(O.FlowSpec(), w), strict=True)
     with torch.no_grad():
         m.rank_embed.weight.copy_(t(g["rank_embed"]))
@@ -84,6 +84,41 @@ def test_infer_chunk_rail_mask_and_logq():
     same = (y.cpu() - yref).abs().max(dim=1).values < 1e-3
     assert same.float().mean() > 0.9
     assert rel_err(logq.detach().cpu().numpy()[same.numpy()], g["infer_logq"][same.numpy()]) <= 2e-3
+
+
+@pytest.mark.parametrize("tier", ["fp32", "bf16"])
+def test_posterior_chunk_is_the_infer_loop_body(tier):
+    """posterior_chunk = one iteration of infer()'s loop (pipeline.py:168-186) on the device, against the golden
+    theta / log q / rail mask the reference code produced (fp32 tier: 1e-5 median on theta, 2e-3 on log q where
+    the wrap agrees; tensor-core tier: its stated 5e-3 / 5e-2)."""
+    import posteriflow_b200 as P
+    spec, w, g = load_golden("lean_glue")
+    m = lean_model(w, g, tier=tier)
+    n = int(g["n"])
+    ctx = m._full_context(t(g["context"], "cuda")[:1], torch.zeros(1, dtype=torch.long, device="cuda"))
+    z = t(g["z"], "cuda")[:n]
+    theta, logq, railed = P.posterior_chunk(m.flow, m.scaler, ctx, n, z=z, sort_masses=False)
+    ref = g["infer_theta"]
+    nonc = ~O.Scaler().circ_mask.numpy()
+    tol_t, tol_q = (1e-5, 2e-3) if tier == "fp32" else (5e-3, 5e-2)
+    err = np.abs(theta[0].cpu().numpy()[:, nonc] - ref[:, nonc]) / np.maximum(1, np.abs(ref[:, nonc]))
+    assert np.median(err) <= tol_t
+    assert abs(float(railed.float().mean()) - float(g["infer_railed"].mean())) <= (1.0 if tier == "fp32" else 3.0) / n + 1e-6
+    yref = O.Scaler().normalize(torch.from_numpy(ref))
+    ygot = O.Scaler().normalize(theta[0].cpu())
+    if tier == "fp32":
+        same = (ygot - yref).abs().max(dim=1).values < 1e-3
+        assert same.float().mean() > 0.9
+    else:   # bf16 operands: rows whose non-circular dims stayed within 0.1 (normalised units) of the reference
+        same = (ygot - yref)[:, torch.from_numpy(nonc)].abs().max(dim=1).values < 0.1
+        assert same.float().mean() > 0.6
+    eq = np.abs(logq.cpu().numpy() - g["infer_logq"]) / np.maximum(1, np.abs(g["infer_logq"]))
+    assert (np.max(eq[same.numpy()]) if tier == "fp32" else np.median(eq[same.numpy()])) <= tol_q
+    # mass ordering (pipeline.py:184-186) leaves everything else untouched
+    th2, lq2, _ = P.posterior_chunk(m.flow, m.scaler, ctx, n, z=z, sort_masses=True)
+    assert torch.equal(lq2, logq) and bool((th2[..., 0] >= th2[..., 1]).all())
+    assert torch.equal(th2[..., 2:], theta[..., 2:])
+    assert torch.equal(torch.maximum(theta[..., 0], theta[..., 1]), th2[..., 0])
 
 
 def test_broadcast_equals_dense_context():
