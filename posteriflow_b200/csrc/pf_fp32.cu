@@ -696,7 +696,7 @@ struct BwdWs {
 };
 
 static pf_status colsum(pf_flow* f, cudaStream_t st, const float* src, int ld, int R, int ncols, const ColMap& map) {
-  int slabs = cdiv(R, 512);
+  int slabs = cdiv(R, 64);
   if (slabs > 4 * f->sm_count) slabs = 4 * f->sm_count;
   int rps = cdiv(R, slabs);
   dim3 grid(cdiv(ncols, 32), cdiv(R, rps)), block(32, 8);

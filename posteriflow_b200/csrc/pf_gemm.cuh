@@ -17,30 +17,34 @@ __device__ __forceinline__ float sanitize_ctx(float v) {  // flows.py:632 nan_to
   return v;
 }
 
-// BN = 64 (thread tile 8x4) or 32 (thread tile 8x2: the sampler's 26-unit degree groups)
-template <class Epi, int AMODE, int BN>
+// BN = 64 (thread tile TMx4) or 32 (thread tile TMx2: the sampler's 26-unit degree groups).
+// BM = 128 (TM = 8) for row counts that fill the GPU; BM = 32 (TM = 2) for the training step's ~1 k rows, where
+// 128-row tiles would leave three quarters of the SMs without a CTA.
+template <class Epi, int AMODE, int BN, int BM = NT_BM>
 __global__ void __launch_bounds__(NT_THREADS)
 sgemm_nt_kernel(const float* __restrict__ A, int lda, const float* __restrict__ B, int ldb, int M, int N, int K,
                 Epi epi) {
   constexpr int TN = BN / 16;
-  __shared__ __align__(16) float As[2][NT_BK][NT_BM + 4];
+  constexpr int TM = BM / 16;
+  static_assert(TM == 8 || TM == 2, "row tile");
+  __shared__ __align__(16) float As[2][NT_BK][BM + 4];
   __shared__ __align__(16) float Bs[2][NT_BK][BN + 4];
   const int tid = threadIdx.x;
-  const int m0 = blockIdx.y * NT_BM, n0 = blockIdx.x * BN;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
   const int lk = tid & 15;   // k within tile for loads
   const int lr = tid >> 4;   // 0..15 row (stride 16) for loads
   const int ty = tid >> 4, tx = tid & 15;
 
-  float ra[8], rb[TN];
-  float acc[8][TN];
+  float ra[TM], rb[TN];
+  float acc[TM][TN];
 #pragma unroll
-  for (int i = 0; i < 8; ++i)
+  for (int i = 0; i < TM; ++i)
 #pragma unroll
     for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
 
   auto gload = [&](int k0) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < TM; ++i) {
       int m = m0 + lr + 16 * i, k = k0 + lk;
       float v = (m < M && k < K) ? A[(int64_t)m * lda + k] : 0.f;
       ra[i] = AMODE == A_RELU ? fmaxf(v, 0.f) : (AMODE == A_SANITIZE ? sanitize_ctx(v) : v);
@@ -53,7 +57,7 @@ sgemm_nt_kernel(const float* __restrict__ A, int lda, const float* __restrict__ 
   };
   auto sstore = [&](int buf) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) As[buf][lk][lr + 16 * i] = ra[i];
+    for (int i = 0; i < TM; ++i) As[buf][lk][lr + 16 * i] = ra[i];
 #pragma unroll
     for (int i = 0; i < TN; ++i) Bs[buf][lk][lr + 16 * i] = rb[i];
   };
@@ -67,9 +71,16 @@ sgemm_nt_kernel(const float* __restrict__ A, int lda, const float* __restrict__ 
     if (kt + 1 < nk) gload((kt + 1) * NT_BK);
 #pragma unroll
     for (int k = 0; k < NT_BK; ++k) {
-      float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 8]);
-      float4 a1 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 8 + 4]);
-      const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      float av[TM];
+      if constexpr (TM == 8) {
+        float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 8]);
+        float4 a1 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 8 + 4]);
+        av[0] = a0.x; av[1] = a0.y; av[2] = a0.z; av[3] = a0.w;
+        av[4] = a1.x; av[5] = a1.y; av[6] = a1.z; av[7] = a1.w;
+      } else {
+        float2 a0 = *reinterpret_cast<const float2*>(&As[buf][k][ty * 2]);
+        av[0] = a0.x; av[1] = a0.y;
+      }
       float bv[TN];
       if (TN == 4) {
         float4 b = *reinterpret_cast<const float4*>(&Bs[buf][k][tx * 4]);
@@ -79,7 +90,7 @@ sgemm_nt_kernel(const float* __restrict__ A, int lda, const float* __restrict__ 
         bv[0] = b.x; bv[1] = b.y;
       }
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
+      for (int i = 0; i < TM; ++i)
 #pragma unroll
         for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
     }
@@ -89,8 +100,8 @@ sgemm_nt_kernel(const float* __restrict__ A, int lda, const float* __restrict__ 
     }
   }
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    int m = m0 + ty * 8 + i;
+  for (int i = 0; i < TM; ++i) {
+    int m = m0 + ty * TM + i;
     if (m >= M) continue;
 #pragma unroll
     for (int j = 0; j < TN; ++j) {
@@ -106,7 +117,12 @@ inline pf_status sgemm_nt(pf_flow* f, cudaStream_t st, const float* A, int lda, 
   static_assert(BN == 64 || BN == 32, "tile");
   if (M <= 0 || N <= 0) return PF_OK;
   dim3 grid((N + BN - 1) / BN, (M + NT_BM - 1) / NT_BM);
-  sgemm_nt_kernel<Epi, AMODE, BN><<<grid, NT_THREADS, 0, st>>>(A, lda, B, ldb, M, N, K, epi);
+  if ((int)(grid.x * grid.y) < 2 * f->sm_count) {   // too few 128-row tiles to fill the GPU: 32-row tiles
+    grid.y = (M + 31) / 32;
+    sgemm_nt_kernel<Epi, AMODE, BN, 32><<<grid, NT_THREADS, 0, st>>>(A, lda, B, ldb, M, N, K, epi);
+  } else {
+    sgemm_nt_kernel<Epi, AMODE, BN><<<grid, NT_THREADS, 0, st>>>(A, lda, B, ldb, M, N, K, epi);
+  }
   PF_LAUNCH_CHECK(f);
   return PF_OK;
 }

@@ -191,9 +191,10 @@ def nsf_backward(saved: Tensor, ctx: Tensor, gz: Tensor, glogdet: Tensor, weight
     ctx, gz, glogdet = _f32c(ctx), _f32c(gz), _f32c(glogdet)
     R, E = _rows(gz, ctx, n_per_ctx)
     L = fh.shape[3]
-    gx = torch.zeros_like(gz)
-    gctx = torch.zeros_like(ctx)
-    gws = [torch.zeros(w.shape, dtype=torch.float32, device=gz.device) for w in weights]
+    gx = torch.empty_like(gz)
+    gctx = torch.empty_like(ctx)
+    gws = [torch.empty(w.shape, dtype=torch.float32, device=gz.device) for w in weights]
+    torch._foreach_zero_([gx, gctx] + gws)   # the wgrad kernels accumulate with atomics: one multi-tensor fill
     arr = (A.LayerGrads * L)()
     for l in range(L):
         g = gws[l * NW:(l + 1) * NW]

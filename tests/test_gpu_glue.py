@@ -198,3 +198,38 @@ def test_philox_noise_is_standard_normal_and_reproducible():
         z, _ = flow.forward(y, ctx, n_per_ctx=4096)
     assert abs(float(z.mean())) < 0.02 and abs(float(z.std()) - 1.0) < 0.02
     assert abs(float((z ** 4).mean()) - 3.0) < 0.2
+
+
+def test_batch_nll_fused_matches_loop_and_oracle():
+    """N1: one flow call for all signal ranks == the reference's per-rank loop (train_lean_npe.py:108-127)."""
+    import posteriflow_b200 as P
+    from posteriflow_b200.train import batch_nll_reference_order
+    spec, w, g = load_golden("lean_glue")
+    m = lean_model(w, g)
+    gen = torch.Generator().manual_seed(11)
+    B = 48
+    nsig = torch.multinomial(torch.tensor([.55, .20, .12, .08, .05]), B, replacement=True, generator=gen) + 1
+    sc = O.Scaler()
+    params = sc.denormalize(torch.rand(B, 5, 11, generator=gen) * 2 - 1)
+    ctx = torch.randn(B, 256, generator=gen)
+    c1 = ctx.cuda().requires_grad_(True)
+    fused = P.batch_nll(m, None, params.cuda(), nsig.cuda(), context=c1)
+    l0 = m.flow.gpu_launches
+    fused.backward()
+    c2 = ctx.cuda().requires_grad_(True)
+    loop = batch_nll_reference_order(m, None, params.cuda(), nsig.cuda(), context=c2)
+    loop.backward()
+    assert m.flow.gpu_launches > l0
+    # oracle: the reference loop on the CPU
+    tot, cnt = 0.0, 0
+    with torch.no_grad():
+        for r in range(int(nsig.max())):
+            idx = (nsig > r).nonzero(as_tuple=True)[0]
+            fc = O.full_context(ctx[idx], t(g["rank_embed"]), torch.full((idx.numel(),), r, dtype=torch.long))
+            tot += float(O.flow_nll(spec, w, sc.normalize(params[idx, r, :]), fc).double().sum())
+            cnt += idx.numel()
+    ref = tot / cnt
+    assert abs(float(fused) - ref) <= 1e-4 * max(1.0, abs(ref)), (float(fused), ref)
+    assert abs(float(loop) - ref) <= 1e-4 * max(1.0, abs(ref))
+    scale = float(c2.grad.abs().max())
+    assert float((c1.grad - c2.grad).abs().max()) <= 1e-4 * scale
