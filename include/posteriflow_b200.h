@@ -204,6 +204,21 @@ pf_status pf_flow_backward(pf_flow* flow, const void* saved, const float* ctx, c
 pf_status pf_physical_logq(const float* y, const float* nll, const pf_scaler* scaler, int32_t D, int64_t R,
                            float* theta, float* logq, uint32_t flags, int32_t device, void* stream);
 
+/* ---- on-device posterior summaries ----------------------------------------------------------- */
+
+/* Replaces the host-side numpy summaries the reference computes after pulling every sample off the device
+ * (scripts/overlap_benchmark.py:67-89 calib_block, scripts/validate_checkpoint.py:102-128,
+ * experiments/train_lean_npe.py:160-167), per event e and dimension j over the n samples theta[e, :, j]:
+ *   quant[e, i, j]      = np.quantile(theta[e, :, j], q[i])          ('linear' method = torch.quantile), i < Q <= 8
+ *   lower_median[e, j]  = torch.median(theta[e, :, j]).values        (lower of the two middle elements)
+ *   below[e, j]         = (theta[e, :, j] < truth[e, j]).mean()      (the SBC rank statistic; needs truth [E, D])
+ *   rail_frac[e]        = railed[e*n : (e+1)*n].mean()               (pipeline.py:188, validate_checkpoint.py:126)
+ * theta [E, n, D] float32 as pf_sample_fused writes it; q is a HOST array; every output may be NULL.
+ * Order statistics are exact (radix select on the float keys), the interpolation is numpy's _lerp in double. */
+pf_status pf_posterior_summary(const float* theta, int64_t E, int64_t n, int32_t D, const double* q /* [host] Q */,
+                               int32_t Q, const float* truth, const uint8_t* railed, float* quant,
+                               float* lower_median, float* below, float* rail_frac, int32_t device, void* stream);
+
 /* ---- sizes / diagnostics -------------------------------------------------------------------- */
 
 size_t pf_flow_workspace_bytes(const pf_flow* flow, int32_t op, int64_t R, int64_t E);

@@ -24,7 +24,7 @@ EXPORTS = [
     "pf_flow_create", "pf_flow_destroy", "pf_flow_pack", "pf_flow_ctxproj", "pf_flow_inverse",
     "pf_sample_fused", "pf_flow_forward", "pf_flow_backward", "pf_flow_workspace_bytes",
     "pf_flow_saved_bytes", "pf_flow_last_launch_count", "pf_flow_hidden_perm", "pf_status_str",
-    "pf_last_cuda_error", "pf_abi_version", "pf_physical_logq",
+    "pf_last_cuda_error", "pf_abi_version", "pf_physical_logq", "pf_posterior_summary",
 ]
 
 _fp = C.c_void_p  # every device pointer is passed as an integer address
@@ -90,6 +90,9 @@ def load_library() -> C.CDLL:
     lib.pf_flow_backward.restype = i32
     lib.pf_physical_logq.argtypes = [_fp, _fp, C.POINTER(Scaler), i32, i64, _fp, _fp, u32, i32, _fp]
     lib.pf_physical_logq.restype = i32
+    lib.pf_posterior_summary.argtypes = [_fp, i64, i64, i32, C.POINTER(C.c_double), i32, _fp, _fp, _fp, _fp, _fp, _fp,
+                                         i32, _fp]
+    lib.pf_posterior_summary.restype = i32
     lib.pf_flow_workspace_bytes.argtypes = [C.c_void_p, i32, i64, i64]
     lib.pf_flow_workspace_bytes.restype = sz
     lib.pf_flow_saved_bytes.argtypes = [C.c_void_p, i64, i64]

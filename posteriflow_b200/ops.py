@@ -352,3 +352,43 @@ def nsf_physical(y: Tensor, nll: Tensor, sort_masses: bool, lo: Tensor, hi: Tens
 @nsf_physical.register_fake
 def _(y, nll, sort_masses, lo, hi, log_mask, circ_mask):
     return torch.empty_like(y), y.new_empty(y.shape[0])
+
+
+@torch.library.custom_op("posteriflow::posterior_summary", mutates_args=())
+def posterior_summary_op(theta: Tensor, q: Sequence[float], truth: Optional[Tensor], railed: Optional[Tensor]
+                         ) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """Per-event summaries of theta [E, n, D] on the device (overlap_benchmark.py:67-89, validate_checkpoint.py:102-128):
+    (quantiles [E, Q, D], lower median [E, D], fraction of samples below truth [E, D], railing fraction [E])."""
+    _require_cuda(theta, truth, railed)
+    theta = _f32c(theta)
+    if theta.dim() != 3:
+        raise ValueError("theta must be [E, n, D]")
+    E, n, D = theta.shape
+    Q = len(q)
+    dev = theta.device
+    quant = torch.empty(E, Q, D, dtype=torch.float32, device=dev)
+    lower = torch.empty(E, D, dtype=torch.float32, device=dev)
+    below = torch.zeros(E, D, dtype=torch.float32, device=dev)
+    rail = torch.zeros(E, dtype=torch.float32, device=dev)
+    tr = _f32c(truth) if truth is not None else None
+    rl = railed.to(torch.uint8).contiguous() if railed is not None else None
+    if tr is not None and tuple(tr.shape) != (E, D):
+        raise ValueError(f"truth must be [{E}, {D}]")
+    if rl is not None and rl.numel() != E * n:
+        raise ValueError(f"railed must have {E * n} entries")
+    lib = A.load_library()
+    qa = (C.c_double * max(Q, 1))(*[float(v) for v in q])
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    with torch.cuda.device(idx):
+        A.check(lib.pf_posterior_summary(theta.data_ptr(), E, n, D, qa, Q, _ptr(tr), _ptr(rl),
+                                         quant.data_ptr() if Q else None, lower.data_ptr(),
+                                         below.data_ptr() if tr is not None else None,
+                                         rail.data_ptr() if rl is not None else None, idx, _stream()),
+                "pf_posterior_summary")
+    return quant, lower, below, rail
+
+
+@posterior_summary_op.register_fake
+def _(theta, q, truth, railed):
+    E, n, D = theta.shape
+    return theta.new_empty(E, len(q), D), theta.new_empty(E, D), theta.new_empty(E, D), theta.new_empty(E)
