@@ -101,6 +101,7 @@ struct pf_flow {
   // bf16 tensor-core tier (pf_tc.cu): opaque state (weight image + padded side arrays), built by pf_flow_pack
   void* tc;              // NULL when tier != PF_TIER_BF16
   int UF;                // padded per-dim parameter count (MULT rounded up to 4)
+  void* dense;           // dense density-direction kernel state (pf_tc_dense.cu), NULL when the shape is not covered
 };
 
 // bf16 tensor-core tier entry points (pf_tc.cu)
@@ -115,3 +116,10 @@ pf_status pf_tc_forward(pf_flow* f, cudaStream_t st, const float* x, const float
 pf_status pf_tc_ctxproj(pf_flow* f, cudaStream_t st, const float* ctx, int64_t E, uint32_t flags, float* proj);
 size_t pf_tc_workspace_bytes(const pf_flow* f, int64_t R, int64_t E);
 void pf_tc_destroy(pf_flow* f);
+// dense tcgen05 density direction (pf_tc_dense.cu): H = 256, 16 bins, D <= 11
+bool pf_dn_supported(const pf_flow* f);
+pf_status pf_dn_pack(pf_flow* f, cudaStream_t st);
+void pf_dn_destroy(pf_flow* f);
+pf_status pf_dn_forward(pf_flow* f, cudaStream_t st, const float* x, const float* ctx, const int64_t* row2ctx,
+                        int64_t n_per_ctx, int64_t R, int64_t E, float* z, float* logdet, uint32_t flags,
+                        void* workspace, size_t workspace_bytes, int* err);

@@ -134,6 +134,7 @@ extern "C" pf_status pf_flow_create(const pf_flow_desc* d, pf_flow** out) {
 extern "C" void pf_flow_destroy(pf_flow* f) {
   if (!f) return;
   pf_tc_destroy(f);
+  pf_dn_destroy(f);
   if (f->arena) cudaFree(f->arena);
   if (f->d_perm) cudaFree(f->d_perm);
   if (f->d_flag) cudaFree(f->d_flag);
@@ -196,6 +197,7 @@ extern "C" pf_status pf_flow_pack(pf_flow* f, const pf_layer_ptrs* layers, void*
 
   }
   PF_TRY(pf_tc_pack(f, st));
+  PF_TRY(pf_dn_pack(f, st));
   int flag = 0;
   PF_CUDA(cudaMemcpyAsync(&flag, f->d_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
   PF_CUDA(cudaStreamSynchronize(st));

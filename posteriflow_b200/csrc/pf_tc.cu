@@ -1099,6 +1099,24 @@ pf_status pf_tc_forward(pf_flow* f, cudaStream_t st, const float* x, const float
                         void* workspace, size_t workspace_bytes) {
   if (!x || !z) return PF_ERR_INVALID;
   const uint32_t fl = flags & (PF_FLAG_SANITIZE_CTX | PF_FLAG_CTX_IS_PROJ);
+  // dense per-layer schedule (pf_tc_dense.cu) when the shape is covered; a pre-projected context is in this tier's
+  // padded layout and stays with the stepwise kernel.  PF_TC_DENSE=0 forces the stepwise kernel (A/B, tests).
+  TcState* t = reinterpret_cast<TcState*>(f->tc);
+  const char* dn = getenv("PF_TC_DENSE");
+  if (f->dense && t && !(fl & PF_FLAG_CTX_IS_PROJ) && !(dn && dn[0] == '0')) {
+    PF_TRY(pf_dn_forward(f, st, x, ctx, row2ctx, n_per_ctx, R, E, z, logdet, fl, workspace, workspace_bytes, t->err));
+    if (t->debug_sync) {
+      int herr = 0;
+      PF_CUDA(cudaStreamSynchronize(st));
+      PF_CUDA(cudaMemcpy(&herr, t->err, sizeof(int), cudaMemcpyDeviceToHost));
+      if (herr) {
+        snprintf(g_cuda_err, sizeof(g_cuda_err), "dense density kernel: barrier timeout, code %d", herr);
+        cudaMemset(t->err, 0, sizeof(int));
+        return PF_ERR_CUDA;
+      }
+    }
+    return PF_OK;
+  }
   return tc_run(f, st, false, x, 0, ctx, row2ctx, n_per_ctx, R, E, z, logdet, nullptr, fl, nullptr, workspace,
                 workspace_bytes);
 }

@@ -1,0 +1,656 @@
+// Tensor-core tier, density direction (x -> z, NSFPosteriorFlow.forward, flows.py:610-618; the flow part of
+// compute_psd_aware_nll, flows.py:727-779) as DENSE per-layer GEMMs: with x known, a MADE layer is one pass
+//   h0 = W0 x + b0 + relu(c0);  2 x [ u = Wa relu(h) + ba ; h += gate * (Wb relu(u) + bb) ];  p = Wf h + bf
+// so each 128-row tile needs 6 MMA stages of N = 256 / 240 per layer (60 per tile) instead of the 660 skinny
+// N = 32 stages of the stepwise schedule the sampling direction is forced into (pf_tc.cu).
+//
+// One persistent CTA per SM, tile = 128 flow rows = TMEM lanes = UMMA M.  320 threads:
+//   warps 0-7  row warps, two threads per flow row (thread pair = column halves / dimension halves)
+//   warp 8     MMA issuer (converged warp, one elected lane), owns the TMEM allocation
+//   warp 9     weight loader: streams the layer's bf16 blobs (UMMA canonical K-major layout, 786 KB per layer,
+//              L2-resident) through a 6 x 16 KB shared-memory ring with cp.async.bulk + mbarrier complete_tx
+// Tensor memory: cols [0,256) stage accumulator, [256,512) the fp32 residual stream h (tcgen05.ld/st by the row
+// warps); for the final layer the accumulator is [0,240) params of dims 1..5 | [240,480) dims 6..10 (dim 0 has no
+// hidden input under the autoregressive mask: bias only).  Shared memory: the bf16 A operand [128 x 256] in UMMA
+// layout (written by the epilogues), the x tile (bf16 hi + lo halves, K = 32), the ring, per-layer constants.
+#include <stdlib.h>
+
+#include "pf_common.cuh"
+#include "pf_sm100.cuh"
+#include "pf_spline.cuh"
+#include "pf_tail.cuh"
+
+namespace pf {
+using namespace pf::sm100;
+
+constexpr int DN_ROWS = 128;
+constexpr int DN_THREADS = 320;
+constexpr int DN_NSLOT = 6;
+constexpr int DN_SLOT = 16384;
+constexpr int DN_H = 256;
+constexpr int DN_NB = 16;
+constexpr int DN_MULT = 3 * DN_NB - 1;   // 47
+constexpr int DN_HACC = 0, DN_HRES = 256;
+
+struct DnShape {
+  int D, L, PLD, DP;
+  int ga, gb;        // dims 1..ga in final-layer group A, ga+1..ga+gb in group B (dim 0: bias only)
+  int NA, NBn;       // UMMA N of the two groups (multiples of 16, <= 256)
+  uint32_t layer_bytes;
+};
+
+struct DnState {
+  DnShape s;
+  uint8_t* image;
+  int smem;
+  long long* prof;
+};
+
+struct DnArgs {
+  DnShape s;
+  const uint8_t* image;
+  const float *b0, *ba, *bb, *bf;   // fp32 packed biases of the handle ([L][H], [L][2][H], [L][2][H], [L][PLD])
+  const float* proj;                // [ctx rows][L*3*H]  relu(c0) | sigmoid gate 1 | sigmoid gate 2
+  int64_t ldproj;
+  CtxMap cm;
+  const float* x;                   // [R, D]
+  int64_t R;
+  int n_tiles;
+  float* z; float* logdet;
+  float tail;
+  int* err;
+  long long* prof;                  // NULL, or 8 cycle counters filled by CTA 0 (PF_TC_PROF=1)
+};
+
+// bf16 weight image of one layer, chunk after chunk (one chunk = [N x 16] in UMMA K-major no-swizzle layout):
+// I (2 chunks, N=256: W0 for the hi half of x, W0 again for the lo half) | A1 B1 A2 B2 (16 chunks each, N=256) |
+// FA (16 chunks, N=NA) | FB (16 chunks, N=NB)
+__global__ void dn_pack_kernel(DnShape s, uint8_t* __restrict__ image, const float* __restrict__ W0,
+                               const float* __restrict__ Wa, const float* __restrict__ Wb,
+                               const float* __restrict__ Wf) {
+  const int l = blockIdx.y;
+  const int c = blockIdx.x;   // chunk index within the layer: 0..1 I, 2..65 hidden, 66..81 FA, 82..97 FB
+  int stage, cc, N;
+  uint32_t off;
+  if (c < 2) { stage = 0; cc = c; N = 256; off = (uint32_t)c * 8192u; }
+  else if (c < 66) { stage = 1 + (c - 2) / 16; cc = (c - 2) % 16; N = 256; off = (uint32_t)c * 8192u; }
+  else if (c < 82) { stage = 5; cc = c - 66; N = s.NA; off = 66u * 8192u + (uint32_t)cc * (uint32_t)s.NA * 32u; }
+  else { stage = 6; cc = c - 82; N = s.NBn; off = 66u * 8192u + 16u * (uint32_t)s.NA * 32u + (uint32_t)cc * (uint32_t)s.NBn * 32u; }
+  __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(image + (size_t)l * s.layer_bytes + off);
+  const int H = DN_H;
+  for (int e = threadIdx.x; e < N * 16; e += blockDim.x) {
+    const int n = e / 16, kk = e % 16;
+    float v = 0.f;
+    if (stage == 0) {
+      if (kk < s.D) v = W0[((size_t)l * H + n) * s.DP + kk];
+    } else if (stage <= 4) {
+      const int blk = (stage - 1) / 2;
+      const float* W = ((stage - 1) & 1) ? Wb : Wa;
+      v = W[(((size_t)l * 2 + blk) * H + n) * H + cc * 16 + kk];
+    } else {
+      const int first = stage == 5 ? 1 : 1 + s.ga, cnt = stage == 5 ? s.ga : s.gb;
+      if (n < cnt * DN_MULT) v = Wf[((size_t)l * s.PLD + (size_t)first * DN_MULT + n) * H + cc * 16 + kk];
+    }
+    dst[(kk / 8) * (N * 8) + (n / 8) * 64 + (n % 8) * 8 + (kk % 8)] = __float2bfloat16(v);
+  }
+}
+
+__device__ __forceinline__ float dn_finite(float v) { return fminf(fmaxf(v, -3.0e38f), 3.0e38f); }   // NaN -> -3e38
+__device__ __forceinline__ float dn_relu(float v) { return fminf(fmaxf(v, 0.f), 3.0e38f); }          // NaN -> 0
+
+// Forward rational-quadratic spline of one (row, dim) from its 3*NB-1 unnormalised parameters (Appendix A.5-A.7,
+// nflows unconstrained_rational_quadratic_spline with linear tails), hardware ex2 / lg2 / rcp.
+__device__ __forceinline__ float dn_rqs_forward(float* q, float x, float B, float& lad) {
+  constexpr int NB = DN_NB;
+  if (!(x >= -B && x <= B)) { lad = 0.f; return x; }
+  float mw = q[0], mh = q[NB];
+#pragma unroll
+  for (int i = 1; i < NB; ++i) { mw = fmaxf(mw, q[i]); mh = fmaxf(mh, q[NB + i]); }
+  float sw = 0.f, sh = 0.f;
+#pragma unroll
+  for (int i = 0; i < NB; ++i) {
+    q[i] = fx_ex2((q[i] - mw) * 1.4426950408889634f);
+    q[NB + i] = fx_ex2((q[NB + i] - mh) * 1.4426950408889634f);
+    sw += q[i]; sh += q[NB + i];
+  }
+  const float cwn = (2.f * B) * (1.f - kMinBin * NB) * fx_rcp(sw);
+  const float chn = (2.f * B) * (1.f - kMinBin * NB) * fx_rcp(sh);
+  const float base = (2.f * B) * kMinBin;
+  int k = 0;
+  float xk = -B, wk = 0.f, px = -B, cx = 0.f;
+#pragma unroll
+  for (int i = 0; i < NB; ++i) {
+    cx += fmaf(cwn, q[i], base);
+    const float nx = (i == NB - 1) ? B : cx - B;
+    if (i == 0 || x >= px) { k = i; xk = px; wk = nx - px; }
+    px = nx;
+  }
+  float yk = -B, hk = 0.f, py = -B, cy = 0.f;
+#pragma unroll
+  for (int i = 0; i < NB; ++i) {
+    cy += fmaf(chn, q[NB + i], base);
+    const float ny = (i == NB - 1) ? B : cy - B;
+    if (i == k) { yk = py; hk = ny - py; }
+    py = ny;
+  }
+  float u0 = kEdgeLogit, u1 = kEdgeLogit;
+#pragma unroll
+  for (int i = 0; i < NB - 1; ++i) {
+    const float u = q[2 * NB + i];
+    if (i + 1 == k) u0 = u;
+    if (i == k) u1 = u;
+  }
+  const float dk = kMinDeriv + (u0 > 20.f ? u0 : fx_log(1.f + fx_exp(u0)));
+  const float dk1 = kMinDeriv + (u1 > 20.f ? u1 : fx_log(1.f + fx_exp(u1)));
+  const float rw = fx_rcp(wk);
+  const float sl = hk * rw;
+  const float th = (x - xk) * rw;
+  const float omt = 1.f - th;
+  const float tt = th * omt;
+  const float den = fmaf(dk + dk1 - 2.f * sl, tt, sl);
+  const float rden = fx_rcp(den);
+  const float dnum = sl * sl * (dk1 * th * th + 2.f * sl * tt + dk * omt * omt);
+  lad = fx_log(dnum * rden * rden);
+  return fmaf(hk * (sl * th * th + dk * tt), rden, yk);
+}
+
+// shared-memory carve (bytes)
+constexpr int DN_OFF_ACT = 0;                          // [128 x 256] bf16, UMMA layout
+constexpr int DN_OFF_XT = 65536;                       // [128 x 32] bf16 (x hi | x lo), UMMA layout
+constexpr int DN_OFF_RING = DN_OFF_XT + 8192;
+constexpr int DN_OFF_CST = DN_OFF_RING + DN_NSLOT * DN_SLOT;
+constexpr int DN_CST_BIAS = 0;                         // floats: b0 | ba0 | bb0 | ba1 | bb1
+constexpr int DN_CST_BF = 5 * DN_H;                    // [16 dims][48]
+constexpr int DN_CST_CTX = DN_CST_BF + 16 * 48;        // [2 events][3][256]
+constexpr int DN_CST_FLOATS = DN_CST_CTX + 2 * 3 * DN_H;
+constexpr int DN_OFF_Y = DN_OFF_CST + DN_CST_FLOATS * 4;     // [2][128][12] fp32 layer inputs / outputs
+constexpr int DN_OFF_RED = DN_OFF_Y + 2 * DN_ROWS * 12 * 4;  // [128] logdet partial of half 1, [2][128] bad flags
+constexpr int DN_OFF_BAR = DN_OFF_RED + 3 * DN_ROWS * 4;
+constexpr int DN_SMEM = DN_OFF_BAR + 256;
+
+__global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const DnArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const DnShape& s = a.s;
+  const int D = s.D;
+  uint8_t* sACT = smem + DN_OFF_ACT;
+  uint8_t* sXT = smem + DN_OFF_XT;
+  uint8_t* ring = smem + DN_OFF_RING;
+  float* cst = reinterpret_cast<float*>(smem + DN_OFF_CST);
+  float* ybuf = reinterpret_cast<float*>(smem + DN_OFF_Y);
+  float* red = reinterpret_cast<float*>(smem + DN_OFF_RED);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + DN_OFF_BAR);
+  uint64_t* full = bars;                     // [NSLOT]
+  uint64_t* empty = bars + DN_NSLOT;         // [NSLOT]
+  uint64_t* acc_bar = bars + 2 * DN_NSLOT;   // accumulator of the current stage complete
+  uint64_t* accb_bar = acc_bar + 1;          // second final-layer group complete
+  uint64_t* op_bar = acc_bar + 2;            // operands of the next stage written (8 warp arrivals)
+  volatile int* abort_s = reinterpret_cast<volatile int*>(acc_bar + 3);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 4);
+
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  if (tid == 0) {
+    for (int i = 0; i < DN_NSLOT; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(acc_bar, 1);
+    mbar_init(accb_bar, 1);
+    mbar_init(op_bar, 8);
+    *abort_s = 0;
+    fence_mbar_init();
+  }
+  if (warp == 8) tmem_alloc(tmem_slot, 512);
+  for (int i = tid; i < (65536 + 8192) / 16; i += DN_THREADS) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  auto wait = [&](uint64_t* bar, uint32_t parity, int code) -> bool {
+    for (uint32_t i = 0; i < (1u << 22); ++i) {
+      if (mbar_try_wait(bar, parity)) return true;
+      if ((i & 255) == 255 && *abort_s) return false;
+    }
+    *abort_s = 1;
+    atomicExch(a.err, code);
+    return false;
+  };
+
+  if (warp < 8) {
+    // ============================ row warps ============================
+    const int half = warp >> 2, q4 = warp & 3;
+    const int r = q4 * 32 + lane;
+    const int rt = half * 128 + r;                              // index among the 256 row threads
+    const uint32_t tl = tmem + ((uint32_t)(q4 * 32) << 16);
+    const uint32_t rowoff = (uint32_t)(r / 8) * 128 + (uint32_t)(r % 8) * 16;
+    const int ch = half * 128;                                  // this thread's column half in the hidden stages
+    const int jfirst = half ? 1 + s.ga : 0;                     // this thread's dimensions in the spline stage
+    const int jcount = half ? s.gb : 1 + s.ga;
+    uint32_t acc_par = 0, accb_par = 0;
+    bool ok = true;
+    const bool prof = a.prof && blockIdx.x == 0 && tid == 0;
+    long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // 0 consts, 1 hidden wait, 2 hidden compute, 3 F wait, 4 spline, 5 total
+    long long tmark = clock64();
+    const long long t_begin = tmark;
+    auto mark = [&](int k) { if (prof) { const long long n = clock64(); pc[k] += n - tmark; tmark = n; } };
+    auto arrive_ops = [&]() {
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(op_bar);
+    };
+    // write one value of the next layer's x tile: column jn (bf16 hi) and 16 + jn (bf16 lo)
+    auto put_x = [&](int jn, float v) {
+      const float xc = dn_finite(v);
+      const __nv_bfloat16 hi = __float2bfloat16(xc);
+      const __nv_bfloat16 lo = __float2bfloat16(xc - __bfloat162float(hi));
+      *reinterpret_cast<__nv_bfloat16*>(sXT + (jn / 8) * 2048 + rowoff + (jn % 8) * 2) = hi;
+      *reinterpret_cast<__nv_bfloat16*>(sXT + (2 + jn / 8) * 2048 + rowoff + (jn % 8) * 2) = lo;
+    };
+    for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
+      const int64_t grow = (int64_t)tile * DN_ROWS + r;
+      const bool valid = grow < a.R;
+      const int64_t first_row = (int64_t)tile * DN_ROWS;
+      const int64_t last_row = first_row + DN_ROWS - 1 < a.R ? first_row + DN_ROWS - 1 : a.R - 1;
+      const bool ctx_staged = !a.cm.row2ctx && a.cm.n_per_ctx >= DN_ROWS;
+      const int64_t e0 = a.cm(first_row), e1 = a.cm(last_row);
+      const int64_t cidx = valid ? a.cm(grow) : e0;
+      const int esel = (ctx_staged && cidx != e0) ? 1 : 0;
+      const float* projr = a.proj + cidx * a.ldproj;
+      float* yin = ybuf + r * 12;
+      float* yout = ybuf + DN_ROWS * 12 + r * 12;
+      float ld_acc = 0.f;
+      bool bad = false;
+      if (half == 0) {
+        for (int j = 0; j < D; ++j) {
+          const float v = valid ? a.x[grow * D + j] : 0.f;
+          yin[j] = v;
+          put_x(D - 1 - j, v);
+        }
+      }
+      arrive_ops();                                             // x tile of layer 0
+      for (int l = 0; l < s.L && ok; ++l) {
+        // ---- this layer's constants -> shared memory (all 256 row threads) ----
+        bar_sync(1, 256);                                       // previous layer's readers are done
+        {
+          const float* srcs[5] = {a.b0 + (size_t)l * DN_H, a.ba + ((size_t)l * 2) * DN_H, a.bb + ((size_t)l * 2) * DN_H,
+                                  a.ba + ((size_t)l * 2 + 1) * DN_H, a.bb + ((size_t)l * 2 + 1) * DN_H};
+          float v[5], c[6];
+#pragma unroll
+          for (int i = 0; i < 5; ++i) v[i] = __ldg(srcs[i] + rt);
+          if (ctx_staged) {
+#pragma unroll
+            for (int i = 0; i < 6; ++i)
+              c[i] = __ldg(a.proj + (i < 3 ? e0 : e1) * a.ldproj + ((size_t)l * 3 + (i % 3)) * DN_H + rt);
+          }
+          float bfv[3];
+#pragma unroll
+          for (int i = 0; i < 3; ++i) {
+            const int e = rt + 256 * i, j = e / 48, k = e % 48;
+            bfv[i] = (j < D && k < DN_MULT) ? __ldg(a.bf + (size_t)l * s.PLD + j * DN_MULT + k) : 0.f;
+          }
+#pragma unroll
+          for (int i = 0; i < 5; ++i) cst[DN_CST_BIAS + i * DN_H + rt] = v[i];
+          if (ctx_staged) {
+#pragma unroll
+            for (int i = 0; i < 6; ++i) cst[DN_CST_CTX + i * DN_H + rt] = c[i];
+          }
+#pragma unroll
+          for (int i = 0; i < 3; ++i) cst[DN_CST_BF + rt + 256 * i] = bfv[i];
+        }
+        bar_sync(1, 256);
+        mark(0);
+        const float* cctx = cst + DN_CST_CTX + esel * 3 * DN_H;
+        const float* pl = projr + (size_t)l * 3 * DN_H;
+        // ---- five hidden stages: I, A1, B1, A2, B2 ----
+#pragma unroll 1
+        for (int st = 0; st < 5 && ok; ++st) {
+          if (!(ok = wait(acc_bar, acc_par, 10 + st))) break;
+          mark(1);
+          acc_par ^= 1;
+          tc_fence_after();
+          const bool res = (st == 0 || st == 2 || st == 4);          // stage writes the residual stream h
+          const float* bias = cst + DN_CST_BIAS + st * DN_H;          // b0 | ba0 | bb0 | ba1 | bb1
+          const int sec = st == 0 ? 0 : (st == 2 ? 1 : 2);            // context section used by this stage
+#pragma unroll 1
+          for (int b = 0; b < 4; ++b) {
+            const int c0 = ch + 32 * b;
+            uint32_t v[32];
+            float o[32];
+            tmem_ld32(tl + DN_HACC + c0, v);
+            if (res) {
+              float g[32];
+              if (ctx_staged) {
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {
+                  const float4 t4 = *reinterpret_cast<const float4*>(cctx + sec * DN_H + c0 + i);
+                  g[i] = t4.x; g[i + 1] = t4.y; g[i + 2] = t4.z; g[i + 3] = t4.w;
+                }
+              } else {
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {
+                  const float4 t4 = __ldg(reinterpret_cast<const float4*>(pl + sec * DN_H + c0 + i));
+                  g[i] = t4.x; g[i + 1] = t4.y; g[i + 2] = t4.z; g[i + 3] = t4.w;
+                }
+              }
+              if (st == 0) {
+                tmem_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(v[i]) + bias[c0 + i] + g[i];
+              } else {
+                uint32_t hr[32];
+                tmem_ld32(tl + DN_HRES + c0, hr);
+                tmem_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                  o[i] = fmaf(g[i], __uint_as_float(v[i]) + bias[c0 + i], __uint_as_float(hr[i]));
+              }
+              uint32_t ow[32];
+#pragma unroll
+              for (int i = 0; i < 32; ++i) ow[i] = __float_as_uint(o[i]);
+              tmem_st16(tl + DN_HRES + c0, ow);
+              tmem_st16(tl + DN_HRES + c0 + 16, ow + 16);
+            } else {
+              tmem_wait_ld();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(v[i]) + bias[c0 + i];
+            }
+            // next stage's A operand: relu (clamped finite) except after the last block, where the final layer
+            // takes h itself
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              uint4 w4;
+              if (st == 4) {
+                w4.x = pack_bf16(dn_finite(o[8 * i]), dn_finite(o[8 * i + 1]));
+                w4.y = pack_bf16(dn_finite(o[8 * i + 2]), dn_finite(o[8 * i + 3]));
+                w4.z = pack_bf16(dn_finite(o[8 * i + 4]), dn_finite(o[8 * i + 5]));
+                w4.w = pack_bf16(dn_finite(o[8 * i + 6]), dn_finite(o[8 * i + 7]));
+              } else {
+                w4.x = pack_bf16(dn_relu(o[8 * i]), dn_relu(o[8 * i + 1]));
+                w4.y = pack_bf16(dn_relu(o[8 * i + 2]), dn_relu(o[8 * i + 3]));
+                w4.z = pack_bf16(dn_relu(o[8 * i + 4]), dn_relu(o[8 * i + 5]));
+                w4.w = pack_bf16(dn_relu(o[8 * i + 6]), dn_relu(o[8 * i + 7]));
+              }
+              *reinterpret_cast<uint4*>(sACT + (size_t)(c0 / 8 + i) * 2048 + rowoff) = w4;
+            }
+          }
+          if (res) tmem_wait_st();
+          arrive_ops();
+          mark(2);
+        }
+        if (!ok) break;
+        // ---- final layer: 3*NB-1 spline parameters per dimension -> forward spline ----
+        if (!(ok = wait(acc_bar, acc_par, 16))) break;       // group A (dims 1..ga)
+        acc_par ^= 1;
+        if (half == 1) {                                       // group B (dims ga+1..): only half 1 reads it
+          if (!(ok = wait(accb_bar, accb_par, 17))) break;
+        }
+        tc_fence_after();
+        mark(3);
+        const float* bfc = cst + DN_CST_BF;
+#pragma unroll 1
+        for (int jj = 0; jj < jcount; ++jj) {
+          const int j = jfirst + jj;
+          float q[48];
+#pragma unroll
+          for (int i = 0; i < 48; i += 4) {
+            const float4 t4 = *reinterpret_cast<const float4*>(bfc + j * 48 + i);
+            q[i] = t4.x; q[i + 1] = t4.y; q[i + 2] = t4.z; q[i + 3] = t4.w;
+          }
+          if (j > 0) {
+            const int col = half ? s.NA + (j - 1 - s.ga) * DN_MULT : (j - 1) * DN_MULT;
+            uint32_t v[48];
+            tmem_ld16(tl + col, v);
+            tmem_ld16(tl + col + 16, v + 16);
+            tmem_ld16(tl + col + 32, v + 32);
+            tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < DN_MULT; ++i) q[i] += __uint_as_float(v[i]);
+          }
+          const float xin = yin[D - 1 - j];
+          bad = bad || !(fabsf(xin) <= 3.0e38f);
+          float lad;
+          const float y = dn_rqs_forward(q, xin, a.tail, lad);
+          ld_acc += lad;
+          yout[j] = y;
+          if (l + 1 < s.L) put_x(D - 1 - j, y);
+        }
+        if (half == 0) {                                       // keep the group-B barrier phase in step
+          if (!(ok = wait(accb_bar, accb_par, 18))) break;
+        }
+        accb_par ^= 1;
+        if (l + 1 < s.L) arrive_ops();                          // x tile of the next layer
+        mark(4);
+        float* tsw = yin; yin = yout; yout = tsw;
+      }
+      if (!ok) break;
+      // ---- z, logdet: combine the two halves of every row ----
+      if (half == 1) red[r] = ld_acc;
+      red[(1 + half) * DN_ROWS + r] = bad ? 1.f : 0.f;
+      bar_sync(2, 256);
+      if (valid) {
+        // a non-finite value that entered the conditioner turns the whole row into NaN, as the reference's does
+        const bool anybad = red[DN_ROWS + r] != 0.f || red[2 * DN_ROWS + r] != 0.f;
+        for (int jj = 0; jj < jcount; ++jj) {
+          const int j = jfirst + jj;
+          a.z[grow * D + j] = anybad ? __int_as_float(0x7fc00000) : yin[j];
+        }
+        if (half == 0 && a.logdet) a.logdet[grow] = anybad ? __int_as_float(0x7fc00000) : ld_acc + red[r];
+      }
+      bar_sync(2, 256);                                         // red / ybuf are reused by the next tile
+    }
+    if (prof) {
+      for (int i = 0; i < 5; ++i) a.prof[i] = pc[i];
+      a.prof[5] = clock64() - t_begin;
+    }
+  } else if (warp == 8) {
+    // ============================ MMA issuer ============================
+    uint32_t op_par = 0, slot = 0, full_par = 0;
+    const uint32_t idesc_h = umma_idesc_bf16(DN_ROWS, 256);
+    const uint32_t idesc_a = umma_idesc_bf16(DN_ROWS, s.NA), idesc_b = umma_idesc_bf16(DN_ROWS, s.NBn);
+    const uint32_t aX = smem_u32(sXT), aACT = smem_u32(sACT), aRing = smem_u32(ring);
+    bool ok = true;
+    for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
+      for (int l = 0; l < s.L && ok; ++l) {
+        for (int st = 0; st < 7 && ok; ++st) {               // I, A1, B1, A2, B2, FA, FB
+          const int N = st < 5 ? 256 : (st == 5 ? s.NA : s.NBn);
+          const int nch = st == 0 ? 2 : 16;
+          const uint32_t idesc = st < 5 ? idesc_h : (st == 5 ? idesc_a : idesc_b);
+          const uint32_t acc = tmem + (st == 6 ? (uint32_t)s.NA : 0u);
+          const uint32_t abase = st == 0 ? aX : aACT;
+          if (st != 6) {                                       // FB reads the same operand as FA
+            if (!(ok = wait(&full[slot], full_par, 30))) break;   // weights first: prefetched long ago
+            if (!(ok = wait(op_bar, op_par, 20 + st))) break;
+            op_par ^= 1;
+            tc_fence_after();
+          }
+          for (int c0 = 0; c0 < nch && ok; c0 += 2) {
+            if (!(ok = wait(&full[slot], full_par, 31))) break;
+            tc_fence_after();
+            const uint32_t bbase = aRing + slot * DN_SLOT;
+            if (elect_one_sync()) {
+              uint64_t bd = umma_smem_desc(bbase, N * 16, 128);
+              const uint64_t bstep = (uint64_t)((2u * (uint32_t)N * 16u) >> 4);
+              uint64_t ad = umma_smem_desc(abase + (uint32_t)c0 * 4096u, 2048, 128);
+              umma_ss(acc, ad, bd, idesc, c0 > 0 ? 1u : 0u);
+              ad += 256u; bd += bstep;
+              umma_ss(acc, ad, bd, idesc, 1u);
+              umma_commit(&empty[slot]);
+              if (c0 + 2 >= nch) umma_commit(st == 6 ? accb_bar : acc_bar);
+            }
+            __syncwarp();
+            if (++slot == DN_NSLOT) { slot = 0; full_par ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 9) {
+    // ============================ weight loader ============================
+    uint32_t slot = 0, empty_par = 1;   // a fresh barrier passes a wait on parity 1
+    bool ok = true;
+    for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
+      for (int l = 0; l < s.L && ok; ++l) {
+        const uint8_t* src = a.image + (size_t)l * s.layer_bytes;
+        for (int st = 0; st < 7 && ok; ++st) {
+          const int N = st < 5 ? 256 : (st == 5 ? s.NA : s.NBn);
+          const int nch = st == 0 ? 2 : 16;
+          const uint32_t bytes = 2u * (uint32_t)N * 32u;
+          for (int c0 = 0; c0 < nch; c0 += 2) {
+            if (!(ok = wait(&empty[slot], empty_par, 40))) break;
+            if (elect_one_sync()) {
+              mbar_arrive_expect_tx(&full[slot], bytes);
+              bulk_g2s(ring + (size_t)slot * DN_SLOT, src, bytes, &full[slot]);
+            }
+            __syncwarp();
+            src += bytes;
+            if (++slot == DN_NSLOT) { slot = 0; empty_par ^= 1; }
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc(tmem, 512);
+}
+
+}  // namespace pf
+using namespace pf;
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+#include "pf_gemm.cuh"
+
+namespace pf {
+// proj[e, n] = relu | sigmoid (acc + b[n]) in the handle's sorted hidden order (same as the FP32 tier's projection)
+struct EpiCtxProjDense {
+  float* out; int ld; const float* bias; int H;
+  __device__ __forceinline__ void operator()(int m, int n, float acc) const {
+    float v = acc + bias[n];
+    int sec = (n / H) % 3;
+    out[(int64_t)m * ld + n] = sec == 0 ? fmaxf(v, 0.f) : 1.f / (1.f + expf(-v));
+  }
+};
+}  // namespace pf
+
+static bool dn_plan(const pf_flow* f, DnShape& s) {
+  memset(&s, 0, sizeof(s));
+  if (f->H != DN_H || f->NB != DN_NB || f->D < 2 || f->D > 11 || f->desc.num_blocks != 2) return false;
+  s.D = f->D; s.L = f->L; s.PLD = f->PLD; s.DP = f->DP;
+  s.ga = (f->D - 1 + 1) / 2;
+  s.gb = f->D - 1 - s.ga;
+  s.NA = round_up(s.ga * DN_MULT, 16);
+  s.NBn = s.gb > 0 ? round_up(s.gb * DN_MULT, 16) : 16;
+  if (s.NA > 256 || s.NBn > 256 || s.NA + s.NBn > 512) return false;
+  s.layer_bytes = 66u * 8192u + 16u * 32u * (uint32_t)(s.NA + s.NBn);
+  return true;
+}
+
+bool pf_dn_supported(const pf_flow* f) {
+  DnShape s;
+  return f->desc.tier == PF_TIER_BF16 && dn_plan(f, s);
+}
+
+pf_status pf_dn_pack(pf_flow* f, cudaStream_t st) {
+  DnShape s;
+  if (f->desc.tier != PF_TIER_BF16 || !dn_plan(f, s)) return PF_OK;   // the stepwise kernel serves other shapes
+  DnState* t = reinterpret_cast<DnState*>(f->dense);
+  if (!t) {
+    t = new DnState();
+    memset(t, 0, sizeof(*t));
+    t->s = s;
+    t->smem = DN_SMEM;
+    cudaError_t e = cudaMalloc(&t->image, (size_t)s.L * s.layer_bytes);
+    if (e != cudaSuccess) {
+      delete t;
+      return cuda_fail(e, "dense density image allocation", __FILE__, __LINE__);
+    }
+    const char* pr = getenv("PF_TC_PROF");
+    if (pr && pr[0] == '1' && cudaMalloc(&t->prof, 8 * sizeof(long long)) != cudaSuccess) t->prof = nullptr;
+    f->dense = t;
+  }
+  dim3 grid(98, s.L);
+  dn_pack_kernel<<<grid, 256, 0, st>>>(s, t->image, f->W0, f->Wa, f->Wb, f->Wf);
+  PF_LAUNCH_CHECK(f);
+  return PF_OK;
+}
+
+void pf_dn_destroy(pf_flow* f) {
+  DnState* t = reinterpret_cast<DnState*>(f->dense);
+  if (!t) return;
+  cudaFree(t->image);
+  if (t->prof) cudaFree(t->prof);
+  delete t;
+  f->dense = nullptr;
+}
+
+// x [R, D] -> z [R, D], logdet [R].  `err` = device int for protocol timeouts (owned by the caller).
+pf_status pf_dn_forward(pf_flow* f, cudaStream_t st, const float* x, const float* ctx, const int64_t* row2ctx,
+                        int64_t n_per_ctx, int64_t R, int64_t E, float* z, float* logdet, uint32_t flags,
+                        void* workspace, size_t workspace_bytes, int* err) {
+  DnState* t = reinterpret_cast<DnState*>(f->dense);
+  if (!t) return PF_ERR_NOT_PACKED;
+  const DnShape& s = t->s;
+  const bool is_proj = flags & PF_FLAG_CTX_IS_PROJ;
+  const bool dense = !row2ctx && n_per_ctx == 1;
+  const int64_t ldproj = (int64_t)f->L * 3 * DN_H;
+  const int64_t chunk = dense ? (R < PF_ROW_CHUNK ? R : PF_ROW_CHUNK) : R;
+  const int64_t prow = is_proj ? 0 : (dense ? chunk : E);
+  if ((size_t)prow * ldproj * sizeof(float) > workspace_bytes || (prow && !workspace)) return PF_ERR_WORKSPACE;
+  float* wproj = reinterpret_cast<float*>(workspace);
+  auto project = [&](const float* c, int64_t rows) -> pf_status {
+    const int N = f->L * 3 * DN_H;
+    EpiCtxProjDense epi{wproj, N, f->bctx, DN_H};
+    if (flags & PF_FLAG_SANITIZE_CTX)
+      return sgemm_nt<EpiCtxProjDense, A_SANITIZE, 64>(f, st, c, f->C, f->Wctx, f->C, (int)rows, N, f->C, epi);
+    return sgemm_nt<EpiCtxProjDense, A_PLAIN, 64>(f, st, c, f->C, f->Wctx, f->C, (int)rows, N, f->C, epi);
+  };
+  const float* proj_all = nullptr;
+  if (is_proj) proj_all = ctx;
+  else if (!dense) {
+    PF_TRY(project(ctx, E));
+    proj_all = wproj;
+  }
+  static bool attr_done[64] = {};
+  const int dev = f->desc.device;
+  if (dev < 64 && !attr_done[dev]) {
+    PF_CUDA(cudaFuncSetAttribute(tc_dense_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, t->smem));
+    attr_done[dev] = true;
+  }
+  for (int64_t r0 = 0; r0 < R; r0 += chunk) {
+    const int64_t rows = (R - r0) < chunk ? (R - r0) : chunk;
+    DnArgs a;
+    memset(&a, 0, sizeof(a));
+    a.s = s;
+    a.image = t->image;
+    a.b0 = f->b0; a.ba = f->ba; a.bb = f->bb; a.bf = f->bf;
+    a.ldproj = ldproj;
+    if (proj_all) {
+      a.proj = proj_all;
+      a.cm = CtxMap{row2ctx, n_per_ctx, r0};
+    } else {
+      PF_TRY(project(ctx + r0 * f->C, rows));
+      a.proj = wproj;
+      a.cm = CtxMap{nullptr, 1, 0};
+    }
+    a.x = x + r0 * s.D;
+    a.R = rows;
+    a.n_tiles = (int)((rows + DN_ROWS - 1) / DN_ROWS);
+    a.z = z + r0 * s.D;
+    a.logdet = logdet ? logdet + r0 : nullptr;
+    a.tail = f->desc.tail_bound;
+    a.err = err;
+    a.prof = t->prof;
+    const int grid = a.n_tiles < f->sm_count ? a.n_tiles : f->sm_count;
+    tc_dense_forward_kernel<<<grid, DN_THREADS, t->smem, st>>>(a);
+    PF_LAUNCH_CHECK(f);
+  }
+  if (t->prof) {
+    long long h[8];
+    PF_CUDA(cudaStreamSynchronize(st));
+    PF_CUDA(cudaMemcpy(h, t->prof, sizeof(h), cudaMemcpyDeviceToHost));
+    fprintf(stderr, "[pf_dn prof] CTA0: total %lld cycles: constants %lld | hidden wait %lld compute %lld | final wait %lld "
+            "spline %lld\n", h[5], h[0], h[1], h[2], h[3], h[4]);
+  }
+  return PF_OK;
+}

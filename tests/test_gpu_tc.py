@@ -143,7 +143,9 @@ def test_tc_round_trip_inverse_then_forward(R):
         z2, ld2 = tc.forward(x, ctx, n_per_ctx=R)
     dz = (z2 - z).abs().flatten()
     dl = (ld + ld2).abs() / ld.abs().clamp_min(1.0)
-    assert float(dz.median()) <= 5e-3 and float(dl.median()) <= 2e-2, (float(dz.median()), float(dl.median()))
+    # the two directions run different schedules (stepwise sampler, dense density kernel): two independent bf16
+    # evaluations of the conditioner, each within that tier's 5e-3 median of float64 -> 1e-2 for the round trip
+    assert float(dz.median()) <= 1e-2 and float(dl.median()) <= 2e-2, (float(dz.median()), float(dl.median()))
 
 
 def test_tc_second_instantiated_shape_8x192x16():
