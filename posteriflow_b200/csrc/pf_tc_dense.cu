@@ -95,6 +95,12 @@ __global__ void dn_pack_kernel(DnShape s, uint8_t* __restrict__ image, const flo
   }
 }
 
+// two floats -> packed bf16x2 with relu fused into the conversion (lo in bits 0..15)
+__device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
+  uint32_t d;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
 __device__ __forceinline__ float dn_finite(float v) { return fminf(fmaxf(v, -3.0e38f), 3.0e38f); }   // NaN -> -3e38
 __device__ __forceinline__ float dn_relu(float v) { return fminf(fmaxf(v, 0.f), 3.0e38f); }          // NaN -> 0
 
@@ -161,8 +167,8 @@ constexpr int DN_OFF_RING = DN_OFF_XT + 8192;
 constexpr int DN_OFF_CST = DN_OFF_RING + DN_NSLOT * DN_SLOT;
 constexpr int DN_CST_BIAS = 0;                         // floats: b0 | ba0 | bb0 | ba1 | bb1
 constexpr int DN_CST_BF = 5 * DN_H;                    // [16 dims][48]
-constexpr int DN_CST_CTX = DN_CST_BF + 16 * 48;        // [2 events][3][256]
-constexpr int DN_CST_FLOATS = DN_CST_CTX + 2 * 3 * DN_H;
+constexpr int DN_CST_CTX = DN_CST_BF + 16 * 48;        // [2 events][5][256]: relu(c0)+b0 | g1 | g1*bb0 | g2 | g2*bb1
+constexpr int DN_CST_FLOATS = DN_CST_CTX + 2 * 5 * DN_H;
 constexpr int DN_OFF_Y = DN_OFF_CST + DN_CST_FLOATS * 4;     // [2][128][12] fp32 layer inputs / outputs
 constexpr int DN_OFF_RED = DN_OFF_Y + 2 * DN_ROWS * 12 * 4;  // [128] logdet partial of half 1, [2][128] bad flags
 constexpr int DN_OFF_BAR = DN_OFF_RED + 3 * DN_ROWS * 4;
@@ -290,16 +296,23 @@ __global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const D
           }
 #pragma unroll
           for (int i = 0; i < 5; ++i) cst[DN_CST_BIAS + i * DN_H + rt] = v[i];
-          if (ctx_staged) {
+          if (ctx_staged) {   // fold the biases into the event's context terms: one add / one fma per element later
 #pragma unroll
-            for (int i = 0; i < 6; ++i) cst[DN_CST_CTX + i * DN_H + rt] = c[i];
+            for (int ev = 0; ev < 2; ++ev) {
+              float* d = cst + DN_CST_CTX + ev * 5 * DN_H + rt;
+              d[0] = c[3 * ev] + v[0];
+              d[DN_H] = c[3 * ev + 1];
+              d[2 * DN_H] = c[3 * ev + 1] * v[2];
+              d[3 * DN_H] = c[3 * ev + 2];
+              d[4 * DN_H] = c[3 * ev + 2] * v[4];
+            }
           }
 #pragma unroll
           for (int i = 0; i < 3; ++i) cst[DN_CST_BF + rt + 256 * i] = bfv[i];
         }
         bar_sync(1, 256);
         mark(0);
-        const float* cctx = cst + DN_CST_CTX + esel * 3 * DN_H;
+        const float* cctx = cst + DN_CST_CTX + esel * 5 * DN_H;
         const float* pl = projr + (size_t)l * 3 * DN_H;
         // ---- five hidden stages: I, A1, B1, A2, B2 ----
 #pragma unroll 1
@@ -311,64 +324,86 @@ __global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const D
           const bool res = (st == 0 || st == 2 || st == 4);          // stage writes the residual stream h
           const float* bias = cst + DN_CST_BIAS + st * DN_H;          // b0 | ba0 | bb0 | ba1 | bb1
           const int sec = st == 0 ? 0 : (st == 2 ? 1 : 2);            // context section used by this stage
+          // staged: add = relu(c0)+b0 (stage I) or gate*bias (B stages), mul = gate
+          const float* cadd = cctx + (st == 0 ? 0 : (st == 2 ? 2 : 4)) * DN_H;
+          const float* cmul = cctx + (st == 2 ? 1 : 3) * DN_H;
 #pragma unroll 1
           for (int b = 0; b < 4; ++b) {
             const int c0 = ch + 32 * b;
             uint32_t v[32];
             float o[32];
             tmem_ld32(tl + DN_HACC + c0, v);
-            if (res) {
-              float g[32];
-              if (ctx_staged) {
+            if (!res) {                       // A stages: u = acc + ba
+              tmem_wait_ld();
 #pragma unroll
-                for (int i = 0; i < 32; i += 4) {
-                  const float4 t4 = *reinterpret_cast<const float4*>(cctx + sec * DN_H + c0 + i);
-                  g[i] = t4.x; g[i + 1] = t4.y; g[i + 2] = t4.z; g[i + 3] = t4.w;
-                }
-              } else {
-#pragma unroll
-                for (int i = 0; i < 32; i += 4) {
-                  const float4 t4 = __ldg(reinterpret_cast<const float4*>(pl + sec * DN_H + c0 + i));
-                  g[i] = t4.x; g[i + 1] = t4.y; g[i + 2] = t4.z; g[i + 3] = t4.w;
-                }
+              for (int i = 0; i < 32; i += 4) {
+                const float4 t4 = *reinterpret_cast<const float4*>(bias + c0 + i);
+                o[i] = __uint_as_float(v[i]) + t4.x; o[i + 1] = __uint_as_float(v[i + 1]) + t4.y;
+                o[i + 2] = __uint_as_float(v[i + 2]) + t4.z; o[i + 3] = __uint_as_float(v[i + 3]) + t4.w;
               }
-              if (st == 0) {
+            } else {
+              if (st == 0) {                  // h0 = acc + b0 + relu(c0)
                 tmem_wait_ld();
+                if (ctx_staged) {
 #pragma unroll
-                for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(v[i]) + bias[c0 + i] + g[i];
-              } else {
+                  for (int i = 0; i < 32; i += 4) {
+                    const float4 t4 = *reinterpret_cast<const float4*>(cadd + c0 + i);
+                    o[i] = __uint_as_float(v[i]) + t4.x; o[i + 1] = __uint_as_float(v[i + 1]) + t4.y;
+                    o[i + 2] = __uint_as_float(v[i + 2]) + t4.z; o[i + 3] = __uint_as_float(v[i + 3]) + t4.w;
+                  }
+                } else {
+#pragma unroll
+                  for (int i = 0; i < 32; i += 4) {
+                    const float4 t4 = *reinterpret_cast<const float4*>(bias + c0 + i);
+                    const float4 g4 = __ldg(reinterpret_cast<const float4*>(pl + c0 + i));
+                    o[i] = __uint_as_float(v[i]) + t4.x + g4.x; o[i + 1] = __uint_as_float(v[i + 1]) + t4.y + g4.y;
+                    o[i + 2] = __uint_as_float(v[i + 2]) + t4.z + g4.z; o[i + 3] = __uint_as_float(v[i + 3]) + t4.w + g4.w;
+                  }
+                }
+              } else {                        // h += gate * (acc + bb)
                 uint32_t hr[32];
                 tmem_ld32(tl + DN_HRES + c0, hr);
                 tmem_wait_ld();
+                if (ctx_staged) {
 #pragma unroll
-                for (int i = 0; i < 32; ++i)
-                  o[i] = fmaf(g[i], __uint_as_float(v[i]) + bias[c0 + i], __uint_as_float(hr[i]));
+                  for (int i = 0; i < 32; i += 4) {
+                    const float4 g4 = *reinterpret_cast<const float4*>(cmul + c0 + i);
+                    const float4 a4 = *reinterpret_cast<const float4*>(cadd + c0 + i);
+                    o[i] = fmaf(g4.x, __uint_as_float(v[i]), __uint_as_float(hr[i]) + a4.x);
+                    o[i + 1] = fmaf(g4.y, __uint_as_float(v[i + 1]), __uint_as_float(hr[i + 1]) + a4.y);
+                    o[i + 2] = fmaf(g4.z, __uint_as_float(v[i + 2]), __uint_as_float(hr[i + 2]) + a4.z);
+                    o[i + 3] = fmaf(g4.w, __uint_as_float(v[i + 3]), __uint_as_float(hr[i + 3]) + a4.w);
+                  }
+                } else {
+#pragma unroll
+                  for (int i = 0; i < 32; i += 4) {
+                    const float4 t4 = *reinterpret_cast<const float4*>(bias + c0 + i);
+                    const float4 g4 = __ldg(reinterpret_cast<const float4*>(pl + sec * DN_H + c0 + i));
+                    o[i] = fmaf(g4.x, __uint_as_float(v[i]) + t4.x, __uint_as_float(hr[i]));
+                    o[i + 1] = fmaf(g4.y, __uint_as_float(v[i + 1]) + t4.y, __uint_as_float(hr[i + 1]));
+                    o[i + 2] = fmaf(g4.z, __uint_as_float(v[i + 2]) + t4.z, __uint_as_float(hr[i + 2]));
+                    o[i + 3] = fmaf(g4.w, __uint_as_float(v[i + 3]) + t4.w, __uint_as_float(hr[i + 3]));
+                  }
+                }
               }
               uint32_t ow[32];
 #pragma unroll
               for (int i = 0; i < 32; ++i) ow[i] = __float_as_uint(o[i]);
               tmem_st16(tl + DN_HRES + c0, ow);
               tmem_st16(tl + DN_HRES + c0 + 16, ow + 16);
-            } else {
-              tmem_wait_ld();
-#pragma unroll
-              for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(v[i]) + bias[c0 + i];
             }
-            // next stage's A operand: relu (clamped finite) except after the last block, where the final layer
-            // takes h itself
+            // next stage's A operand: relu fused into the bf16 conversion, except after the last block, where the
+            // final layer takes h itself.  (Rows are independent in the MMA: a non-finite value stays in its row,
+            // which the `bad` flag turns into NaN as the reference does.)
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               uint4 w4;
               if (st == 4) {
-                w4.x = pack_bf16(dn_finite(o[8 * i]), dn_finite(o[8 * i + 1]));
-                w4.y = pack_bf16(dn_finite(o[8 * i + 2]), dn_finite(o[8 * i + 3]));
-                w4.z = pack_bf16(dn_finite(o[8 * i + 4]), dn_finite(o[8 * i + 5]));
-                w4.w = pack_bf16(dn_finite(o[8 * i + 6]), dn_finite(o[8 * i + 7]));
+                w4.x = pack_bf16(o[8 * i], o[8 * i + 1]); w4.y = pack_bf16(o[8 * i + 2], o[8 * i + 3]);
+                w4.z = pack_bf16(o[8 * i + 4], o[8 * i + 5]); w4.w = pack_bf16(o[8 * i + 6], o[8 * i + 7]);
               } else {
-                w4.x = pack_bf16(dn_relu(o[8 * i]), dn_relu(o[8 * i + 1]));
-                w4.y = pack_bf16(dn_relu(o[8 * i + 2]), dn_relu(o[8 * i + 3]));
-                w4.z = pack_bf16(dn_relu(o[8 * i + 4]), dn_relu(o[8 * i + 5]));
-                w4.w = pack_bf16(dn_relu(o[8 * i + 6]), dn_relu(o[8 * i + 7]));
+                w4.x = pack_bf16_relu(o[8 * i], o[8 * i + 1]); w4.y = pack_bf16_relu(o[8 * i + 2], o[8 * i + 3]);
+                w4.z = pack_bf16_relu(o[8 * i + 4], o[8 * i + 5]); w4.w = pack_bf16_relu(o[8 * i + 6], o[8 * i + 7]);
               }
               *reinterpret_cast<uint4*>(sACT + (size_t)(c0 / 8 + i) * 2048 + rowoff) = w4;
             }
