@@ -230,6 +230,27 @@ def run_ours(args):
     clocks = clk.summary()
     ms_e2e, _ = timed(step_e2e, args.steps, max(1, args.warmup // 2))
 
+    # log-prob (density direction) of the same shard, the fused infer() loop body (N2) and the on-device summaries (N3)
+    wrap_flags = A.PF_FLAG_SANITIZE_CTX | A.PF_FLAG_CLAMP | A.PF_FLAG_WRAP
+    with torch.no_grad():
+        y_norm = P.sample_fused(flow, scaler, ctx_full, n, z=None, seed=7, flags=wrap_flags)[0].reshape(R, D)
+        theta_dev, _, railed_dev = P.sample_fused(flow, scaler, ctx_full, n, z=None, seed=7)
+    truth_dev = theta_dev[:, 0, :].contiguous()
+
+    def step_logprob(i):
+        with torch.no_grad():
+            return flow.compute_psd_aware_nll(y_norm, ctx_full, None, n_per_ctx=n)
+
+    def step_infer(i):
+        return P.posterior_chunk(flow, scaler, ctx_full, n, z=None, seed=2000 + i)
+
+    def step_summary(i):
+        return P.posterior_summary(theta_dev, truth=truth_dev, railed=railed_dev)
+
+    ms_lp, launches_lp = timed(step_logprob, args.steps, args.warmup)
+    ms_inf, launches_inf = timed(step_infer, args.steps, args.warmup)
+    ms_sum, _ = timed(step_summary, args.steps, args.warmup)
+
     # NLL training step of the flow head (config #4 shard): forward + backward (+ gradient all-reduce)
     Bt = args.train_events
     nsig = torch.multinomial(torch.tensor([.55, .20, .12, .08, .05]), Bt, replacement=True, generator=g) + 1
@@ -237,7 +258,8 @@ def run_ours(args):
     rk = torch.cat([torch.arange(int(k)) for k in nsig])
     Rt = int(ev.numel())
     sc_cpu = P.ParamScaler()
-    theta_phys = sc_cpu.denormalize(torch.rand(Rt, D, generator=g) * 2 - 1).to(dev)
+    params_b = sc_cpu.denormalize(torch.rand(Bt, 5, D, generator=g) * 2 - 1).to(dev)   # [B, max_signals, 11] physical
+    nsig_dev = nsig.to(dev)
     tctx = torch.randn(Bt, 256, generator=g).to(dev).requires_grad_(True)
     ev, rk = ev.to(dev), rk.to(dev)
     params = [p for p in model.parameters() if p.requires_grad]
@@ -246,7 +268,7 @@ def run_ours(args):
         for p in params:
             p.grad = None
         tctx.grad = None
-        loss = model.nll(None, theta_phys, rk, context=tctx[ev]).sum() / Rt
+        loss = P.batch_nll(model, None, params_b, nsig_dev, context=tctx)   # N1: one flow call for all ranks
         loss.backward()
         if world > 1:
             allreduce_gradients(params)
@@ -268,7 +290,7 @@ def run_ours(args):
         "data": "synthetic (random-init weights, N(0,1) contexts standing in for encoder output, in-kernel Philox base noise)",
         "config": workload_config(world) if (E, n) == (EVENTS_PER_GPU, SAMPLES_PER_EVENT) else
         {"workload": f"{E} events x {n} samples per GPU (non-default)", "parallelism": f"events sharded over {world} GPU(s)"},
-        "tier": args.tier + (" (sampler: tcgen05 bf16 operands, fp32 accumulate + fp32 spline; training step: FP32 kernels)"
+        "tier": args.tier + (" (sampler + log-prob: tcgen05 bf16 operands, fp32 accumulate + fp32 spline; training step: FP32 kernels)"
                              if args.tier == "bf16" else ""),
         "e2e": {"value": R * world * args.steps / (ms_e2e * 1e-3), "unit": "samples/s",
                 "h2d_bytes_per_step": int(ctx_host.numel() * 4), "d2h_bytes_per_step": int(theta_host.numel() * 4),
@@ -281,10 +303,29 @@ def run_ours(args):
                      "flop_per_row": flop_row,
                      "note": "whole sampler step per GPU (dense single-pass conditioner FLOPs, SURVEY 8d); "
                              "hbm: %.1f GB/s of algorithmic output (49 B/row)" % (rows_s / world * 49 / 1e9)},
+        "log_prob": {"metric": "log_prob_rows_per_sec", "value": R * world * args.steps / (ms_lp * 1e-3), "unit": "rows/s",
+                     "ms_per_step": ms_lp / args.steps, "gpu_launches": int(launches_lp),
+                     "api": "NSFPosteriorFlow.compute_psd_aware_nll(y [R,11], context [E,288], n_per_ctx=n), no gradient",
+                     "roofline": {"bound": "tensor", "achieved": R * args.steps / (ms_lp * 1e-3) * flop_row / 1e12,
+                                  "peak": peak, "unit": "TFLOP/s",
+                                  "frac": R * args.steps / (ms_lp * 1e-3) * flop_row / 1e12 / peak,
+                                  "flop_per_row": flop_row}},
+        "infer_loop": {"metric": "samples_with_log_prob_per_sec", "value": R * world * args.steps / (ms_inf * 1e-3),
+                       "unit": "samples/s", "ms_per_step": ms_inf / args.steps, "gpu_launches": int(launches_inf),
+                       "api": "posteriflow_b200.posterior_chunk (pipeline.py:168-186 on the device: sampler -> wrap -> rail "
+                              "mask -> density -> physical log-prob -> m1>=m2)"},
+        "summary": {"metric": "posterior_summary_ms", "ms_per_step": ms_sum / args.steps,
+                    "api": "posteriflow_b200.posterior_summary(theta [E,n,11], truth, railed): 5 quantiles + medians + SBC "
+                           "ranks + railing fraction per event",
+                    "roofline": {"bound": "hbm", "achieved": R * D * 4 * args.steps / (ms_sum * 1e-3) / 1e9,
+                                 "peak": float(pk["hbm_gbs"]), "unit": "GB/s",
+                                 "frac": R * D * 4 * args.steps / (ms_sum * 1e-3) / 1e9 / float(pk["hbm_gbs"]),
+                                 "bytes_per_row": D * 4}},
         "train": {"metric": "nll_train_steps_per_sec", "value": args.steps / (ms_train * 1e-3), "unit": "steps/s",
                   "events_per_gpu": Bt, "flow_rows_per_gpu": Rt, "ms_per_step": ms_train / args.steps,
                   "gpu_launches": int(launches_train),
-                  "includes": "scaler.normalize, rank embedding, flow forward+backward (all weights, context), "
+                  "includes": "batch_nll (one flow call for all signal ranks): row gather, scaler.normalize, rank embedding, flow "
+                              "forward+backward (all weights, context), "
                               + ("NCCL gradient all-reduce" if world > 1 else "no all-reduce at 1 GPU")
                               + "; encoder and optimizer excluded (encoder stays reference PyTorch)",
                   "roofline": {"bound": "tensor", "achieved": ach_t, "peak": peak, "unit": "TFLOP/s",
