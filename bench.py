@@ -152,6 +152,14 @@ def workload_config(n_gpus):
                   "5.5 MB bf16 weight image is re-read from L2 by design"}
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE tc_sampler_kernel launch, from the `ncu --set full` capture
+# summarised in profiles/r01_tc_sampler_ncu_full.txt (taken at 148 events x 1280 samples = 189 440 rows per launch)
+NCU_SAMPLER_DRAM_BYTES = 10.40e6
+NCU_SAMPLER_TRAFFIC_NOTE = ("ncu capture at 189 440 rows/launch (profiles/r01_tc_sampler_ncu_full.txt): 10.4 MB read "
+                            "(5.5 MB bf16 weight image once + context projections), 0 B written back before kernel end; "
+                            "algorithmic 9.3 MB (49 B/row) -- tensor-bound kernel, HBM traffic is not the limiter")
+
+
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
@@ -299,7 +307,8 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                     "traffic": None, "peak_source": f"{pk_kind} bf16_tflops_sustained",
+                     "traffic": NCU_SAMPLER_DRAM_BYTES, "traffic_note": NCU_SAMPLER_TRAFFIC_NOTE,
+                     "peak_source": f"{pk_kind} bf16_tflops_sustained",
                      "flop_per_row": flop_row,
                      "note": "whole sampler step per GPU (dense single-pass conditioner FLOPs, SURVEY 8d); "
                              "hbm: %.1f GB/s of algorithmic output (49 B/row)" % (rows_s / world * 49 / 1e9)},
