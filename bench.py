@@ -272,7 +272,21 @@ def run_ours(args):
     ev, rk = ev.to(dev), rk.to(dev)
     params = [p for p in model.parameters() if p.requires_grad]
 
+    gstep = P.GraphedNLLStep(model, distributed=(world > 1))
+    flow_ids = {id(p) for p in gstep.flow_params}
+    other_params = [p for p in params if id(p) not in flow_ids]      # rank embedding
+
     def step_train(i):
+        """public training API: batch_nll forward + backward as one CUDA-graph replay (+ gradient all-reduce)"""
+        for p in params:
+            p.grad = None
+        tctx.grad = None
+        loss = gstep(params_b, nsig_dev, tctx)
+        if world > 1:
+            gstep.allreduce(extra_params=other_params)
+        return loss
+
+    def step_train_eager(i):
         for p in params:
             p.grad = None
         tctx.grad = None
@@ -282,7 +296,31 @@ def run_ours(args):
             allreduce_gradients(params)
         return loss
 
-    ms_train, launches_train = timed(step_train, args.steps, args.warmup)
+    ms_train, _ = timed(step_train, args.steps, args.warmup)
+    launches_train = gstep.last_launches * args.steps
+    ms_train_eager, _ = timed(step_train_eager, args.steps, args.warmup)
+
+    # config #4 un-sharded (4096 events on ONE GPU): reported at N = 1 only, next to the per-GPU shard above
+    full = None
+    if world == 1 and args.train_events_full > 0:
+        Bf = args.train_events_full
+        nsig_f = torch.multinomial(torch.tensor([.55, .20, .12, .08, .05]), Bf, replacement=True, generator=g) + 1
+        params_f = sc_cpu.denormalize(torch.rand(Bf, 5, D, generator=g) * 2 - 1).to(dev)
+        nsig_f_dev = nsig_f.to(dev)
+        fctx = torch.randn(Bf, 256, generator=g).to(dev).requires_grad_(True)
+
+        def step_train_full(i):
+            for p in params:
+                p.grad = None
+            fctx.grad = None
+            return gstep(params_f, nsig_f_dev, fctx)
+
+        ms_full, _ = timed(step_train_full, args.steps, args.warmup)
+        Rf = int(nsig_f.sum())
+        full = {"events": Bf, "flow_rows": Rf, "ms_per_step": ms_full / args.steps,
+                "steps_per_sec": args.steps / (ms_full * 1e-3), "gpu_launches": int(gstep.last_launches * args.steps),
+                "roofline_frac": 3 * (F_X + F_CTX) * Rf * args.steps / (ms_full * 1e-3) / 1e12 / float(peaks()[0]["bf16_tflops_sustained"]),
+                "kernels": "split-bf16 tcgen05 GEMMs (calls of >= 2048 rows)" if args.tier == "bf16" else "FP32-FMA GEMMs"}
 
     pk, pk_kind = peaks()
     rows_s = R * world * args.steps / (ms * 1e-3)
@@ -298,7 +336,7 @@ def run_ours(args):
         "data": "synthetic (random-init weights, N(0,1) contexts standing in for encoder output, in-kernel Philox base noise)",
         "config": workload_config(world) if (E, n) == (EVENTS_PER_GPU, SAMPLES_PER_EVENT) else
         {"workload": f"{E} events x {n} samples per GPU (non-default)", "parallelism": f"events sharded over {world} GPU(s)"},
-        "tier": args.tier + (" (sampler + log-prob: tcgen05 bf16 operands, fp32 accumulate + fp32 spline; training step: FP32 kernels)"
+        "tier": args.tier + (" (sampler + log-prob: tcgen05 bf16 operands, fp32 accumulate + fp32 spline; training step: FP32-FMA GEMMs below 2048 flow rows per call, split-bf16 tcgen05 GEMMs above)"
                              if args.tier == "bf16" else ""),
         "e2e": {"value": R * world * args.steps / (ms_e2e * 1e-3), "unit": "samples/s",
                 "h2d_bytes_per_step": int(ctx_host.numel() * 4), "d2h_bytes_per_step": int(theta_host.numel() * 4),
@@ -332,7 +370,11 @@ def run_ours(args):
                                  "bytes_per_row": D * 4}},
         "train": {"metric": "nll_train_steps_per_sec", "value": args.steps / (ms_train * 1e-3), "unit": "steps/s",
                   "events_per_gpu": Bt, "flow_rows_per_gpu": Rt, "ms_per_step": ms_train / args.steps,
-                  "gpu_launches": int(launches_train),
+                  "gpu_launches": int(launches_train), "ms_per_step_eager_autograd": ms_train_eager / args.steps,
+                  "full_batch_1gpu": full,
+                  "api": "posteriflow_b200.GraphedNLLStep (batch_nll forward + backward captured in one CUDA graph per "
+                         "row bucket; weight / bias / context gradients on a side stream; FP32-FMA GEMMs at this "
+                         "row count, split-bf16 tcgen05 GEMMs from 2048 rows per call)",
                   "includes": "batch_nll (one flow call for all signal ranks): row gather, scaler.normalize, rank embedding, flow "
                               "forward+backward (all weights, context), "
                               + ("NCCL gradient all-reduce" if world > 1 else "no all-reduce at 1 GPU")
@@ -358,6 +400,7 @@ def main():
     ap.add_argument("--events", type=int, default=EVENTS_PER_GPU)
     ap.add_argument("--samples", type=int, default=SAMPLES_PER_EVENT)
     ap.add_argument("--train-events", type=int, default=TRAIN_EVENTS_PER_GPU)
+    ap.add_argument("--train-events-full", type=int, default=4096, help="config #4 un-sharded, timed at N=1 (0 = skip)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

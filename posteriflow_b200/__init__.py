@@ -9,8 +9,8 @@ from .flow import FLOW_NORM_BOUND, NSFPosteriorFlow  # noqa: F401
 from .lean import LeanNPE, ParamScaler, PARAM_NAMES, accelerate, posterior_chunk, sample_fused  # noqa: F401
 from .result import load_posterior, posterior_arrays, save_posterior  # noqa: F401
 from .summary import calib_block, posterior_summary  # noqa: F401
-from .train import batch_nll, signal_rows  # noqa: F401
+from .train import GraphedNLLStep, batch_nll, signal_rows  # noqa: F401
 
 __all__ = ["NSFPosteriorFlow", "LeanNPE", "ParamScaler", "PARAM_NAMES", "FLOW_NORM_BOUND", "accelerate",
-           "sample_fused", "posterior_chunk", "ops", "batch_nll", "signal_rows", "save_posterior", "load_posterior",
+           "sample_fused", "posterior_chunk", "ops", "batch_nll", "signal_rows", "GraphedNLLStep", "save_posterior", "load_posterior",
            "posterior_arrays", "posterior_summary", "calib_block"]

@@ -14,6 +14,7 @@
 //   loss.backward() through nflows (experiments/train_lean_npe.py:365) -> pf_flow_backward
 #include "pf_common.cuh"
 #include "pf_gemm.cuh"
+#include "pf_tc_gemm.cuh"
 #include "pf_spline.cuh"
 #include "pf_tail.cuh"
 
@@ -208,8 +209,24 @@ static pf_status ctxproj_impl(pf_flow* f, cudaStream_t st, const float* ctx, int
   const int N = f->L * 3 * f->H;
   EpiCtxProj epi{proj, N, f->bctx, f->H};
   if (flags & PF_FLAG_SANITIZE_CTX)
-    return sgemm_nt<EpiCtxProj, A_SANITIZE, 64>(f, st, ctx, f->C, f->Wctx, f->C, (int)E, N, f->C, epi);
-  return sgemm_nt<EpiCtxProj, A_PLAIN, 64>(f, st, ctx, f->C, f->Wctx, f->C, (int)E, N, f->C, epi);
+    return gemm_nt<EpiCtxProj, A_SANITIZE, 64>(f, st, ctx, f->C, f->Wctx, f->C, (int)E, N, f->C, epi);
+  return gemm_nt<EpiCtxProj, A_PLAIN, 64>(f, st, ctx, f->C, f->Wctx, f->C, (int)E, N, f->C, epi);
+}
+
+// PF_TC_DEBUG=1: synchronise and surface a barrier timeout of the split-bf16 tcgen05 GEMMs (pf_tc_gemm.cuh)
+static pf_status train_tc_check(pf_flow* f, cudaStream_t st, const char* where) {
+  if (!f->train_tc || !f->train_debug) return PF_OK;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) return PF_OK;  // no sync inside a capture
+  int herr = 0;
+  PF_CUDA(cudaStreamSynchronize(st));
+  PF_CUDA(cudaMemcpy(&herr, f->tg_err, sizeof(int), cudaMemcpyDeviceToHost));
+  if (herr) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: tensor-core GEMM barrier timeout, code %d", where, herr);
+    cudaMemset(f->tg_err, 0, sizeof(int));
+    return PF_ERR_CUDA;
+  }
+  return PF_OK;
 }
 
 static pf_status check_call(pf_flow* f, int64_t R, int64_t E, const int64_t* row2ctx, int64_t n_per_ctx) {
@@ -382,13 +399,13 @@ extern "C" pf_status pf_flow_forward(pf_flow* f, const float* x, const float* ct
       const float* Wb1 = f->Wb + ((size_t)l * 2 + 0) * H * H; const float* bb1 = f->bb + ((size_t)l * 2 + 0) * H;
       const float* Wa2 = f->Wa + ((size_t)l * 2 + 1) * H * H; const float* ba2 = f->ba + ((size_t)l * 2 + 1) * H;
       const float* Wb2 = f->Wb + ((size_t)l * 2 + 1) * H * H; const float* bb2 = f->bb + ((size_t)l * 2 + 1) * H;
-      PF_TRY((sgemm_nt<EpiBias, A_RELU, 64>(f, st, H0, H, Wa1, H, rows, H, H, EpiBias{U1, H, ba1, 0})));
-      PF_TRY((sgemm_nt<EpiGluResidual, A_RELU, 64>(f, st, U1, H, Wb1, H, rows, H, H,
+      PF_TRY((gemm_nt<EpiBias, A_RELU, 64>(f, st, H0, H, Wa1, H, rows, H, H, EpiBias{U1, H, ba1, 0})));
+      PF_TRY((gemm_nt<EpiGluResidual, A_RELU, 64>(f, st, U1, H, Wb1, H, rows, H, H,
                                                    EpiGluResidual{H0, H1, V1, H, bb1, 0, pl + H, ldproj, cm})));
-      PF_TRY((sgemm_nt<EpiBias, A_RELU, 64>(f, st, H1, H, Wa2, H, rows, H, H, EpiBias{U2, H, ba2, 0})));
-      PF_TRY((sgemm_nt<EpiGluResidual, A_RELU, 64>(f, st, U2, H, Wb2, H, rows, H, H,
+      PF_TRY((gemm_nt<EpiBias, A_RELU, 64>(f, st, H1, H, Wa2, H, rows, H, H, EpiBias{U2, H, ba2, 0})));
+      PF_TRY((gemm_nt<EpiGluResidual, A_RELU, 64>(f, st, U2, H, Wb2, H, rows, H, H,
                                                    EpiGluResidual{H1, H2, V2, H, bb2, 0, pl + 2 * H, ldproj, cm})));
-      PF_TRY((sgemm_nt<EpiBias, A_PLAIN, 64>(f, st, H2, H, f->Wf + (size_t)l * PLD * H, H, rows, P, H,
+      PF_TRY((gemm_nt<EpiBias, A_PLAIN, 64>(f, st, H2, H, f->Wf + (size_t)l * PLD * H, H, rows, P, H,
                                              EpiBias{Pl, PLD, f->bf + (size_t)l * PLD, 0})));
       PF_NB_DISPATCH(f->NB, PF_TRY(launch_spline_fwd<NB_>(f, st, xin, Pl, rows, yout, ldc, l > 0)));
     }
@@ -398,7 +415,7 @@ extern "C" pf_status pf_flow_forward(pf_flow* f, const float* x, const float* ct
       PF_LAUNCH_CHECK(f);
     }
   }
-  return PF_OK;
+  return train_tc_check(f, st, "pf_flow_forward");
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -683,13 +700,23 @@ struct LoadCtx {
   __device__ __forceinline__ float operator()(int m, int n) const { return ctx[cm(m) * C + n]; }
 };
 
+// Gradient activations of one layer.  Two sets (layer parity): the weight / bias / context gradients of layer l
+// (none of which is on the layer-to-layer dependency chain) run on the handle's side stream while the main
+// stream already works on layer l-1, so the set of layer l must survive until layer l-2 starts.
+struct BwdSet { float *gp, *gh, *gu[2], *gv[2], *gproj; };
 struct BwdWs {
-  float *gp, *gh, *gu, *gv, *gproj, *gxd, *ga, *gb;
+  BwdSet set[2];
+  float *gxd, *ga, *gb;
   size_t bytes; bool ok;
   BwdWs(const pf_flow* f, void* base, size_t cap, int64_t R) {
     Carver c(base, base ? cap : (size_t)-1 / 2);
-    gp = c.f32((size_t)R * f->PLD); gh = c.f32((size_t)R * f->H); gu = c.f32((size_t)R * f->H);
-    gv = c.f32((size_t)R * f->H); gproj = c.f32((size_t)R * 3 * f->H); gxd = c.f32((size_t)R * f->D);
+    for (int i = 0; i < 2; ++i) {
+      BwdSet& b = set[i];
+      b.gp = c.f32((size_t)R * f->PLD); b.gh = c.f32((size_t)R * f->H);
+      for (int k = 0; k < 2; ++k) { b.gu[k] = c.f32((size_t)R * f->H); b.gv[k] = c.f32((size_t)R * f->H); }
+      b.gproj = c.f32((size_t)R * 3 * f->H);
+    }
+    gxd = c.f32((size_t)R * f->D);
     ga = c.f32((size_t)R * f->D); gb = c.f32((size_t)R * f->D);
     bytes = c.used; ok = c.ok;
   }
@@ -737,72 +764,96 @@ extern "C" pf_status pf_flow_backward(pf_flow* f, const void* saved, const float
   const int64_t nRH = (int64_t)R * H;
   const unsigned gRH = (unsigned)((nRH + 255) / 256);
 
+  // Two streams: `st` carries the dependency chain (spline backward and the data gradients, 10 kernels per layer),
+  // `sd` (the handle's side stream, forked from and joined back into `st` with events, so the pair is capturable
+  // in a CUDA graph) the 13 kernels per layer whose results nobody downstream waits for.
+  const bool two = f->side != nullptr && f->train_streams;
+  cudaStream_t sd = two ? f->side : st;
   const float* gy = gz;      // gradient wrt the current layer's output
   float* gnext = ws.ga;
   for (int l = L - 1; l >= 0; --l) {
     const pf_layer_grads* g = grads ? &grads[l] : nullptr;
+    const int par = (L - 1 - l) & 1;
+    const BwdSet& b = ws.set[par];
     const float* xin = sv.XS + (size_t)l * R * D;
     const float* H0 = sv.a(f, R, l, 0); const float* U1 = sv.a(f, R, l, 1); const float* V1 = sv.a(f, R, l, 2);
     const float* H1 = sv.a(f, R, l, 3); const float* U2 = sv.a(f, R, l, 4); const float* V2 = sv.a(f, R, l, 5);
     const float* H2 = sv.a(f, R, l, 6);
     const float* Pl = sv.P + (size_t)l * R * PLD;
     const float* pl = sv.proj + (size_t)l * 3 * H;
+    // this parity's buffers were last read by the side work of layer l+2
+    if (two && l + 2 <= L - 1) PF_CUDA(cudaStreamWaitEvent(st, f->ev_side[par], 0));
+    // ---- chain ----
     // 1. spline: d(params), direct d(x)
-    PF_NB_DISPATCH(f->NB, PF_TRY(launch_spline_bwd<NB_>(f, st, xin, Pl, R, gy, glogdet, ws.gp, ws.gxd)));
+    PF_NB_DISPATCH(f->NB, PF_TRY(launch_spline_bwd<NB_>(f, st, xin, Pl, R, gy, glogdet, b.gp, ws.gxd)));
     // 2. final layer
-    if (g && g->final_w)
-      PF_TRY((sgemm_tn(f, st, LoadPlain{ws.gp, PLD}, LoadPlain{H2, H}, R, P, H,
-                       EpiWgrad{g->final_w, H, nullptr, perm, RULE_FINAL, D, MULT})));
-    if (g && g->final_b) PF_TRY(colsum(f, st, ws.gp, PLD, R, P, ColMap{nullptr, H, 0, {g->final_b, nullptr, nullptr}}));
-    PF_TRY((sgemm_nt<EpiStore, A_PLAIN, 64>(f, st, ws.gp, PLD, f->WfT + (size_t)l * H * PLD, PLD, R, H, P,
-                                            EpiStore{ws.gh, H})));
+    PF_TRY((gemm_nt<EpiStore, A_PLAIN, 64>(f, st, b.gp, PLD, f->WfT + (size_t)l * H * PLD, PLD, R, H, P,
+                                           EpiStore{b.gh, H})));
     // 3. residual blocks, last first
     for (int k = 1; k >= 0; --k) {
       const float* Hin = k ? H1 : H0;
       const float* U = k ? U2 : U1;
       const float* V = k ? V2 : V1;
-      glu_bwd_kernel<<<gRH, 256, 0, st>>>(ws.gh, V, pl + (size_t)(k + 1) * H, ldproj, cm, R, H, ws.gv, ws.gproj, 3 * H,
+      glu_bwd_kernel<<<gRH, 256, 0, st>>>(b.gh, V, pl + (size_t)(k + 1) * H, ldproj, cm, R, H, b.gv[k], b.gproj, 3 * H,
                                           k + 1);
       PF_LAUNCH_CHECK(f);
-      if (g && g->blk_lin_w[k][1])
-        PF_TRY((sgemm_tn(f, st, LoadPlain{ws.gv, H}, LoadRelu{U, H}, R, H, H,
-                         EpiWgrad{g->blk_lin_w[k][1], H, perm, perm, RULE_HIDDEN, D, MULT})));
-      if (g && g->blk_lin_b[k][1])
-        PF_TRY(colsum(f, st, ws.gv, H, R, H, ColMap{perm, H, 0, {g->blk_lin_b[k][1], nullptr, nullptr}}));
-      PF_TRY((sgemm_nt<EpiReluMaskStore, A_PLAIN, 64>(f, st, ws.gv, H, f->WbT + ((size_t)l * 2 + k) * H * H, H, R, H, H,
-                                                      EpiReluMaskStore{ws.gu, U, H})));
-      if (g && g->blk_lin_w[k][0])
-        PF_TRY((sgemm_tn(f, st, LoadPlain{ws.gu, H}, LoadRelu{Hin, H}, R, H, H,
-                         EpiWgrad{g->blk_lin_w[k][0], H, perm, perm, RULE_HIDDEN, D, MULT})));
-      if (g && g->blk_lin_b[k][0])
-        PF_TRY(colsum(f, st, ws.gu, H, R, H, ColMap{perm, H, 0, {g->blk_lin_b[k][0], nullptr, nullptr}}));
-      PF_TRY((sgemm_nt<EpiReluMaskAdd, A_PLAIN, 64>(f, st, ws.gu, H, f->WaT + ((size_t)l * 2 + k) * H * H, H, R, H, H,
-                                                    EpiReluMaskAdd{ws.gh, Hin, H})));
+      PF_TRY((gemm_nt<EpiReluMaskStore, A_PLAIN, 64>(f, st, b.gv[k], H, f->WbT + ((size_t)l * 2 + k) * H * H, H, R, H, H,
+                                                     EpiReluMaskStore{b.gu[k], U, H})));
+      PF_TRY((gemm_nt<EpiReluMaskAdd, A_PLAIN, 64>(f, st, b.gu[k], H, f->WaT + ((size_t)l * 2 + k) * H * H, H, R, H, H,
+                                                   EpiReluMaskAdd{b.gh, Hin, H})));
     }
     // 4. initial layer + relu(context_layer)
-    ctx_relu_bwd_kernel<<<gRH, 256, 0, st>>>(ws.gh, pl, ldproj, cm, R, H, ws.gproj, 3 * H);
+    ctx_relu_bwd_kernel<<<gRH, 256, 0, st>>>(b.gh, pl, ldproj, cm, R, H, b.gproj, 3 * H);
     PF_LAUNCH_CHECK(f);
-    if (g && g->initial_w)
-      PF_TRY((sgemm_tn(f, st, LoadPlain{ws.gh, H}, LoadRev{xin, D}, R, H, D,
-                       EpiWgrad{g->initial_w, D, perm, nullptr, RULE_INITIAL, D, MULT})));
-    if (g && g->initial_b) PF_TRY(colsum(f, st, ws.gh, H, R, H, ColMap{perm, H, 0, {g->initial_b, nullptr, nullptr}}));
     float* gout = (l == 0) ? gx : gnext;
     if (gout)
-      PF_TRY((sgemm_nt<EpiGxOut, A_PLAIN, 32>(f, st, ws.gh, H, f->W0T + (size_t)l * f->DP * H, H, R, D, H,
-                                              EpiGxOut{gout, ws.gxd, D})));
-    // 5. context path: d(ctx) and the three context Linear layers
+      PF_TRY((gemm_nt<EpiGxOut, A_PLAIN, 32>(f, st, b.gh, H, f->W0T + (size_t)l * f->DP * H, H, R, D, H,
+                                             EpiGxOut{gout, ws.gxd, D})));
+    if (two) {
+      PF_CUDA(cudaEventRecord(f->ev_main[par], st));
+      PF_CUDA(cudaStreamWaitEvent(sd, f->ev_main[par], 0));
+    }
+    // ---- off the chain: weight, bias and context gradients of this layer ----
+    if (g && g->final_w)
+      PF_TRY((gemm_tn(f, sd, LoadPlain{b.gp, PLD}, LoadPlain{H2, H}, R, P, H,
+                      EpiWgrad{g->final_w, H, nullptr, perm, RULE_FINAL, D, MULT})));
+    if (g && g->final_b) PF_TRY(colsum(f, sd, b.gp, PLD, R, P, ColMap{nullptr, H, 0, {g->final_b, nullptr, nullptr}}));
+    for (int k = 1; k >= 0; --k) {
+      const float* Hin = k ? H1 : H0;
+      const float* U = k ? U2 : U1;
+      if (g && g->blk_lin_w[k][1])
+        PF_TRY((gemm_tn(f, sd, LoadPlain{b.gv[k], H}, LoadRelu{U, H}, R, H, H,
+                        EpiWgrad{g->blk_lin_w[k][1], H, perm, perm, RULE_HIDDEN, D, MULT})));
+      if (g && g->blk_lin_b[k][1])
+        PF_TRY(colsum(f, sd, b.gv[k], H, R, H, ColMap{perm, H, 0, {g->blk_lin_b[k][1], nullptr, nullptr}}));
+      if (g && g->blk_lin_w[k][0])
+        PF_TRY((gemm_tn(f, sd, LoadPlain{b.gu[k], H}, LoadRelu{Hin, H}, R, H, H,
+                        EpiWgrad{g->blk_lin_w[k][0], H, perm, perm, RULE_HIDDEN, D, MULT})));
+      if (g && g->blk_lin_b[k][0])
+        PF_TRY(colsum(f, sd, b.gu[k], H, R, H, ColMap{perm, H, 0, {g->blk_lin_b[k][0], nullptr, nullptr}}));
+    }
+    if (g && g->initial_w)
+      PF_TRY((gemm_tn(f, sd, LoadPlain{b.gh, H}, LoadRev{xin, D}, R, H, D,
+                      EpiWgrad{g->initial_w, D, perm, nullptr, RULE_INITIAL, D, MULT})));
+    if (g && g->initial_b) PF_TRY(colsum(f, sd, b.gh, H, R, H, ColMap{perm, H, 0, {g->initial_b, nullptr, nullptr}}));
+    // context path: d(ctx) and the three context Linear layers
     if (gctx)
-      PF_TRY((sgemm_nt<EpiCtxAtomic, A_PLAIN, 64>(f, st, ws.gproj, 3 * H, f->WctxT + (size_t)l * 3 * H, (int)ldproj, R,
-                                                  C, 3 * H, EpiCtxAtomic{gctx, C, cm})));
+      PF_TRY((gemm_nt<EpiCtxAtomic, A_PLAIN, 64>(f, sd, b.gproj, 3 * H, f->WctxT + (size_t)l * 3 * H, (int)ldproj, R,
+                                                 C, 3 * H, EpiCtxAtomic{gctx, C, cm})));
     if (g && (g->ctx_w || g->blk_ctx_w[0] || g->blk_ctx_w[1]))
-      PF_TRY((sgemm_tn(f, st, LoadPlain{ws.gproj, 3 * H}, LoadCtx{ctx, C, cm}, R, 3 * H, C,
-                       EpiWgradCtx{{g->ctx_w, g->blk_ctx_w[0], g->blk_ctx_w[1]}, C, H, perm})));
+      PF_TRY((gemm_tn(f, sd, LoadPlain{b.gproj, 3 * H}, LoadCtx{ctx, C, cm}, R, 3 * H, C,
+                      EpiWgradCtx{{g->ctx_w, g->blk_ctx_w[0], g->blk_ctx_w[1]}, C, H, perm})));
     if (g && (g->ctx_b || g->blk_ctx_b[0] || g->blk_ctx_b[1]))
-      PF_TRY(colsum(f, st, ws.gproj, 3 * H, R, 3 * H, ColMap{perm, H, 3, {g->ctx_b, g->blk_ctx_b[0], g->blk_ctx_b[1]}}));
+      PF_TRY(colsum(f, sd, b.gproj, 3 * H, R, 3 * H, ColMap{perm, H, 3, {g->ctx_b, g->blk_ctx_b[0], g->blk_ctx_b[1]}}));
+    if (two) PF_CUDA(cudaEventRecord(f->ev_side[par], sd));
     gy = gnext;
     gnext = (gnext == ws.ga) ? ws.gb : ws.ga;
   }
-  return PF_OK;
+  if (two) {   // join: everything the side stream produced is ordered before what follows on `st`
+    PF_CUDA(cudaStreamWaitEvent(st, f->ev_side[0], 0));
+    if (L > 1) PF_CUDA(cudaStreamWaitEvent(st, f->ev_side[1], 0));
+  }
+  return train_tc_check(f, st, "pf_flow_backward");
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -1,6 +1,8 @@
 // Handle lifetime + weight packing (replaces nflows' per-call `weight * mask`).
 #include <vector>
 
+#include <stdlib.h>
+
 #include "pf_common.cuh"
 
 namespace pf {
@@ -88,6 +90,16 @@ extern "C" pf_status pf_flow_create(const pf_flow_desc* d, pf_flow** out) {
   f->NB = d->num_bins; f->MULT = 3 * f->NB - 1; f->P = f->D * f->MULT; f->PLD = round_up(f->P, 4);
   f->DP = round_up(f->D, 4); f->G = f->D - 1;
   cudaDeviceGetAttribute(&f->sm_count, cudaDevAttrMultiProcessorCount, d->device);
+  {
+    const char* tt = getenv("PF_TRAIN_TC");
+    const char* dbg = getenv("PF_TC_DEBUG");
+    f->train_tc = d->tier == PF_TIER_BF16 && !(tt && tt[0] == '0');
+    f->train_debug = dbg && dbg[0] == '1';
+    const char* mr = getenv("PF_TRAIN_TC_MIN_ROWS");
+    f->train_tc_min_rows = mr ? atoi(mr) : 2048;
+    const char* ts = getenv("PF_TRAIN_STREAMS");
+    f->train_streams = !(ts && ts[0] == '0');
+  }
 
   // degree-sorted hidden permutation (stable): slot s <- nflows unit perm[s]
   f->perm_host = new int[f->H];
@@ -117,6 +129,13 @@ extern "C" pf_status pf_flow_create(const pf_flow_desc* d, pf_flow** out) {
   cudaError_t e = cudaMalloc(&f->arena, n * sizeof(float));
   if (e == cudaSuccess) e = cudaMalloc(&f->d_perm, H * sizeof(int));
   if (e == cudaSuccess) e = cudaMalloc(&f->d_flag, sizeof(int));
+  if (e == cudaSuccess) e = cudaMalloc(&f->tg_err, sizeof(int));
+  if (e == cudaSuccess) e = cudaMemset(f->tg_err, 0, sizeof(int));
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&f->side, cudaStreamNonBlocking);
+  for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+    e = cudaEventCreateWithFlags(&f->ev_main[i], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&f->ev_side[i], cudaEventDisableTiming);
+  }
   if (e == cudaSuccess) e = cudaMemcpy(f->d_perm, f->perm_host, H * sizeof(int), cudaMemcpyHostToDevice);
   if (e != cudaSuccess) {
     pf_status st = cuda_fail(e, "arena allocation", __FILE__, __LINE__);
@@ -138,6 +157,12 @@ extern "C" void pf_flow_destroy(pf_flow* f) {
   if (f->arena) cudaFree(f->arena);
   if (f->d_perm) cudaFree(f->d_perm);
   if (f->d_flag) cudaFree(f->d_flag);
+  if (f->tg_err) cudaFree(f->tg_err);
+  for (int i = 0; i < 2; ++i) {
+    if (f->ev_main[i]) cudaEventDestroy(f->ev_main[i]);
+    if (f->ev_side[i]) cudaEventDestroy(f->ev_side[i]);
+  }
+  if (f->side) cudaStreamDestroy(f->side);
   delete[] f->perm_host;
   delete f;
 }

@@ -59,3 +59,122 @@ def batch_nll_reference_order(model, strain, params, nsig, asd_bands=None, conte
         losses.append(model.nll(None, params[idx, r, :], rank, context=context[idx]).sum())
         count += idx.numel()
     return torch.stack(losses).sum() / count
+
+
+class GraphedNLLStep:
+    """`batch_nll` + backward of the flow head as ONE CUDA-graph replay per step.
+
+    The flow's forward-with-saved-activations and backward are ~320 dependent kernel launches per step
+    (DESIGN.md 5.6); issued eagerly through autograd the host needs longer to launch them than the device to run
+    them.  Here the two custom ops (`posteriflow::nsf_forward(save=True)`, `posteriflow::nsf_backward`) and the
+    NLL arithmetic between them are captured once per row-count bucket and replayed:
+
+        step = GraphedNLLStep(model)
+        loss = step(params, nsig, context)      # .grad of the flow weights, rank embedding and `context` are set
+
+    Rows are padded to a multiple of `bucket` (weight 0: a padded row contributes exactly zero to every
+    gradient), so a handful of graphs covers the step-to-step variation of the number of signals.  The part of
+    the graph of `context` that lies outside the flow (row gather, rank embedding, the caller's encoder) stays
+    with autograd: the graph hands back d loss / d full-context and `Tensor.backward` carries it on.
+    Same value and gradients as `batch_nll(...).backward()` (tests/test_gpu_glue.py)."""
+
+    def __init__(self, model, bucket: int = 128, distributed: bool = False):
+        self.model, self.bucket, self.distributed = model, int(bucket), distributed
+        self.graphs = {}
+        self.flow_params = model.flow.layer_weights()
+        self._gbuf = None
+        self.flat_grad = None
+        self.last_launches = 0
+
+    def _capture(self, cap: int):
+        import math
+        m = self.model
+        dev = self.flow_params[0].device
+        D, C = m.flow.features, m.flow.context_features
+        st = {"x": torch.zeros(cap, D, device=dev), "ctx": torch.zeros(cap, C, device=dev),
+              "w": torch.zeros(cap, device=dev)}
+        fh = m.flow.handle()
+        weights = [p.detach() for p in self.flow_params]
+        const = D * math.log(2 * math.pi)
+
+        def body():
+            z, ld, saved = torch.ops.posteriflow.nsf_forward(st["x"], st["ctx"], weights, fh.id, 1, True)
+            nll = 0.5 * ((z * z).sum(dim=1) + const) - ld
+            loss = (nll * st["w"]).sum()
+            outs = torch.ops.posteriflow.nsf_backward(saved, st["ctx"], z * st["w"].unsqueeze(1), -st["w"], weights,
+                                                      fh.id, 1)
+            return loss, outs[1], list(outs[2:])
+
+        s = torch.cuda.Stream(device=dev)
+        s.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(s):
+            for _ in range(2):      # warm-up outside capture (lazy attribute setting, allocator)
+                body()
+        torch.cuda.current_stream(dev).wait_stream(s)
+        g = torch.cuda.CUDAGraph()
+        l0 = fh.launches
+        with torch.cuda.graph(g):
+            st["loss"], st["gctx"], st["gw"] = body()
+        st["graph"] = g
+        st["launches"] = fh.launches - l0      # library kernels inside one replay
+        return st
+
+    def __call__(self, params: Tensor, nsig: Tensor, context: Tensor) -> Tensor:
+        m = self.model
+        event, rank = signal_rows(nsig.to(context.device), int(m.max_signals))
+        R = int(event.numel())
+        if R == 0:
+            return context.sum() * 0.0
+        m.flow.handle()                         # re-pack if an optimizer step changed the weights
+        cap = (R + self.bucket - 1) // self.bucket * self.bucket
+        st = self.graphs.get(cap)
+        if st is None:
+            st = self.graphs[cap] = self._capture(cap)
+        ctx_full = m._full_context(context[event], rank)          # autograd-tracked (encoder, rank embedding)
+        count = torch.tensor(float(R), device=context.device)
+        if self.distributed:
+            from .dist import _world
+            import torch.distributed as dist
+            if _world()[1] > 1:
+                dist.all_reduce(count)
+        with torch.no_grad():
+            st["x"][:R].copy_(m.scaler.normalize(params[event, rank, :]))
+            st["ctx"][:R].copy_(ctx_full)
+            st["w"].zero_()
+            st["w"][:R] = 1.0 / count
+        st["graph"].replay()
+        self.last_launches = st["launches"]
+        # the graph's gradient tensors are overwritten by the next replay: hand out copies (two multi-tensor kernels)
+        if self._gbuf is None:      # views of ONE flat buffer: the data-parallel all-reduce is a single collective
+            self.flat_grad = torch.empty(sum(g.numel() for g in st["gw"]), dtype=torch.float32, device=st["gw"][0].device)
+            self._gbuf, o = [], 0
+            for g in st["gw"]:
+                self._gbuf.append(self.flat_grad[o:o + g.numel()].view_as(g))
+                o += g.numel()
+        fresh = [i for i, p in enumerate(self.flow_params) if p.requires_grad and p.grad is None]
+        accum = [i for i, p in enumerate(self.flow_params) if p.requires_grad and p.grad is not None]
+        if fresh:
+            torch._foreach_copy_([self._gbuf[i] for i in fresh], [st["gw"][i] for i in fresh])
+            for i in fresh:
+                self.flow_params[i].grad = self._gbuf[i]
+        if accum:
+            torch._foreach_add_([self.flow_params[i].grad for i in accum], [st["gw"][i] for i in accum])
+        if ctx_full.requires_grad:
+            ctx_full.backward(st["gctx"][:R])
+        return st["loss"].detach()
+
+    def allreduce(self, extra_params=()) -> int:
+        """Data-parallel gradient exchange after a step: ONE all-reduce (sum) of the flat flow-gradient
+        buffer (25 MB fp32) -- no flatten / unflatten copies -- plus one bucket for `extra_params` (rank embedding,
+        encoder).  Falls back to the bucketed path if the .grad tensors are not this object's views (e.g. after
+        gradient accumulation into foreign tensors).  Returns the number of collectives issued."""
+        import torch.distributed as dist
+        from .dist import _world, allreduce_gradients
+        if _world()[1] == 1:
+            return 0
+        mine = self._gbuf is not None and all(
+            (not p.requires_grad) or p.grad is self._gbuf[i] for i, p in enumerate(self.flow_params))
+        if not mine:
+            return allreduce_gradients(list(self.flow_params) + list(extra_params))
+        dist.all_reduce(self.flat_grad)
+        return 1 + allreduce_gradients(list(extra_params))

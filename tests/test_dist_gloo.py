@@ -67,3 +67,47 @@ def test_gradient_allreduce_matches_single_process_mean():
         gw, gb, n = res[r]
         assert torch.allclose(gw, lin.weight.grad, atol=1e-5) and torch.allclose(gb, lin.bias.grad, atol=1e-6)
         assert n >= 2
+
+
+def _flat_worker(rank, world, port, out):
+    """GraphedNLLStep.allreduce on CPU tensors: the graph replay itself needs a GPU, the exchange does not."""
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import posteriflow_b200 as P
+        torch.manual_seed(0)
+        m = P.LeanNPE(flow_layers=1, flow_hidden=32, flow_bins=8)
+        step = P.GraphedNLLStep(m, distributed=True)
+        ps = step.flow_params
+        step.flat_grad = torch.empty(sum(p.numel() for p in ps))
+        step._gbuf, o = [], 0
+        for i, p in enumerate(ps):
+            v = step.flat_grad[o:o + p.numel()].view_as(p)
+            v.fill_(float(rank + 1) * (i + 1))
+            p.grad = v
+            step._gbuf.append(v)
+            o += p.numel()
+        m.rank_embed.weight.grad = torch.full_like(m.rank_embed.weight, float(rank + 1))
+        n1 = step.allreduce(extra_params=[m.rank_embed.weight])
+        a = (float(ps[0].grad.flatten()[0]), float(ps[-1].grad.flatten()[-1]), float(m.rank_embed.weight.grad[0, 0]))
+        # foreign .grad tensors: falls back to the bucketed path, same sums
+        for i, p in enumerate(ps):
+            p.grad = torch.full_like(p, float(rank + 1) * (i + 1))
+        n2 = step.allreduce()
+        b = (float(ps[0].grad.flatten()[0]), float(ps[-1].grad.flatten()[-1]))
+        out[rank] = (n1, a, n2, b, len(ps))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_graphed_step_allreduce_is_one_collective_on_the_flat_buffer():
+    world, port = 2, _free_port()
+    with mp.Manager() as m:
+        out = m.dict()
+        mp.spawn(_flat_worker, args=(world, port, out), nprocs=world, join=True)
+        res = dict(out)
+    for r in range(world):
+        n1, a, n2, b, nps = res[r]
+        assert n1 == 2                     # flat flow gradients + one bucket for the rank embedding
+        assert a == (3.0, 3.0 * nps, 3.0)  # (1 + 2) * (i + 1)
+        assert n2 >= 1 and b == (3.0, 3.0 * nps)

@@ -233,3 +233,45 @@ def test_batch_nll_fused_matches_loop_and_oracle():
     assert abs(float(loop) - ref) <= 1e-4 * max(1.0, abs(ref))
     scale = float(c2.grad.abs().max())
     assert float((c1.grad - c2.grad).abs().max()) <= 1e-4 * scale
+
+
+@pytest.mark.parametrize("tier", ["fp32", "bf16"])
+def test_graphed_nll_step_matches_batch_nll(tier, monkeypatch):
+    """GraphedNLLStep (one CUDA-graph replay per step, rows padded to a bucket with zero weight) == batch_nll +
+    backward through autograd: same loss, same gradient of the context, the rank embedding and every flow weight;
+    replaying the cached graph on a second batch with a different number of rows in the same bucket stays exact,
+    and a second call without clearing .grad accumulates."""
+    import posteriflow_b200 as P
+    if tier == "bf16":       # capture the split-bf16 tcgen05 GEMMs too (by default they serve calls of >= 2048 rows)
+        monkeypatch.setenv("PF_TRAIN_TC_MIN_ROWS", "0")
+    spec, w, g = load_golden("lean_glue")
+    m = lean_model(w, g, tier=tier)
+    sc = O.Scaler()
+    step = P.GraphedNLLStep(m, bucket=64)
+    gen = torch.Generator().manual_seed(12)
+    tol = 1e-4 if tier == "fp32" else 5e-4
+    for trial in range(3):
+        B = 40
+        nsig = torch.multinomial(torch.tensor([.55, .20, .12, .08, .05]), B, replacement=True, generator=gen) + 1
+        params = sc.denormalize(torch.rand(B, 5, 11, generator=gen) * 2 - 1).cuda()
+        ctx = torch.randn(B, 256, generator=gen)
+        m.zero_grad(set_to_none=True)
+        c1 = ctx.cuda().requires_grad_(True)
+        ref = P.batch_nll(m, None, params, nsig.cuda(), context=c1)
+        ref.backward()
+        ref_g = {n: p.grad.clone() for n, p in m.named_parameters() if p.grad is not None}
+        m.zero_grad(set_to_none=True)
+        c2 = ctx.cuda().requires_grad_(True)
+        loss = step(params, nsig.cuda(), c2)
+        assert abs(float(loss) - float(ref)) <= tol * max(1.0, abs(float(ref)))
+        assert float((c2.grad - c1.grad).abs().max()) <= tol * float(c1.grad.abs().max())
+        got_g = {n: p.grad for n, p in m.named_parameters() if p.grad is not None}
+        assert set(got_g) == set(ref_g)
+        for n in ref_g:
+            assert float((got_g[n] - ref_g[n]).abs().max()) <= tol * max(1e-12, float(ref_g[n].abs().max())), n
+        if trial == 2:      # accumulate: a second call on the same batch doubles the flow-weight gradients
+            c3 = ctx.cuda().requires_grad_(True)
+            step(params, nsig.cuda(), c3)
+            n0 = "flow.transform._transforms.1.autoregressive_net.final_layer.weight"
+            assert float((m.get_parameter(n0).grad - 2 * ref_g[n0]).abs().max()) <= 2 * tol * float(ref_g[n0].abs().max())
+    assert len(step.graphs) <= 2

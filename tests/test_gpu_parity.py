@@ -58,17 +58,30 @@ def test_forward_and_nll_match_reference(case):
     assert torch.equal(nll, nll_none)
 
 
+@pytest.mark.parametrize("tier", ["fp32", "bf16"])
 @pytest.mark.parametrize("case", ["lean_default", "lean_stress", "lean_stress_1layer", "tiny_explicit"])
-def test_backward_matches_reference_autograd(case):
+def test_backward_matches_reference_autograd(case, tier, monkeypatch):
+    """tier="bf16": the training path of the tensor-core tier (split-bf16 tcgen05 GEMMs, pf_tc_gemm.cuh: three MMAs per
+    product keep ~16 significand bits), forced on for these small batches (PF_TRAIN_TC_MIN_ROWS=0; by default calls
+    under 2048 rows stay on the FP32-FMA kernels).  Stated tolerance of that path, float64-arbitrated like the FP32
+    one: gradients of x / context within 2e-3 of the gradient's scale, weight-gradient norms within 1e-3, sampled
+    weight-gradient entries within 5e-2 of the tensor's rms entry (measured 2.8e-2: the fixture puts inputs exactly ON
+    spline knots, where a 1e-5 change of a knot moves a row to the neighbouring bin -- the flow is C1 there, the
+    parameter gradients are not), median error within 16x of the float32 reference's own (measured 5-7x)."""
+    mf, tol_g, tol_n, tol_s = (2.0, TOL, TOL, TOL) if tier == "fp32" else (16.0, 2e-3, 1e-3, 5e-2)
+    if tier == "bf16":
+        monkeypatch.setenv("PF_TRAIN_TC_MIN_ROWS", "0")      # read when the handle is created
+    if tier == "bf16" and case == "tiny_explicit":
+        pytest.skip("the tensor-core tier covers the LeanNPE / head shapes only (tests/test_gpu_tc.py)")
     spec, w, g = load_golden(case)
-    flow = make_flow(spec, w, "cuda")
+    flow = make_flow(spec, w, "cuda", tier=tier)
     x = t(g["fwd_x"], "cuda").requires_grad_(True)
     ctx = t(g["ctx"], "cuda").requires_grad_(True)
     gw = t(g["grad_upstream"], "cuda").float()
     loss = (flow.compute_psd_aware_nll(x, ctx, torch.zeros_like(x)) * gw).sum()
     loss.backward()
     def gcheck(name, got, r32, r64):  # relative to the gradient's own scale (max |ref|)
-        check_parity(name, got, r32, r64, scale=max(1e-6, float(np.abs(r64).max())))
+        check_parity(name, got, r32, r64, tol=tol_g, scale=max(1e-6, float(np.abs(r64).max())), median_factor=mf)
     gcheck("grad x", x.grad.cpu().numpy(), g["grad_x_f32"], g["grad_x_f64"])
     gcheck("grad ctx", ctx.grad.cpu().numpy(), g["grad_ctx_f32"], g["grad_ctx_f64"])
     names = [str(n) for n in g["grad_w_names"]]
@@ -88,10 +101,10 @@ def test_backward_matches_reference_autograd(case):
         ref_s64.append(g["grad_w_samples_f64"][i] / sc)
     n64 = g["grad_w_norms_f64"]
     check_parity("weight-grad norms", np.array(got_norm) / n64, g["grad_w_norms_f32"] / n64, np.ones_like(n64),
-                 median_factor=None)
+                 tol=tol_n, median_factor=None)
     # sampled entries, each tensor normalised by its own rms gradient entry
     check_parity("weight-grad samples", np.stack(got_s), np.stack(ref_s32), np.stack(ref_s64),
-                 scale=max(1.0, float(np.abs(np.stack(ref_s64)).max())))
+                 tol=tol_s, scale=max(1.0, float(np.abs(np.stack(ref_s64)).max())), median_factor=mf)
     # masked entries receive exactly zero gradient, like d(W*mask)/dW
     net = flow.transform._transforms[1].autoregressive_net
     for lin in (net.initial_layer, net.final_layer, net.blocks[0].linear_layers[0], net.blocks[1].linear_layers[1]):
