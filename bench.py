@@ -320,7 +320,7 @@ def run_ours(args):
         full = {"events": Bf, "flow_rows": Rf, "ms_per_step": ms_full / args.steps,
                 "steps_per_sec": args.steps / (ms_full * 1e-3), "gpu_launches": int(gstep.last_launches * args.steps),
                 "roofline_frac": 3 * (F_X + F_CTX) * Rf * args.steps / (ms_full * 1e-3) / 1e12 / float(peaks()[0]["bf16_tflops_sustained"]),
-                "kernels": "split-bf16 tcgen05 GEMMs (calls of >= 2048 rows)" if args.tier == "bf16" else "FP32-FMA GEMMs"}
+                "kernels": "split-bf16 tcgen05 GEMMs (calls of >= 512 rows)" if args.tier == "bf16" else "FP32-FMA GEMMs"}
 
     pk, pk_kind = peaks()
     rows_s = R * world * args.steps / (ms * 1e-3)
@@ -336,7 +336,7 @@ def run_ours(args):
         "data": "synthetic (random-init weights, N(0,1) contexts standing in for encoder output, in-kernel Philox base noise)",
         "config": workload_config(world) if (E, n) == (EVENTS_PER_GPU, SAMPLES_PER_EVENT) else
         {"workload": f"{E} events x {n} samples per GPU (non-default)", "parallelism": f"events sharded over {world} GPU(s)"},
-        "tier": args.tier + (" (sampler + log-prob: tcgen05 bf16 operands, fp32 accumulate + fp32 spline; training step: FP32-FMA GEMMs below 2048 flow rows per call, split-bf16 tcgen05 GEMMs above)"
+        "tier": args.tier + (" (sampler + log-prob: tcgen05 bf16 operands, fp32 accumulate + fp32 spline; training step: split-bf16 tcgen05 GEMMs, fp32 accumulate; FP32-FMA GEMMs for calls under 512 flow rows)"
                              if args.tier == "bf16" else ""),
         "e2e": {"value": R * world * args.steps / (ms_e2e * 1e-3), "unit": "samples/s",
                 "h2d_bytes_per_step": int(ctx_host.numel() * 4), "d2h_bytes_per_step": int(theta_host.numel() * 4),
@@ -373,8 +373,8 @@ def run_ours(args):
                   "gpu_launches": int(launches_train), "ms_per_step_eager_autograd": ms_train_eager / args.steps,
                   "full_batch_1gpu": full,
                   "api": "posteriflow_b200.GraphedNLLStep (batch_nll forward + backward captured in one CUDA graph per "
-                         "row bucket; weight / bias / context gradients on a side stream; FP32-FMA GEMMs at this "
-                         "row count, split-bf16 tcgen05 GEMMs from 2048 rows per call)",
+                         "row bucket; weight / bias / context gradients on a side stream; split-bf16 tcgen05 GEMMs from "
+                         "512 rows per call)",
                   "includes": "batch_nll (one flow call for all signal ranks): row gather, scaler.normalize, rank embedding, flow "
                               "forward+backward (all weights, context), "
                               + ("NCCL gradient all-reduce" if world > 1 else "no all-reduce at 1 GPU")

@@ -104,7 +104,7 @@ struct pf_flow {
   void* dense;           // dense density-direction kernel state (pf_tc_dense.cu), NULL when the shape is not covered
   // training path of the tensor-core tier (pf_tc_gemm.cuh): split-bf16 tcgen05 GEMMs instead of the FP32-FMA ones
   bool train_tc;         // tier == PF_TIER_BF16 and PF_TRAIN_TC != 0
-  int train_tc_min_rows; // calls with fewer flow rows stay on the FP32-FMA GEMMs (PF_TRAIN_TC_MIN_ROWS, default 2048)
+  int train_tc_min_rows; // calls with fewer flow rows stay on the FP32-FMA GEMMs (PF_TRAIN_TC_MIN_ROWS, default 512)
   bool train_debug;      // PF_TC_DEBUG=1: synchronise and check tg_err after every training call
   int* tg_err;           // device error flag of those kernels (barrier timeout)
   // backward: side stream for the gradients that are off the layer-to-layer chain (fork / join with events)

@@ -96,7 +96,7 @@ extern "C" pf_status pf_flow_create(const pf_flow_desc* d, pf_flow** out) {
     f->train_tc = d->tier == PF_TIER_BF16 && !(tt && tt[0] == '0');
     f->train_debug = dbg && dbg[0] == '1';
     const char* mr = getenv("PF_TRAIN_TC_MIN_ROWS");
-    f->train_tc_min_rows = mr ? atoi(mr) : 2048;
+    f->train_tc_min_rows = mr ? atoi(mr) : 512;
     const char* ts = getenv("PF_TRAIN_STREAMS");
     f->train_streams = !(ts && ts[0] == '0');
   }

@@ -8,16 +8,13 @@
 // so gradients keep ~1e-5 relative accuracy: the training step can use the tensor pipe without giving up the
 // weight-gradient tolerance that a plain bf16 product (2^-9) would.
 //
-// Shape of one CTA (256 threads, 80-96 KB of shared memory: two per SM, so one CTA's operand loads overlap the other's
-// MMAs and epilogue): a 128-row x BN-column output tile, the accumulator is BN columns of
-// tensor memory (lane = output row).  K advances in stages of KS = 128: all threads convert the stage's operands
-// into the UMMA canonical K-major no-swizzle layout in shared memory (8-row x 16-byte core matrices; element
-// (row, k) at (k/8) * ROWS*16 + row*16 + (k%8)*2, i.e. LBO = ROWS*16 along K, SBO = 128 along rows -- the layout
-// verified by tests/umma_probe.cu), one 16-byte store per (row, 8 k) so stores are bank-conflict free; then a
-// converged warp elects one lane to issue the stage's MMAs and a single commit.  The products here have K <= 768
-// (hidden 256, final 517, context 3*256 / 288) or K = rows of a <= 256-row slice (weight gradients): two to six
-// stages of load -> MMA -> wait, the overlap comes from the second resident CTA; the epilogue functor
-// runs on values read back with tcgen05.ld and transposed through shared memory (tg_epilogue).
+// Shape of one CTA (288 threads, 80-96 KB of shared memory, two per SM): a 128-row x BN-column output tile, the
+// accumulator is BN columns of tensor memory (lane = output row).  The contraction advances through a 4-stage ring
+// of 32-element stages: eight producer warps convert operands into the UMMA canonical K-major no-swizzle layout
+// (8-row x 16-byte core matrices; element (row, k) at (k/8) * ROWS*16 + row*16 + (k%8)*2, i.e. LBO = ROWS*16 along K,
+// SBO = 128 along rows -- the layout verified by tests/umma_probe.cu; one 16-byte store per (row, 8 k), bank-conflict
+// free), a ninth, converged warp elects one lane to issue each stage's six MMAs; the epilogue functor runs on values
+// read back with tcgen05.ld and transposed through shared memory so its global accesses are coalesced.
 #pragma once
 #include "pf_common.cuh"
 #include "pf_gemm.cuh"
@@ -25,10 +22,15 @@
 
 namespace pf {
 
-constexpr int TG_ROWS = 128, TG_KS = 128, TG_THREADS = 256;
-constexpr int TG_UB = 8;   // items whose global loads are in flight together per thread
+constexpr int TG_ROWS = 128;       // output rows per CTA = UMMA M = TMEM lanes
+constexpr int TG_KSTG = 32;        // contraction elements per ring stage (two K=16 MMA chunks)
+constexpr int TG_STAGES = 4;       // ring depth
+constexpr int TG_PRODUCERS = 256;  // warps 0-7: operand producers during the main loop, epilogue afterwards
+constexpr int TG_THREADS = TG_PRODUCERS + 32;   // + warp 8: MMA issuer, owns the TMEM allocation
 template <int BN>
-constexpr int tg_smem_bytes() { return 2 * TG_KS * TG_ROWS * 2 + 2 * TG_KS * BN * 2 + 64; }
+__host__ __device__ constexpr int tg_stage_bytes() { return 2 * (TG_KSTG / 8) * (TG_ROWS + BN) * 16; }   // hi + lo of A and B
+template <int BN>
+__host__ __device__ constexpr int tg_smem_bytes() { return TG_STAGES * tg_stage_bytes<BN>() + 128; }
 
 __device__ __forceinline__ void tg_split_store(uint8_t* hi_dst, uint8_t* lo_dst, const float* v) {
   uint32_t h[4], l[4];
@@ -43,247 +45,185 @@ __device__ __forceinline__ void tg_split_store(uint8_t* hi_dst, uint8_t* lo_dst,
   *reinterpret_cast<uint4*>(lo_dst) = make_uint4(l[0], l[1], l[2], l[3]);
 }
 
-// issue the three split-bf16 MMAs of every K=16 chunk of one stage, then one commit (call from a converged warp)
-template <int BN>
-__device__ __forceinline__ void tg_issue_stage(uint32_t tmem, uint32_t aAh, uint32_t aAl, uint32_t aBh, uint32_t aBl,
-                                               int nchunks, bool first_stage, uint64_t* bar) {
-  using namespace sm100;
-  if (elect_one_sync()) {
-    const uint32_t idesc = umma_idesc_bf16(TG_ROWS, BN);
-    uint64_t ah = umma_smem_desc(aAh, TG_ROWS * 16, 128), al = umma_smem_desc(aAl, TG_ROWS * 16, 128);
-    uint64_t bh = umma_smem_desc(aBh, BN * 16, 128), bl = umma_smem_desc(aBl, BN * 16, 128);
-    const uint64_t astep = (uint64_t)((2u * TG_ROWS * 16u) >> 4), bstep = (uint64_t)((2u * (uint32_t)BN * 16u) >> 4);
-    uint32_t accf = first_stage ? 0u : 1u;
-    for (int c = 0; c < nchunks; ++c) {
-      umma_ss(tmem, ah, bh, idesc, accf);
-      umma_ss(tmem, ah, bl, idesc, 1u);
-      umma_ss(tmem, al, bh, idesc, 1u);
-      accf = 1u;
-      ah += astep; al += astep; bh += bstep; bl += bstep;
+// ---- operand sources: 8 consecutive contraction elements of one output row / column ------------------------------
+// NT (forward products, data gradients): both operands are K-contiguous fp32 matrices
+template <int AMODE>
+struct SrcNT {
+  const float* A; int lda; const float* B; int ldb; bool a_vec, b_vec;
+  __device__ __forceinline__ void load8(const float* p, bool vec, int k, int kend, float* v) const {
+    if (vec && k + 8 <= kend) {
+      const float4 x0 = __ldg(reinterpret_cast<const float4*>(p)), x1 = __ldg(reinterpret_cast<const float4*>(p + 4));
+      v[0] = x0.x; v[1] = x0.y; v[2] = x0.z; v[3] = x0.w; v[4] = x1.x; v[5] = x1.y; v[6] = x1.z; v[7] = x1.w;
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = (k + i < kend) ? __ldg(p + i) : 0.f;
     }
-    umma_commit(bar);
   }
-  __syncwarp();
-}
-
-struct TgSmem {
-  uint8_t *Ah, *Al, *Bh, *Bl;
-  uint64_t* bar;
-  uint32_t* tmem_slot;
+  __device__ __forceinline__ void loadA(int row, int k, int kend, float* v) const {
+    load8(A + (int64_t)row * lda + k, a_vec, k, kend, v);
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      v[i] = AMODE == A_RELU ? fmaxf(v[i], 0.f) : (AMODE == A_SANITIZE ? sanitize_ctx(v[i]) : v[i]);
+  }
+  __device__ __forceinline__ void loadB(int row, int k, int kend, float* v) const {
+    load8(B + (int64_t)row * ldb + k, b_vec, k, kend, v);
+  }
 };
-template <int BN>
-__device__ __forceinline__ TgSmem tg_carve(uint8_t* smem) {
-  TgSmem s;
-  s.Ah = smem;
-  s.Al = s.Ah + TG_KS * TG_ROWS * 2;
-  s.Bh = s.Al + TG_KS * TG_ROWS * 2;
-  s.Bl = s.Bh + TG_KS * BN * 2;
-  s.bar = reinterpret_cast<uint64_t*>(s.Bl + TG_KS * BN * 2);
-  s.tmem_slot = reinterpret_cast<uint32_t*>(s.bar + 1);
-  return s;
-}
-
-// prologue / epilogue shared by the two kernels
-template <int BN>
-__device__ __forceinline__ uint32_t tg_begin(const TgSmem& s) {
-  using namespace sm100;
-  if (threadIdx.x == 0) {
-    mbar_init(s.bar, 1);
-    fence_mbar_init();
-  }
-  if ((threadIdx.x >> 5) == 0) {
-    __syncwarp();
-    tmem_alloc(s.tmem_slot, BN < 32 ? 32 : BN);
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  return *s.tmem_slot;
-}
-
-// Epilogue shared by the two kernels: the accumulator tile goes TMEM -> registers (thread = output row, the only
-// shape tcgen05.ld offers) -> shared memory (the operand buffers are free once the last MMA has completed) -> back
-// out with the warp's lanes along the COLUMN index, so the functor's global loads / stores / atomics of one
-// instruction fall into one or two 128-byte lines instead of 32 rows' worth of sectors.
-template <int BN, class F>
-__device__ __forceinline__ void tg_epilogue(uint8_t* smem, uint32_t tmem, int warp, int tid, F&& f) {
-  using namespace sm100;
-  constexpr int LD = BN + 1, HALF = BN / 2;
-  float* stage = reinterpret_cast<float*>(smem);
-  const int row = (warp & 3) * 32 + (tid & 31);
-  const uint32_t tl = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-  const int cbeg = (warp >> 2) * HALF;     // warps 0-3 take columns [0, HALF), warps 4-7 [HALF, BN)
+// TN (weight gradients): the contraction index is the ROW index of both operands, so the source transposes: a thread
+// owns one output row / column n and gathers 8 consecutive m (each of the 8 loads is coalesced across the warp's n)
+template <class LoadA, class LoadB>
+struct SrcTN {
+  LoadA la; LoadB lb;
+  __device__ __forceinline__ void loadA(int row, int k, int kend, float* v) const {
 #pragma unroll
-  for (int c = 0; c < HALF; c += 16) {
-    uint32_t v[16];
-    tmem_ld16(tl + cbeg + c, v);
-    tmem_wait_ld();
+    for (int i = 0; i < 8; ++i) v[i] = (k + i < kend) ? la(k + i, row) : 0.f;
+  }
+  __device__ __forceinline__ void loadB(int row, int k, int kend, float* v) const {
 #pragma unroll
-    for (int i = 0; i < 16; ++i) stage[row * LD + cbeg + c + i] = __uint_as_float(v[i]);
+    for (int i = 0; i < 8; ++i) v[i] = (k + i < kend) ? lb(k + i, row) : 0.f;
   }
-  tc_fence_before();
-  __syncthreads();
-  for (int idx = tid; idx < TG_ROWS * BN; idx += TG_THREADS) {
-    const int r = idx / BN, c = idx % BN;
-    f(r, c, stage[r * LD + c]);
-  }
-}
+};
 
-// C[M,N] = epi( op(A)[M,K] . B[N,K]^T ), both operands K-contiguous fp32 (same contract as sgemm_nt)
-template <class Epi, int AMODE, int BN>
-__global__ void __launch_bounds__(TG_THREADS, 2)
-tc_gemm_nt_kernel(const float* __restrict__ A, int lda, const float* __restrict__ B, int ldb, int M, int N, int K,
-                  Epi epi, int* __restrict__ err) {
+// C[MA, NBc] (+)= epi( sum_k A(row, k) B(col, k) ) over k in this CTA's slice [blockIdx.z * k_per_slice, ...).
+// Warp-specialised: warps 0-7 produce ring stages (global fp32 -> split bf16 -> UMMA layout in shared memory; the
+// loads of stage s+1 are in flight in registers while stage s is converted and stored), warp 8 waits for a full stage,
+// issues its six MMAs and commits them to the stage's `empty` barrier; when the last stage's MMAs have completed the
+// producers turn into the epilogue.
+template <class Src, class Epi, int BN>
+__global__ void __launch_bounds__(TG_THREADS, BN >= 128 ? 1 : 2)
+tc_gemm_kernel(const Src src, int MA, int NBc, int K, int k_per_slice, Epi epi, int* __restrict__ err) {
   using namespace sm100;
   extern __shared__ __align__(128) uint8_t smem[];
-  const TgSmem s = tg_carve<BN>(smem);
-  const uint32_t tmem = tg_begin<BN>(s);
+  constexpr int STG = tg_stage_bytes<BN>();
+  constexpr int KG = TG_KSTG / 8;                       // 8-wide k groups per stage
+  constexpr int A_HALF = KG * TG_ROWS * 16, B_HALF = KG * BN * 16;   // bytes of one (hi or lo) operand image per stage
+  constexpr int ITEMS = (TG_ROWS + BN) * KG;
+  constexpr int IT = (ITEMS + TG_PRODUCERS - 1) / TG_PRODUCERS;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + TG_STAGES * STG);
+  uint64_t* empty = full + TG_STAGES;
+  uint64_t* acc_bar = empty + TG_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
   const int tid = threadIdx.x;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const int m0 = blockIdx.y * TG_ROWS, n0 = blockIdx.x * BN;
-  const bool a_vec = (lda & 3) == 0 && (reinterpret_cast<uintptr_t>(A) & 15) == 0;
-  const bool b_vec = (ldb & 3) == 0 && (reinterpret_cast<uintptr_t>(B) & 15) == 0;
-  uint32_t phase = 0;
-  bool ok = true;
-  for (int k0 = 0; k0 < K && ok; k0 += TG_KS) {
-    const int kc = min(TG_KS, K - k0);
-    const int ngrp = (kc + 15) / 16 * 2;   // 8-wide k groups of this stage (whole K=16 chunks)
-    // A items [0, nA) then B items [nA, nA + nB); an item = one row x 8 consecutive k.  The global loads of TG_UB
-    // items are all issued before the first conversion, so a thread has 2 * TG_UB 16-byte loads in flight (with
-    // one CTA of 8 warps per SM, a load-convert-store loop would expose the full L2 latency per item).
-    const int nA = TG_ROWS * ngrp, nB = BN * ngrp;
-    for (int base = tid; base < nA + nB; base += TG_THREADS * TG_UB) {
-      float v[TG_UB][8];
-#pragma unroll
-      for (int u = 0; u < TG_UB; ++u) {
-        const int idx = base + u * TG_THREADS;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) v[u][i] = 0.f;
-        if (idx < nA + nB) {
-          const bool isA = idx < nA;
-          const int j = isA ? idx : idx - nA;
-          const int r = isA ? (j & (TG_ROWS - 1)) : (j % BN), kg = isA ? (j >> 7) : (j / BN);
-          const int row = (isA ? m0 : n0) + r, k = k0 + kg * 8;
-          if (row < (isA ? M : N)) {
-            const float* p = (isA ? A + (int64_t)row * lda : B + (int64_t)row * ldb) + k;
-            if ((isA ? a_vec : b_vec) && k + 8 <= K) {
-              const float4 x0 = __ldg(reinterpret_cast<const float4*>(p)), x1 = __ldg(reinterpret_cast<const float4*>(p + 4));
-              v[u][0] = x0.x; v[u][1] = x0.y; v[u][2] = x0.z; v[u][3] = x0.w;
-              v[u][4] = x1.x; v[u][5] = x1.y; v[u][6] = x1.z; v[u][7] = x1.w;
-            } else {
-#pragma unroll
-              for (int i = 0; i < 8; ++i)
-                if (k + i < K) v[u][i] = __ldg(p + i);
-            }
-          }
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < TG_UB; ++u) {
-        const int idx = base + u * TG_THREADS;
-        if (idx < nA + nB) {
-          const bool isA = idx < nA;
-          const int j = isA ? idx : idx - nA;
-          const int r = isA ? (j & (TG_ROWS - 1)) : (j % BN), kg = isA ? (j >> 7) : (j / BN);
-          if (isA) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-              v[u][i] = AMODE == A_RELU ? fmaxf(v[u][i], 0.f) : (AMODE == A_SANITIZE ? sanitize_ctx(v[u][i]) : v[u][i]);
-          }
-          const uint32_t off = (uint32_t)kg * ((isA ? TG_ROWS : BN) * 16) + (uint32_t)r * 16;
-          tg_split_store((isA ? s.Ah : s.Bh) + off, (isA ? s.Al : s.Bl) + off, v[u]);
-        }
-      }
-    }
-    fence_proxy_async_smem();
-    __syncthreads();
-    if (warp == 4) {
-      tc_fence_after();
-      tg_issue_stage<BN>(tmem, smem_u32(s.Ah), smem_u32(s.Al), smem_u32(s.Bh), smem_u32(s.Bl), ngrp / 2, k0 == 0, s.bar);
-    }
-    ok = mbar_wait(s.bar, phase);   // MMAs done: shared memory may be rewritten, the accumulator read
-    phase ^= 1;
-    tc_fence_after();
+  const int kbeg = blockIdx.z * k_per_slice;
+  const int kend = min(K, kbeg + k_per_slice);
+  const int nst = kend > kbeg ? (kend - kbeg + TG_KSTG - 1) / TG_KSTG : 0;
+  if (tid == 0) {
+    for (int i = 0; i < TG_STAGES; ++i) { mbar_init(&full[i], TG_PRODUCERS); mbar_init(&empty[i], 1); }
+    mbar_init(acc_bar, 1);
+    fence_mbar_init();
   }
-  if (!ok && tid == 0) atomicExch(err, 60);
-  if (__syncthreads_and(ok)) {
-    tg_epilogue<BN>(smem, tmem, warp, tid, [&](int r, int c, float acc) {
-      const int m = m0 + r, n = n0 + c;
-      if (m < M && n < N) epi(m, n, acc);
-    });
-  }
+  if (warp == 8) tmem_alloc(tmem_slot, BN < 32 ? 32 : BN);
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, BN < 32 ? 32 : BN);
-}
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  bool ok = true;
 
-// C[N1,N2] = epi( sum_m A(m,N1) . B(m,N2) ), split over m in slices (same contract as sgemm_tn: the epilogue
-// accumulates atomically).  The contraction index is the ROW index of both operands, so the loaders transpose on
-// the way into shared memory: a thread owns one n and gathers 8 consecutive m (each of the 8 loads is coalesced
-// across the warp's 32 consecutive n).
-template <class Epi, class LoadA, class LoadB, int BN>
-__global__ void __launch_bounds__(TG_THREADS, 2)
-tc_gemm_tn_kernel(LoadA la, LoadB lb, int M, int N1, int N2, int m_per_slice, Epi epi, int* __restrict__ err) {
-  using namespace sm100;
-  extern __shared__ __align__(128) uint8_t smem[];
-  const TgSmem s = tg_carve<BN>(smem);
-  const uint32_t tmem = tg_begin<BN>(s);
-  const int tid = threadIdx.x;
-  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
-  const int n10 = blockIdx.y * TG_ROWS, n20 = blockIdx.x * BN;
-  const int mbeg = blockIdx.z * m_per_slice;
-  const int mend = min(M, mbeg + m_per_slice);
-  uint32_t phase = 0;
-  bool ok = true;
-  for (int k0 = mbeg; k0 < mend && ok; k0 += TG_KS) {
-    const int kc = min(TG_KS, mend - k0);
-    const int ngrp = (kc + 15) / 16 * 2;
-    const int nA = TG_ROWS * ngrp, nB = BN * ngrp;
-    for (int base = tid; base < nA + nB; base += TG_THREADS * TG_UB) {
-      float v[TG_UB][8];
+  if (warp < 8) {
+    // ============================ producers ============================
+    float cur[IT][8], nxt[IT][8];
+    auto fetch = [&](int s, float (*dst)[8]) {
+      const int k0 = kbeg + s * TG_KSTG;
 #pragma unroll
-      for (int u = 0; u < TG_UB; ++u) {
-        const int idx = base + u * TG_THREADS;
-        const bool isA = idx < nA;
-        const int j = isA ? idx : idx - nA;
-        const int r = isA ? (j & (TG_ROWS - 1)) : (j % BN), kg = isA ? (j >> 7) : (j / BN);
-        const int n = (isA ? n10 : n20) + r, m = k0 + kg * 8;
-        const bool live = idx < nA + nB && n < (isA ? N1 : N2);
+      for (int u = 0; u < IT; ++u) {
+        const int idx = tid + u * TG_PRODUCERS;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) v[u][i] = (live && m + i < mend) ? (isA ? la(m + i, n) : lb(m + i, n)) : 0.f;
-      }
-#pragma unroll
-      for (int u = 0; u < TG_UB; ++u) {
-        const int idx = base + u * TG_THREADS;
-        if (idx < nA + nB) {
-          const bool isA = idx < nA;
-          const int j = isA ? idx : idx - nA;
-          const int r = isA ? (j & (TG_ROWS - 1)) : (j % BN), kg = isA ? (j >> 7) : (j / BN);
-          const uint32_t off = (uint32_t)kg * ((isA ? TG_ROWS : BN) * 16) + (uint32_t)r * 16;
-          tg_split_store((isA ? s.Ah : s.Bh) + off, (isA ? s.Al : s.Bl) + off, v[u]);
+        for (int i = 0; i < 8; ++i) dst[u][i] = 0.f;
+        if (idx < ITEMS) {
+          const bool isA = idx < TG_ROWS * KG;
+          const int j = isA ? idx : idx - TG_ROWS * KG;
+          const int r = isA ? (j & (TG_ROWS - 1)) : (j % BN), kg = isA ? (j / TG_ROWS) : (j / BN);
+          const int row = (isA ? m0 : n0) + r, k = k0 + kg * 8;
+          if (row < (isA ? MA : NBc) && k < kend) {
+            if (isA) src.loadA(row, k, kend, dst[u]);
+            else src.loadB(row, k, kend, dst[u]);
+          }
         }
       }
+    };
+    if (nst > 0) fetch(0, cur);
+    for (int s = 0; s < nst && ok; ++s) {
+      if (s + 1 < nst) fetch(s + 1, nxt);
+      const int slot = s % TG_STAGES;
+      ok = mbar_wait(&empty[slot], ((s / TG_STAGES) & 1) ^ 1);   // a fresh barrier passes a wait on parity 1
+      uint8_t* sb = smem + slot * STG;
+#pragma unroll
+      for (int u = 0; u < IT; ++u) {
+        const int idx = tid + u * TG_PRODUCERS;
+        if (idx < ITEMS) {
+          const bool isA = idx < TG_ROWS * KG;
+          const int j = isA ? idx : idx - TG_ROWS * KG;
+          const int r = isA ? (j & (TG_ROWS - 1)) : (j % BN), kg = isA ? (j / TG_ROWS) : (j / BN);
+          uint8_t* hi = sb + (isA ? 0 : 2 * A_HALF) + (uint32_t)kg * ((isA ? TG_ROWS : BN) * 16) + (uint32_t)r * 16;
+          tg_split_store(hi, hi + (isA ? A_HALF : B_HALF), cur[u]);
+        }
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(&full[slot]);
+#pragma unroll
+      for (int u = 0; u < IT; ++u)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) cur[u][i] = nxt[u][i];
     }
-    fence_proxy_async_smem();
-    __syncthreads();
-    if (warp == 4) {
+  } else {
+    // ============================ MMA issuer (converged warp, one elected lane) ============================
+    const uint32_t idesc = umma_idesc_bf16(TG_ROWS, BN);
+    const uint32_t base = smem_u32(smem);
+    for (int s = 0; s < nst && ok; ++s) {
+      const int slot = s % TG_STAGES;
+      ok = mbar_wait(&full[slot], (s / TG_STAGES) & 1);
       tc_fence_after();
-      tg_issue_stage<BN>(tmem, smem_u32(s.Ah), smem_u32(s.Al), smem_u32(s.Bh), smem_u32(s.Bl), ngrp / 2, k0 == mbeg, s.bar);
+      if (ok && elect_one_sync()) {
+        const uint32_t sa = base + slot * STG;
+        uint64_t ah = umma_smem_desc(sa, TG_ROWS * 16, 128), al = umma_smem_desc(sa + A_HALF, TG_ROWS * 16, 128);
+        uint64_t bh = umma_smem_desc(sa + 2 * A_HALF, BN * 16, 128), bl = umma_smem_desc(sa + 2 * A_HALF + B_HALF, BN * 16, 128);
+        const uint64_t astep = (uint64_t)((2u * TG_ROWS * 16u) >> 4), bstep = (uint64_t)((2u * (uint32_t)BN * 16u) >> 4);
+#pragma unroll
+        for (int c = 0; c < TG_KSTG / 16; ++c) {
+          umma_ss(tmem, ah, bh, idesc, (s > 0 || c > 0) ? 1u : 0u);
+          umma_ss(tmem, ah, bl, idesc, 1u);
+          umma_ss(tmem, al, bh, idesc, 1u);
+          ah += astep; al += astep; bh += bstep; bl += bstep;
+        }
+        umma_commit(&empty[slot]);
+        if (s == nst - 1) umma_commit(acc_bar);
+      }
+      __syncwarp();
     }
-    ok = mbar_wait(s.bar, phase);
-    phase ^= 1;
-    tc_fence_after();
   }
-  if (!ok && tid == 0) atomicExch(err, 61);
-  if (__syncthreads_and(ok) && mbeg < mend) {
-    tg_epilogue<BN>(smem, tmem, warp, tid, [&](int r, int c, float acc) {
-      const int n1 = n10 + r, n2 = n20 + c;
-      if (n1 < N1 && n2 < N2) epi(n1, n2, acc);
-    });
+  if (nst > 0 && ok) ok = mbar_wait(acc_bar, 0);
+  tc_fence_after();
+  if (!ok && (tid & 31) == 0) atomicExch(err, 60 + (warp == 8));
+  ok = __syncthreads_and(ok);
+  if (ok && nst > 0 && warp < 8) {
+    // ============================ epilogue ============================
+    // TMEM -> registers (thread = output row, the only shape tcgen05.ld offers) -> shared memory (the ring is free: every
+    // MMA has completed) -> back out with the warp's lanes along the COLUMN index, so the functor's global loads /
+    // stores / atomics of one instruction fall into one or two 128-byte lines instead of 32 rows' worth of sectors.
+    constexpr int LD = BN + 1, HALF = BN / 2;
+    float* stage = reinterpret_cast<float*>(smem);
+    const int row = (warp & 3) * 32 + (tid & 31);
+    const uint32_t tl = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    const int cbeg = (warp >> 2) * HALF;     // warps 0-3 take columns [0, HALF), warps 4-7 [HALF, BN)
+#pragma unroll
+    for (int c = 0; c < HALF; c += 16) {
+      uint32_t v[16];
+      tmem_ld16(tl + cbeg + c, v);
+      tmem_wait_ld();
+#pragma unroll
+      for (int i = 0; i < 16; ++i) stage[row * LD + cbeg + c + i] = __uint_as_float(v[i]);
+    }
+    bar_sync(1, TG_PRODUCERS);
+    for (int idx = tid; idx < TG_ROWS * BN; idx += TG_PRODUCERS) {
+      const int r = idx / BN, c = idx % BN;
+      if (m0 + r < MA && n0 + c < NBc) epi(m0 + r, n0 + c, stage[r * LD + c]);
+    }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, BN < 32 ? 32 : BN);
+  if (warp == 8) tmem_dealloc(tmem, BN < 32 ? 32 : BN);
 }
 
 // ---- host launchers ---------------------------------------------------------------------------------
@@ -296,50 +236,57 @@ inline pf_status tg_set_smem(int bytes, int dev) {
   return PF_OK;
 }
 
+template <class Src, class Epi, int BN>
+inline pf_status tg_launch(pf_flow* f, cudaStream_t st, const Src& src, int MA, int NBc, int K, int kps, int slices,
+                           const Epi& epi) {
+  PF_TRY((tg_set_smem<tc_gemm_kernel<Src, Epi, BN>>(tg_smem_bytes<BN>(), f->desc.device)));
+  dim3 grid((NBc + BN - 1) / BN, (MA + TG_ROWS - 1) / TG_ROWS, slices);
+  tc_gemm_kernel<Src, Epi, BN><<<grid, TG_THREADS, tg_smem_bytes<BN>(), st>>>(src, MA, NBc, K, kps, epi, f->tg_err);
+  PF_LAUNCH_CHECK(f);
+  return PF_OK;
+}
+
 template <class Epi, int AMODE>
 inline pf_status tc_gemm_nt(pf_flow* f, cudaStream_t st, const float* A, int lda, const float* B, int ldb, int M, int N,
                             int K, const Epi& epi) {
   if (M <= 0 || N <= 0) return PF_OK;
+  const SrcNT<AMODE> src{A, lda, B, ldb, (lda & 3) == 0 && (reinterpret_cast<uintptr_t>(A) & 15) == 0,
+                         (ldb & 3) == 0 && (reinterpret_cast<uintptr_t>(B) & 15) == 0};
   const int mt = (M + TG_ROWS - 1) / TG_ROWS;
-  // 32-column tiles while 64-column ones would leave most SMs without a CTA (the training step's ~1 k rows)
-  if (mt * ((N + 63) / 64) < f->sm_count) {
-    constexpr int BN = 32;
-    PF_TRY((tg_set_smem<tc_gemm_nt_kernel<Epi, AMODE, BN>>(tg_smem_bytes<BN>(), f->desc.device)));
-    dim3 grid((N + BN - 1) / BN, mt);
-    tc_gemm_nt_kernel<Epi, AMODE, BN><<<grid, TG_THREADS, tg_smem_bytes<BN>(), st>>>(A, lda, B, ldb, M, N, K, epi, f->tg_err);
-  } else {
-    constexpr int BN = 64;
-    PF_TRY((tg_set_smem<tc_gemm_nt_kernel<Epi, AMODE, BN>>(tg_smem_bytes<BN>(), f->desc.device)));
-    dim3 grid((N + BN - 1) / BN, mt);
-    tc_gemm_nt_kernel<Epi, AMODE, BN><<<grid, TG_THREADS, tg_smem_bytes<BN>(), st>>>(A, lda, B, ldb, M, N, K, epi, f->tg_err);
-  }
-  PF_LAUNCH_CHECK(f);
-  return PF_OK;
+  // Tile width: every column tile re-reads (and re-converts) the A rows of its row tile, so wide tiles as soon as
+  // they still give most SMs a CTA (7 515 rows x 256 columns: 118 CTAs of 128 x 128 read A twice, 472 CTAs of
+  // 128 x 32 eight times = 61 MB of L2 traffic per product); narrow tiles for the ~1 k-row calls of a sharded batch.
+  if (10 * mt * ((N + 127) / 128) >= 7 * f->sm_count) return tg_launch<SrcNT<AMODE>, Epi, 128>(f, st, src, M, N, K, K, 1, epi);
+  if (mt * ((N + 63) / 64) >= 2 * f->sm_count) return tg_launch<SrcNT<AMODE>, Epi, 64>(f, st, src, M, N, K, K, 1, epi);
+  return tg_launch<SrcNT<AMODE>, Epi, 32>(f, st, src, M, N, K, K, 1, epi);
 }
 
 template <class Epi, class LoadA, class LoadB>
 inline pf_status tc_gemm_tn(pf_flow* f, cudaStream_t st, const LoadA& la, const LoadB& lb, int M, int N1, int N2,
                             const Epi& epi) {
   if (M <= 0 || N1 <= 0 || N2 <= 0) return PF_OK;
-  constexpr int BN = 64;
-  const int tiles = ((N1 + TG_ROWS - 1) / TG_ROWS) * ((N2 + BN - 1) / BN);
-  // rows per slice: 256 (one full stage), 128 when that leaves most of the GPU without a CTA.  Not finer: every
-  // slice adds a full tile of atomics, and these kernels share the GPU with the dependency chain on the main stream.
-  int mps = 256;
-  if (tiles * ((M + mps - 1) / mps) < f->sm_count / 2) mps = 128;
-  const int slices = (M + mps - 1) / mps;
-  PF_TRY((tg_set_smem<tc_gemm_tn_kernel<Epi, LoadA, LoadB, BN>>(tg_smem_bytes<BN>(), f->desc.device)));
-  dim3 grid((N2 + BN - 1) / BN, (N1 + TG_ROWS - 1) / TG_ROWS, slices);
-  tc_gemm_tn_kernel<Epi, LoadA, LoadB, BN><<<grid, TG_THREADS, tg_smem_bytes<BN>(), st>>>(la, lb, M, N1, N2, mps, epi, f->tg_err);
-  PF_LAUNCH_CHECK(f);
-  return PF_OK;
+  const SrcTN<LoadA, LoadB> src{la, lb};
+  // rows per slice: every slice adds a full tile of atomics, and these kernels share the GPU with the dependency
+  // chain on the main stream: about one CTA per SM, never under 128 rows per slice.  128-column tiles for the big
+  // batches (fewer re-reads of the gradient rows), 64-column ones otherwise.
+  auto plan = [&](int BN, int& mps, int& slices) {
+    const int tiles = ((N1 + TG_ROWS - 1) / TG_ROWS) * ((N2 + BN - 1) / BN);
+    slices = (f->sm_count + tiles - 1) / tiles;
+    mps = ((M + slices - 1) / slices + TG_KSTG - 1) / TG_KSTG * TG_KSTG;
+    if (mps < 128) mps = 128;
+    slices = (M + mps - 1) / mps;
+  };
+  int mps, slices;
+  if (M >= 4096 && N2 >= 128) {
+    plan(128, mps, slices);
+    return tg_launch<SrcTN<LoadA, LoadB>, Epi, 128>(f, st, src, N1, N2, M, mps, slices, epi);
+  }
+  plan(64, mps, slices);
+  return tg_launch<SrcTN<LoadA, LoadB>, Epi, 64>(f, st, src, N1, N2, M, mps, slices, epi);
 }
 
 // tier / size dispatch: the FP32 parity tier keeps its FP32-FMA kernels, and so do calls with fewer rows than
-// PF_TRAIN_TC_MIN_ROWS (default 2048).  Measured on B200 (scripts/prof_train.py, one CUDA-graph replay of forward +
-// backward): 7 515 rows (config #4 on one GPU) 10.0 ms with these kernels against 13.9 ms with the FP32-FMA ones;
-// 948 rows (its 8-GPU shard) 4.0 ms against 3.3 ms -- a CTA here is a serial load -> MMA -> epilogue chain and
-// ~64 CTAs cannot hide it, while the FP32 kernels run three double-buffered CTAs per SM.
+// PF_TRAIN_TC_MIN_ROWS (default 512: a 128-row tile of such a call is mostly padding).
 template <class Epi, int AMODE, int BN>
 inline pf_status gemm_nt(pf_flow* f, cudaStream_t st, const float* A, int lda, const float* B, int ldb, int M, int N,
                          int K, const Epi& epi) {

@@ -131,17 +131,19 @@ class GraphedNLLStep:
         if st is None:
             st = self.graphs[cap] = self._capture(cap)
         ctx_full = m._full_context(context[event], rank)          # autograd-tracked (encoder, rank embedding)
-        count = torch.tensor(float(R), device=context.device)
-        if self.distributed:
+        inv_count = 1.0 / R                                      # local mean (train_lean_npe.py:127) ...
+        if self.distributed:                                      # ... or the global one (dist.global_mean_loss)
             from .dist import _world
             import torch.distributed as dist
             if _world()[1] > 1:
+                count = torch.tensor(float(R), device=context.device)
                 dist.all_reduce(count)
+                inv_count = 1.0 / count
         with torch.no_grad():
             st["x"][:R].copy_(m.scaler.normalize(params[event, rank, :]))
             st["ctx"][:R].copy_(ctx_full)
             st["w"].zero_()
-            st["w"][:R] = 1.0 / count
+            st["w"][:R] = inv_count
         st["graph"].replay()
         self.last_launches = st["launches"]
         # the graph's gradient tensors are overwritten by the next replay: hand out copies (two multi-tensor kernels)

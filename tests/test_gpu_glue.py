@@ -242,7 +242,7 @@ def test_graphed_nll_step_matches_batch_nll(tier, monkeypatch):
     replaying the cached graph on a second batch with a different number of rows in the same bucket stays exact,
     and a second call without clearing .grad accumulates."""
     import posteriflow_b200 as P
-    if tier == "bf16":       # capture the split-bf16 tcgen05 GEMMs too (by default they serve calls of >= 2048 rows)
+    if tier == "bf16":       # capture the split-bf16 tcgen05 GEMMs too (by default they serve calls of >= 512 rows)
         monkeypatch.setenv("PF_TRAIN_TC_MIN_ROWS", "0")
     spec, w, g = load_golden("lean_glue")
     m = lean_model(w, g, tier=tier)

@@ -63,7 +63,7 @@ def test_forward_and_nll_match_reference(case):
 def test_backward_matches_reference_autograd(case, tier, monkeypatch):
     """tier="bf16": the training path of the tensor-core tier (split-bf16 tcgen05 GEMMs, pf_tc_gemm.cuh: three MMAs per
     product keep ~16 significand bits), forced on for these small batches (PF_TRAIN_TC_MIN_ROWS=0; by default calls
-    under 2048 rows stay on the FP32-FMA kernels).  Stated tolerance of that path, float64-arbitrated like the FP32
+    under 512 rows stay on the FP32-FMA kernels).  Stated tolerance of that path, float64-arbitrated like the FP32
     one: gradients of x / context within 2e-3 of the gradient's scale, weight-gradient norms within 1e-3, sampled
     weight-gradient entries within 5e-2 of the tensor's rms entry (measured 2.8e-2: the fixture puts inputs exactly ON
     spline knots, where a 1e-5 change of a knot moves a row to the neighbouring bin -- the flow is C1 there, the
