@@ -51,12 +51,17 @@ struct EpiCtxProj {
     out[(int64_t)m * ld + n] = sec == 0 ? fmaxf(v, 0.f) : 1.f / (1.f + expf(-v));
   }
 };
+// Epilogues may split into fetch(m, n) -> operands read from global memory, and apply(m, n, acc, fetched): a caller
+// that handles several elements per thread (pf_tc_gemm.cuh) issues all fetches of a batch before the first apply, so
+// the loads overlap instead of costing one memory latency per element.  operator() stays the single-call form.
 // out[m, n0 + n] = acc + bias[n0 + n]
 struct EpiBias {
   float* out; int ld; const float* bias; int n0;
   __device__ __forceinline__ void operator()(int m, int n, float acc) const {
     out[(int64_t)m * ld + n0 + n] = acc + bias[n0 + n];
   }
+  __device__ __forceinline__ float fetch(int m, int n) const { return bias[n0 + n]; }
+  __device__ __forceinline__ void apply(int m, int n, float acc, float b) const { out[(int64_t)m * ld + n0 + n] = acc + b; }
 };
 // hout = hin + gate * (acc + bias)   (GLU-gated residual, nflows MaskedResidualBlock); optional v store
 struct EpiGluResidual {
@@ -68,6 +73,15 @@ struct EpiGluResidual {
     int64_t i = (int64_t)m * ld + n0 + n;
     if (vout) vout[i] = v;
     hout[i] = hin[i] + g * v;
+  }
+  __device__ __forceinline__ float3 fetch(int m, int n) const {
+    return make_float3(bias[n0 + n], gate[cm(m) * ldg + n0 + n], hin[(int64_t)m * ld + n0 + n]);
+  }
+  __device__ __forceinline__ void apply(int m, int n, float acc, float3 t) const {
+    const float v = acc + t.x;
+    const int64_t i = (int64_t)m * ld + n0 + n;
+    if (vout) vout[i] = v;
+    hout[i] = t.z + t.y * v;
   }
 };
 
@@ -658,6 +672,10 @@ struct EpiReluMaskStore {  // out = pre > 0 ? acc : 0
     int64_t i = (int64_t)m * ld + n;
     out[i] = pre[i] > 0.f ? acc : 0.f;
   }
+  __device__ __forceinline__ float fetch(int m, int n) const { return pre[(int64_t)m * ld + n]; }
+  __device__ __forceinline__ void apply(int m, int n, float acc, float p) const {
+    out[(int64_t)m * ld + n] = p > 0.f ? acc : 0.f;
+  }
 };
 struct EpiReluMaskAdd {  // out += pre > 0 ? acc : 0
   float* out; const float* pre; int ld;
@@ -665,12 +683,21 @@ struct EpiReluMaskAdd {  // out += pre > 0 ? acc : 0
     int64_t i = (int64_t)m * ld + n;
     if (pre[i] > 0.f) out[i] += acc;
   }
+  __device__ __forceinline__ float2 fetch(int m, int n) const {
+    const int64_t i = (int64_t)m * ld + n;
+    return make_float2(pre[i], out[i]);
+  }
+  __device__ __forceinline__ void apply(int m, int n, float acc, float2 t) const {
+    if (t.x > 0.f) out[(int64_t)m * ld + n] = t.y + acc;
+  }
 };
 struct EpiGxOut {  // Gnext[m, D-1-n] = acc + GXd[m, n]   (undo the layer's ReversePermutation)
   float* out; const float* gxd; int D;
   __device__ __forceinline__ void operator()(int m, int n, float acc) const {
     out[(int64_t)m * D + (D - 1 - n)] = acc + gxd[(int64_t)m * D + n];
   }
+  __device__ __forceinline__ float fetch(int m, int n) const { return gxd[(int64_t)m * D + n]; }
+  __device__ __forceinline__ void apply(int m, int n, float acc, float g) const { out[(int64_t)m * D + (D - 1 - n)] = acc + g; }
 };
 struct EpiCtxAtomic {  // gctx[ctx(m), n] += acc
   float* out; int C; CtxMap cm;

@@ -16,6 +16,9 @@
 // free), a ninth, converged warp elects one lane to issue each stage's six MMAs; the epilogue functor runs on values
 // read back with tcgen05.ld and transposed through shared memory so its global accesses are coalesced.
 #pragma once
+#include <type_traits>
+#include <utility>
+
 #include "pf_common.cuh"
 #include "pf_gemm.cuh"
 #include "pf_sm100.cuh"
@@ -27,6 +30,11 @@ constexpr int TG_KSTG = 32;        // contraction elements per ring stage (two K
 constexpr int TG_STAGES = 4;       // ring depth
 constexpr int TG_PRODUCERS = 256;  // warps 0-7: operand producers during the main loop, epilogue afterwards
 constexpr int TG_THREADS = TG_PRODUCERS + 32;   // + warp 8: MMA issuer, owns the TMEM allocation
+constexpr int TG_EU = 8;           // epilogue elements per thread whose global reads are in flight together
+template <class E, class = void>
+struct tg_has_fetch : std::false_type {};
+template <class E>
+struct tg_has_fetch<E, std::void_t<decltype(std::declval<const E&>().fetch(0, 0))>> : std::true_type {};
 template <int BN>
 __host__ __device__ constexpr int tg_stage_bytes() { return 2 * (TG_KSTG / 8) * (TG_ROWS + BN) * 16; }   // hi + lo of A and B
 template <int BN>
@@ -216,9 +224,29 @@ tc_gemm_kernel(const Src src, int MA, int NBc, int K, int k_per_slice, Epi epi, 
       for (int i = 0; i < 16; ++i) stage[row * LD + cbeg + c + i] = __uint_as_float(v[i]);
     }
     bar_sync(1, TG_PRODUCERS);
-    for (int idx = tid; idx < TG_ROWS * BN; idx += TG_PRODUCERS) {
-      const int r = idx / BN, c = idx % BN;
-      if (m0 + r < MA && n0 + c < NBc) epi(m0 + r, n0 + c, stage[r * LD + c]);
+    if constexpr (tg_has_fetch<Epi>::value) {
+      // the functor's global reads of TG_EU elements are issued together, then applied (one memory latency per
+      // batch instead of one per element: with a single resident CTA there are few other warps to hide it)
+      using Fetched = decltype(epi.fetch(0, 0));
+      for (int base = tid; base < TG_ROWS * BN; base += TG_PRODUCERS * TG_EU) {
+        Fetched t[TG_EU];
+#pragma unroll
+        for (int u = 0; u < TG_EU; ++u) {
+          const int idx = base + u * TG_PRODUCERS, r = idx / BN, c = idx % BN;
+          if (idx < TG_ROWS * BN && m0 + r < MA && n0 + c < NBc) t[u] = epi.fetch(m0 + r, n0 + c);
+        }
+#pragma unroll
+        for (int u = 0; u < TG_EU; ++u) {
+          const int idx = base + u * TG_PRODUCERS, r = idx / BN, c = idx % BN;
+          if (idx < TG_ROWS * BN && m0 + r < MA && n0 + c < NBc) epi.apply(m0 + r, n0 + c, stage[r * LD + c], t[u]);
+        }
+      }
+    } else {
+#pragma unroll 4
+      for (int idx = tid; idx < TG_ROWS * BN; idx += TG_PRODUCERS) {
+        const int r = idx / BN, c = idx % BN;
+        if (m0 + r < MA && n0 + c < NBc) epi(m0 + r, n0 + c, stage[r * LD + c]);
+      }
     }
   }
   tc_fence_before();
