@@ -130,7 +130,9 @@ class GraphedNLLStep:
         st = self.graphs.get(cap)
         if st is None:
             st = self.graphs[cap] = self._capture(cap)
-        ctx_full = m._full_context(context[event], rank)          # autograd-tracked (encoder, rank embedding)
+        # LeanNPE._full_context(context[event], rank), spelled with index_select: same values, and the backward is one
+        # index_add kernel per operand instead of the sort-based index_put / embedding backward (~25 small kernels)
+        ctx_full = torch.cat([context.index_select(0, event), m.rank_embed.weight.index_select(0, rank)], dim=1)
         inv_count = 1.0 / R                                      # local mean (train_lean_npe.py:127) ...
         if self.distributed:                                      # ... or the global one (dist.global_mean_loss)
             from .dist import _world
