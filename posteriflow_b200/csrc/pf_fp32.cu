@@ -691,6 +691,31 @@ struct EpiReluMaskAdd {  // out += pre > 0 ? acc : 0
     if (t.x > 0.f) out[(int64_t)m * ld + n] = t.y + acc;
   }
 };
+// Data-gradient epilogue fused with the elementwise kernel that used to follow it on the dependency chain:
+//   g = acc (pre == NULL: final-layer data gradient)  or  gh + [pre > 0] acc (second Linear of a residual block);  gh = g;
+//   then, with t = tvec[ctx(m), n]:  V != NULL: GLU backward of the block below (glu_bwd_kernel): gv = g t,
+//   gproj[m, sec H + n] = g V t (1 - t);   V == NULL: relu(context_layer) backward (ctx_relu_bwd_kernel):
+//   gproj[m, n] = [t > 0] g.
+struct EpiGradFuse {
+  float* gh; const float* pre; int ld;
+  const float* V; const float* tvec; int64_t ldt; CtxMap cm; float* gv; float* gproj; int ldgp; int sec;
+  __device__ __forceinline__ float4 fetch(int m, int n) const {
+    const int64_t i = (int64_t)m * ld + n;
+    return make_float4(pre ? pre[i] : 1.f, pre ? gh[i] : 0.f, tvec[cm(m) * ldt + n], V ? V[i] : 0.f);
+  }
+  __device__ __forceinline__ void apply(int m, int n, float acc, float4 f) const {
+    const int64_t i = (int64_t)m * ld + n;
+    const float g = pre ? (f.x > 0.f ? f.y + acc : f.y) : acc;
+    if (!pre || f.x > 0.f) gh[i] = g;
+    if (V) {
+      gv[i] = g * f.z;
+      gproj[(int64_t)m * ldgp + sec * ld + n] = g * f.w * f.z * (1.f - f.z);
+    } else {
+      gproj[(int64_t)m * ldgp + n] = f.z > 0.f ? g : 0.f;
+    }
+  }
+  __device__ __forceinline__ void operator()(int m, int n, float acc) const { apply(m, n, acc, fetch(m, n)); }
+};
 struct EpiGxOut {  // Gnext[m, D-1-n] = acc + GXd[m, n]   (undo the layer's ReversePermutation)
   float* out; const float* gxd; int D;
   __device__ __forceinline__ void operator()(int m, int n, float acc) const {
@@ -813,25 +838,21 @@ extern "C" pf_status pf_flow_backward(pf_flow* f, const void* saved, const float
     // ---- chain ----
     // 1. spline: d(params), direct d(x)
     PF_NB_DISPATCH(f->NB, PF_TRY(launch_spline_bwd<NB_>(f, st, xin, Pl, R, gy, glogdet, b.gp, ws.gxd)));
-    // 2. final layer
-    PF_TRY((gemm_nt<EpiStore, A_PLAIN, 64>(f, st, b.gp, PLD, f->WfT + (size_t)l * H * PLD, PLD, R, H, P,
-                                           EpiStore{b.gh, H})));
-    // 3. residual blocks, last first
+    // 2. final layer (+ GLU backward of block 1 in its epilogue)
+    PF_TRY((gemm_nt<EpiGradFuse, A_PLAIN, 64>(
+        f, st, b.gp, PLD, f->WfT + (size_t)l * H * PLD, PLD, R, H, P,
+        EpiGradFuse{b.gh, nullptr, H, V2, pl + (size_t)2 * H, ldproj, cm, b.gv[1], b.gproj, 3 * H, 2})));
+    // 3. residual blocks, last first: d relu(u) = gv Wb, then gh += [h > 0] (gu Wa) with, in the same epilogue, the
+    //    GLU backward of block 0 (after block 1) or the relu(context_layer) backward (after block 0)
     for (int k = 1; k >= 0; --k) {
       const float* Hin = k ? H1 : H0;
       const float* U = k ? U2 : U1;
-      const float* V = k ? V2 : V1;
-      glu_bwd_kernel<<<gRH, 256, 0, st>>>(b.gh, V, pl + (size_t)(k + 1) * H, ldproj, cm, R, H, b.gv[k], b.gproj, 3 * H,
-                                          k + 1);
-      PF_LAUNCH_CHECK(f);
       PF_TRY((gemm_nt<EpiReluMaskStore, A_PLAIN, 64>(f, st, b.gv[k], H, f->WbT + ((size_t)l * 2 + k) * H * H, H, R, H, H,
                                                      EpiReluMaskStore{b.gu[k], U, H})));
-      PF_TRY((gemm_nt<EpiReluMaskAdd, A_PLAIN, 64>(f, st, b.gu[k], H, f->WaT + ((size_t)l * 2 + k) * H * H, H, R, H, H,
-                                                   EpiReluMaskAdd{b.gh, Hin, H})));
+      const EpiGradFuse epi = k ? EpiGradFuse{b.gh, Hin, H, V1, pl + (size_t)H, ldproj, cm, b.gv[0], b.gproj, 3 * H, 1}
+                                : EpiGradFuse{b.gh, Hin, H, nullptr, pl, ldproj, cm, nullptr, b.gproj, 3 * H, 0};
+      PF_TRY((gemm_nt<EpiGradFuse, A_PLAIN, 64>(f, st, b.gu[k], H, f->WaT + ((size_t)l * 2 + k) * H * H, H, R, H, H, epi)));
     }
-    // 4. initial layer + relu(context_layer)
-    ctx_relu_bwd_kernel<<<gRH, 256, 0, st>>>(b.gh, pl, ldproj, cm, R, H, b.gproj, 3 * H);
-    PF_LAUNCH_CHECK(f);
     float* gout = (l == 0) ? gx : gnext;
     if (gout)
       PF_TRY((gemm_nt<EpiGxOut, A_PLAIN, 32>(f, st, b.gh, H, f->W0T + (size_t)l * f->DP * H, H, R, D, H,
