@@ -108,8 +108,9 @@ struct pf_flow {
   bool train_debug;      // PF_TC_DEBUG=1: synchronise and check tg_err after every training call
   int* tg_err;           // device error flag of those kernels (barrier timeout)
   // backward: side stream for the gradients that are off the layer-to-layer chain (fork / join with events)
-  cudaStream_t side;
-  cudaEvent_t ev_main[2], ev_side[2];
+  static constexpr int NSIDE = 4;   // final layer | residual block 1 | residual block 0 | initial layer + context path
+  cudaStream_t side[NSIDE];
+  cudaEvent_t ev_main[2], ev_side[2][NSIDE];
   bool train_streams;    // PF_TRAIN_STREAMS != 0
 };
 

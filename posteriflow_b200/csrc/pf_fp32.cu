@@ -609,28 +609,6 @@ spline_bwd_kernel(const float* __restrict__ Xin, const float* __restrict__ P, in
       rqs_forward_backward<NB>(RegParams{q}, x, B, gy, gl, GradStore{GP + (int64_t)r * PLD + j * MULT});
 }
 
-// GLU-residual backward, elementwise: h_out = h_in + g * v
-//   GV = GH * g ;  GPROJ[:, sec*H + u] = GH * v * g * (1 - g)      (GH itself is d(h_in) via the residual)
-__global__ void glu_bwd_kernel(const float* __restrict__ GH, const float* __restrict__ V,
-                               const float* __restrict__ gate, int64_t ldg, CtxMap cm, int R, int H,
-                               float* __restrict__ GV, float* __restrict__ GPROJ, int ldgp, int sec) {
-  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (int64_t)R * H) return;
-  int r = (int)(idx / H), u = (int)(idx % H);
-  float gh = GH[idx], g = gate[cm(r) * ldg + u];
-  GV[idx] = gh * g;
-  GPROJ[(int64_t)r * ldgp + sec * H + u] = gh * V[idx] * g * (1.f - g);
-}
-
-// relu(context_layer) backward: GPROJ[:, u] = GH0 * [c0 > 0]
-__global__ void ctx_relu_bwd_kernel(const float* __restrict__ GH, const float* __restrict__ c0, int64_t ldc, CtxMap cm,
-                                    int R, int H, float* __restrict__ GPROJ, int ldgp) {
-  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (int64_t)R * H) return;
-  int r = (int)(idx / H), u = (int)(idx % H);
-  GPROJ[(int64_t)r * ldgp + u] = c0[cm(r) * ldc + u] > 0.f ? GH[idx] : 0.f;
-}
-
 // dst[map(c)] += sum_r src[r, c]   (bias gradients); grid (ceil(ncols/32), slabs), block (32, 8)
 struct ColMap {
   const int* perm; int H; int sections;  // sections > 0: c -> (c / H) selects dst pointer, perm on c % H
@@ -693,9 +671,9 @@ struct EpiReluMaskAdd {  // out += pre > 0 ? acc : 0
 };
 // Data-gradient epilogue fused with the elementwise kernel that used to follow it on the dependency chain:
 //   g = acc (pre == NULL: final-layer data gradient)  or  gh + [pre > 0] acc (second Linear of a residual block);  gh = g;
-//   then, with t = tvec[ctx(m), n]:  V != NULL: GLU backward of the block below (glu_bwd_kernel): gv = g t,
-//   gproj[m, sec H + n] = g V t (1 - t);   V == NULL: relu(context_layer) backward (ctx_relu_bwd_kernel):
-//   gproj[m, n] = [t > 0] g.
+//   then, with t = tvec[ctx(m), n]:  V != NULL: GLU backward of the block below (h_out = h_in + t v, t = sigmoid
+//   gate): gv = g t, gproj[m, sec H + n] = g V t (1 - t);   V == NULL: relu(context_layer) backward, t = relu'd
+//   context term c0: gproj[m, n] = [t > 0] g.
 struct EpiGradFuse {
   float* gh; const float* pre; int ld;
   const float* V; const float* tvec; int64_t ldt; CtxMap cm; float* gv; float* gproj; int ldgp; int sec;
@@ -813,14 +791,16 @@ extern "C" pf_status pf_flow_backward(pf_flow* f, const void* saved, const float
   if (!ws.ok) return PF_ERR_WORKSPACE;
   CtxMap cm{row2ctx, n_per_ctx, 0};
   const int* perm = f->d_perm;
-  const int64_t nRH = (int64_t)R * H;
-  const unsigned gRH = (unsigned)((nRH + 255) / 256);
 
-  // Two streams: `st` carries the dependency chain (spline backward and the data gradients, 10 kernels per layer),
-  // `sd` (the handle's side stream, forked from and joined back into `st` with events, so the pair is capturable
-  // in a CUDA graph) the 13 kernels per layer whose results nobody downstream waits for.
-  const bool two = f->side != nullptr && f->train_streams;
-  cudaStream_t sd = two ? f->side : st;
+  // `st` carries the dependency chain (spline backward and the data gradients, 7 kernels per layer); the 13 kernels per
+  // layer whose results nobody downstream waits for go to the handle's four side streams, forked from and joined back
+  // into `st` with events (capturable in a CUDA graph): s0 final-layer weight / bias gradient, s1 / s2 the two residual
+  // blocks', s3 initial layer + context path.  All of these kernels are latency-bound at a sharded batch's row count,
+  // so running several at a time is what fills the GPU (948 rows, one graph replay: 1 stream 3.95 ms, 2 streams 3.27,
+  // 3 streams 2.39 with the tcgen05 GEMMs).
+  const bool two = f->side[0] != nullptr && f->train_streams;
+  cudaStream_t sx[pf_flow::NSIDE];
+  for (int j = 0; j < pf_flow::NSIDE; ++j) sx[j] = two ? f->side[j] : st;
   const float* gy = gz;      // gradient wrt the current layer's output
   float* gnext = ws.ga;
   for (int l = L - 1; l >= 0; --l) {
@@ -834,7 +814,8 @@ extern "C" pf_status pf_flow_backward(pf_flow* f, const void* saved, const float
     const float* Pl = sv.P + (size_t)l * R * PLD;
     const float* pl = sv.proj + (size_t)l * 3 * H;
     // this parity's buffers were last read by the side work of layer l+2
-    if (two && l + 2 <= L - 1) PF_CUDA(cudaStreamWaitEvent(st, f->ev_side[par], 0));
+    if (two && l + 2 <= L - 1)
+      for (int j = 0; j < pf_flow::NSIDE; ++j) PF_CUDA(cudaStreamWaitEvent(st, f->ev_side[par][j], 0));
     // ---- chain ----
     // 1. spline: d(params), direct d(x)
     PF_NB_DISPATCH(f->NB, PF_TRY(launch_spline_bwd<NB_>(f, st, xin, Pl, R, gy, glogdet, b.gp, ws.gxd)));
@@ -859,47 +840,48 @@ extern "C" pf_status pf_flow_backward(pf_flow* f, const void* saved, const float
                                              EpiGxOut{gout, ws.gxd, D})));
     if (two) {
       PF_CUDA(cudaEventRecord(f->ev_main[par], st));
-      PF_CUDA(cudaStreamWaitEvent(sd, f->ev_main[par], 0));
+      for (int j = 0; j < pf_flow::NSIDE; ++j) PF_CUDA(cudaStreamWaitEvent(sx[j], f->ev_main[par], 0));
     }
     // ---- off the chain: weight, bias and context gradients of this layer ----
     if (g && g->final_w)
-      PF_TRY((gemm_tn(f, sd, LoadPlain{b.gp, PLD}, LoadPlain{H2, H}, R, P, H,
+      PF_TRY((gemm_tn(f, sx[0], LoadPlain{b.gp, PLD}, LoadPlain{H2, H}, R, P, H,
                       EpiWgrad{g->final_w, H, nullptr, perm, RULE_FINAL, D, MULT})));
-    if (g && g->final_b) PF_TRY(colsum(f, sd, b.gp, PLD, R, P, ColMap{nullptr, H, 0, {g->final_b, nullptr, nullptr}}));
+    if (g && g->final_b) PF_TRY(colsum(f, sx[0], b.gp, PLD, R, P, ColMap{nullptr, H, 0, {g->final_b, nullptr, nullptr}}));
     for (int k = 1; k >= 0; --k) {
       const float* Hin = k ? H1 : H0;
       const float* U = k ? U2 : U1;
       if (g && g->blk_lin_w[k][1])
-        PF_TRY((gemm_tn(f, sd, LoadPlain{b.gv[k], H}, LoadRelu{U, H}, R, H, H,
+        PF_TRY((gemm_tn(f, sx[2 - k], LoadPlain{b.gv[k], H}, LoadRelu{U, H}, R, H, H,
                         EpiWgrad{g->blk_lin_w[k][1], H, perm, perm, RULE_HIDDEN, D, MULT})));
       if (g && g->blk_lin_b[k][1])
-        PF_TRY(colsum(f, sd, b.gv[k], H, R, H, ColMap{perm, H, 0, {g->blk_lin_b[k][1], nullptr, nullptr}}));
+        PF_TRY(colsum(f, sx[2 - k], b.gv[k], H, R, H, ColMap{perm, H, 0, {g->blk_lin_b[k][1], nullptr, nullptr}}));
       if (g && g->blk_lin_w[k][0])
-        PF_TRY((gemm_tn(f, sd, LoadPlain{b.gu[k], H}, LoadRelu{Hin, H}, R, H, H,
+        PF_TRY((gemm_tn(f, sx[2 - k], LoadPlain{b.gu[k], H}, LoadRelu{Hin, H}, R, H, H,
                         EpiWgrad{g->blk_lin_w[k][0], H, perm, perm, RULE_HIDDEN, D, MULT})));
       if (g && g->blk_lin_b[k][0])
-        PF_TRY(colsum(f, sd, b.gu[k], H, R, H, ColMap{perm, H, 0, {g->blk_lin_b[k][0], nullptr, nullptr}}));
+        PF_TRY(colsum(f, sx[2 - k], b.gu[k], H, R, H, ColMap{perm, H, 0, {g->blk_lin_b[k][0], nullptr, nullptr}}));
     }
     if (g && g->initial_w)
-      PF_TRY((gemm_tn(f, sd, LoadPlain{b.gh, H}, LoadRev{xin, D}, R, H, D,
+      PF_TRY((gemm_tn(f, sx[3], LoadPlain{b.gh, H}, LoadRev{xin, D}, R, H, D,
                       EpiWgrad{g->initial_w, D, perm, nullptr, RULE_INITIAL, D, MULT})));
-    if (g && g->initial_b) PF_TRY(colsum(f, sd, b.gh, H, R, H, ColMap{perm, H, 0, {g->initial_b, nullptr, nullptr}}));
+    if (g && g->initial_b) PF_TRY(colsum(f, sx[3], b.gh, H, R, H, ColMap{perm, H, 0, {g->initial_b, nullptr, nullptr}}));
     // context path: d(ctx) and the three context Linear layers
     if (gctx)
-      PF_TRY((gemm_nt<EpiCtxAtomic, A_PLAIN, 64>(f, sd, b.gproj, 3 * H, f->WctxT + (size_t)l * 3 * H, (int)ldproj, R,
+      PF_TRY((gemm_nt<EpiCtxAtomic, A_PLAIN, 64>(f, sx[3], b.gproj, 3 * H, f->WctxT + (size_t)l * 3 * H, (int)ldproj, R,
                                                  C, 3 * H, EpiCtxAtomic{gctx, C, cm})));
     if (g && (g->ctx_w || g->blk_ctx_w[0] || g->blk_ctx_w[1]))
-      PF_TRY((gemm_tn(f, sd, LoadPlain{b.gproj, 3 * H}, LoadCtx{ctx, C, cm}, R, 3 * H, C,
+      PF_TRY((gemm_tn(f, sx[3], LoadPlain{b.gproj, 3 * H}, LoadCtx{ctx, C, cm}, R, 3 * H, C,
                       EpiWgradCtx{{g->ctx_w, g->blk_ctx_w[0], g->blk_ctx_w[1]}, C, H, perm})));
     if (g && (g->ctx_b || g->blk_ctx_b[0] || g->blk_ctx_b[1]))
-      PF_TRY(colsum(f, sd, b.gproj, 3 * H, R, 3 * H, ColMap{perm, H, 3, {g->ctx_b, g->blk_ctx_b[0], g->blk_ctx_b[1]}}));
-    if (two) PF_CUDA(cudaEventRecord(f->ev_side[par], sd));
+      PF_TRY(colsum(f, sx[3], b.gproj, 3 * H, R, 3 * H, ColMap{perm, H, 3, {g->ctx_b, g->blk_ctx_b[0], g->blk_ctx_b[1]}}));
+    if (two)
+      for (int j = 0; j < pf_flow::NSIDE; ++j) PF_CUDA(cudaEventRecord(f->ev_side[par][j], sx[j]));
     gy = gnext;
     gnext = (gnext == ws.ga) ? ws.gb : ws.ga;
   }
   if (two) {   // join: everything the side stream produced is ordered before what follows on `st`
-    PF_CUDA(cudaStreamWaitEvent(st, f->ev_side[0], 0));
-    if (L > 1) PF_CUDA(cudaStreamWaitEvent(st, f->ev_side[1], 0));
+    for (int i = 0; i < (L > 1 ? 2 : 1); ++i)
+      for (int j = 0; j < pf_flow::NSIDE; ++j) PF_CUDA(cudaStreamWaitEvent(st, f->ev_side[i][j], 0));
   }
   return train_tc_check(f, st, "pf_flow_backward");
 }

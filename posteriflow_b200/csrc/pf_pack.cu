@@ -131,10 +131,11 @@ extern "C" pf_status pf_flow_create(const pf_flow_desc* d, pf_flow** out) {
   if (e == cudaSuccess) e = cudaMalloc(&f->d_flag, sizeof(int));
   if (e == cudaSuccess) e = cudaMalloc(&f->tg_err, sizeof(int));
   if (e == cudaSuccess) e = cudaMemset(f->tg_err, 0, sizeof(int));
-  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&f->side, cudaStreamNonBlocking);
+  for (int j = 0; j < pf_flow::NSIDE && e == cudaSuccess; ++j) e = cudaStreamCreateWithFlags(&f->side[j], cudaStreamNonBlocking);
   for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
     e = cudaEventCreateWithFlags(&f->ev_main[i], cudaEventDisableTiming);
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&f->ev_side[i], cudaEventDisableTiming);
+    for (int j = 0; j < pf_flow::NSIDE && e == cudaSuccess; ++j)
+      e = cudaEventCreateWithFlags(&f->ev_side[i][j], cudaEventDisableTiming);
   }
   if (e == cudaSuccess) e = cudaMemcpy(f->d_perm, f->perm_host, H * sizeof(int), cudaMemcpyHostToDevice);
   if (e != cudaSuccess) {
@@ -160,9 +161,11 @@ extern "C" void pf_flow_destroy(pf_flow* f) {
   if (f->tg_err) cudaFree(f->tg_err);
   for (int i = 0; i < 2; ++i) {
     if (f->ev_main[i]) cudaEventDestroy(f->ev_main[i]);
-    if (f->ev_side[i]) cudaEventDestroy(f->ev_side[i]);
+    for (int j = 0; j < pf_flow::NSIDE; ++j)
+      if (f->ev_side[i][j]) cudaEventDestroy(f->ev_side[i][j]);
   }
-  if (f->side) cudaStreamDestroy(f->side);
+  for (int j = 0; j < pf_flow::NSIDE; ++j)
+    if (f->side[j]) cudaStreamDestroy(f->side[j]);
   delete[] f->perm_host;
   delete f;
 }

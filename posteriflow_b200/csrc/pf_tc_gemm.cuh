@@ -97,8 +97,12 @@ struct SrcTN {
 // loads of stage s+1 are in flight in registers while stage s is converted and stored), warp 8 waits for a full stage,
 // issues its six MMAs and commits them to the stage's `empty` barrier; when the last stage's MMAs have completed the
 // producers turn into the epilogue.
-template <class Src, class Epi, int BN>
-__global__ void __launch_bounds__(TG_THREADS, BN >= 128 ? 1 : 2)
+// PD = ring stages whose global loads a producer thread keeps in flight in registers ahead of the one it converts.
+// Every launch uses PD = 1: PD = 2 (one CTA per SM, twice the bytes in flight) was measured on the 64-CTA launches of a
+// ~1 k-row call and changed nothing (2.357 vs 2.367 ms per training step) -- those kernels are bound by their fixed
+// prologue / first-load / epilogue latencies and the launch gap, not by the main loop.
+template <class Src, class Epi, int BN, int PD>
+__global__ void __launch_bounds__(TG_THREADS, (BN >= 128 || PD > 1) ? 1 : 2)
 tc_gemm_kernel(const Src src, int MA, int NBc, int K, int k_per_slice, Epi epi, int* __restrict__ err) {
   using namespace sm100;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -131,7 +135,8 @@ tc_gemm_kernel(const Src src, int MA, int NBc, int K, int k_per_slice, Epi epi, 
 
   if (warp < 8) {
     // ============================ producers ============================
-    float cur[IT][8], nxt[IT][8];
+    constexpr int NBUF = PD + 1;
+    float buf[NBUF][IT][8];
     auto fetch = [&](int s, float (*dst)[8]) {
       const int k0 = kbeg + s * TG_KSTG;
 #pragma unroll
@@ -151,29 +156,33 @@ tc_gemm_kernel(const Src src, int MA, int NBc, int K, int k_per_slice, Epi epi, 
         }
       }
     };
-    if (nst > 0) fetch(0, cur);
-    for (int s = 0; s < nst && ok; ++s) {
-      if (s + 1 < nst) fetch(s + 1, nxt);
-      const int slot = s % TG_STAGES;
-      ok = mbar_wait(&empty[slot], ((s / TG_STAGES) & 1) ^ 1);   // a fresh barrier passes a wait on parity 1
-      uint8_t* sb = smem + slot * STG;
 #pragma unroll
-      for (int u = 0; u < IT; ++u) {
-        const int idx = tid + u * TG_PRODUCERS;
-        if (idx < ITEMS) {
-          const bool isA = idx < TG_ROWS * KG;
-          const int j = isA ? idx : idx - TG_ROWS * KG;
-          const int r = isA ? (j & (TG_ROWS - 1)) : (j % BN), kg = isA ? (j / TG_ROWS) : (j / BN);
-          uint8_t* hi = sb + (isA ? 0 : 2 * A_HALF) + (uint32_t)kg * ((isA ? TG_ROWS : BN) * 16) + (uint32_t)r * 16;
-          tg_split_store(hi, hi + (isA ? A_HALF : B_HALF), cur[u]);
+    for (int p = 0; p < PD; ++p)
+      if (p < nst) fetch(p, buf[p]);
+    for (int s0 = 0; s0 < nst && ok; s0 += NBUF) {
+#pragma unroll
+      for (int jb = 0; jb < NBUF; ++jb) {      // unrolled: the register buffers are indexed statically
+        const int s = s0 + jb;
+        if (s < nst && ok) {
+          if (s + PD < nst) fetch(s + PD, buf[(jb + PD) % NBUF]);
+          const int slot = s % TG_STAGES;
+          ok = mbar_wait(&empty[slot], ((s / TG_STAGES) & 1) ^ 1);   // a fresh barrier passes a wait on parity 1
+          uint8_t* sb = smem + slot * STG;
+#pragma unroll
+          for (int u = 0; u < IT; ++u) {
+            const int idx = tid + u * TG_PRODUCERS;
+            if (idx < ITEMS) {
+              const bool isA = idx < TG_ROWS * KG;
+              const int j = isA ? idx : idx - TG_ROWS * KG;
+              const int r = isA ? (j & (TG_ROWS - 1)) : (j % BN), kg = isA ? (j / TG_ROWS) : (j / BN);
+              uint8_t* hi = sb + (isA ? 0 : 2 * A_HALF) + (uint32_t)kg * ((isA ? TG_ROWS : BN) * 16) + (uint32_t)r * 16;
+              tg_split_store(hi, hi + (isA ? A_HALF : B_HALF), buf[jb][u]);
+            }
+          }
+          fence_proxy_async_smem();
+          mbar_arrive(&full[slot]);
         }
       }
-      fence_proxy_async_smem();
-      mbar_arrive(&full[slot]);
-#pragma unroll
-      for (int u = 0; u < IT; ++u)
-#pragma unroll
-        for (int i = 0; i < 8; ++i) cur[u][i] = nxt[u][i];
     }
   } else {
     // ============================ MMA issuer (converged warp, one elected lane) ============================
@@ -264,12 +273,12 @@ inline pf_status tg_set_smem(int bytes, int dev) {
   return PF_OK;
 }
 
-template <class Src, class Epi, int BN>
+template <class Src, class Epi, int BN, int PD = 1>
 inline pf_status tg_launch(pf_flow* f, cudaStream_t st, const Src& src, int MA, int NBc, int K, int kps, int slices,
                            const Epi& epi) {
-  PF_TRY((tg_set_smem<tc_gemm_kernel<Src, Epi, BN>>(tg_smem_bytes<BN>(), f->desc.device)));
+  PF_TRY((tg_set_smem<tc_gemm_kernel<Src, Epi, BN, PD>>(tg_smem_bytes<BN>(), f->desc.device)));
   dim3 grid((NBc + BN - 1) / BN, (MA + TG_ROWS - 1) / TG_ROWS, slices);
-  tc_gemm_kernel<Src, Epi, BN><<<grid, TG_THREADS, tg_smem_bytes<BN>(), st>>>(src, MA, NBc, K, kps, epi, f->tg_err);
+  tc_gemm_kernel<Src, Epi, BN, PD><<<grid, TG_THREADS, tg_smem_bytes<BN>(), st>>>(src, MA, NBc, K, kps, epi, f->tg_err);
   PF_LAUNCH_CHECK(f);
   return PF_OK;
 }
