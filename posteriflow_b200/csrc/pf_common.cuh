@@ -112,6 +112,7 @@ struct pf_flow {
   cudaStream_t side[NSIDE];
   cudaEvent_t ev_main[2], ev_side[2][NSIDE];
   bool train_streams;    // PF_TRAIN_STREAMS != 0
+  bool train_pdl;        // PF_TRAIN_PDL != 0: programmatic dependent launch of the tcgen05 training GEMMs
 };
 
 // bf16 tensor-core tier entry points (pf_tc.cu)

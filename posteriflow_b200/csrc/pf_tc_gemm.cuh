@@ -132,6 +132,10 @@ tc_gemm_kernel(const Src src, int MA, int NBc, int K, int k_per_slice, Epi epi, 
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   bool ok = true;
+  // Programmatic dependent launch: this grid may have been started while its predecessor in the stream was still
+  // running (its barrier setup and TMEM allocation above overlap the predecessor's tail and the launch latency);
+  // nothing the predecessor wrote is read before this point.  No-op for a normally launched grid.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
 
   if (warp < 8) {
     // ============================ producers ============================
@@ -210,6 +214,7 @@ tc_gemm_kernel(const Src src, int MA, int NBc, int K, int k_per_slice, Epi epi, 
       __syncwarp();
     }
   }
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // the successor may set itself up during our epilogue
   if (nst > 0 && ok) ok = mbar_wait(acc_bar, 0);
   tc_fence_after();
   if (!ok && (tid & 31) == 0) atomicExch(err, 60 + (warp == 8));
@@ -278,6 +283,21 @@ inline pf_status tg_launch(pf_flow* f, cudaStream_t st, const Src& src, int MA, 
                            const Epi& epi) {
   PF_TRY((tg_set_smem<tc_gemm_kernel<Src, Epi, BN, PD>>(tg_smem_bytes<BN>(), f->desc.device)));
   dim3 grid((NBc + BN - 1) / BN, (MA + TG_ROWS - 1) / TG_ROWS, slices);
+  if (f->train_pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(TG_THREADS);
+    cfg.dynamicSmemBytes = tg_smem_bytes<BN>();
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    PF_CUDA(cudaLaunchKernelEx(&cfg, tc_gemm_kernel<Src, Epi, BN, PD>, src, MA, NBc, K, kps, epi, f->tg_err));
+    f->launches++;
+    return PF_OK;
+  }
   tc_gemm_kernel<Src, Epi, BN, PD><<<grid, TG_THREADS, tg_smem_bytes<BN>(), st>>>(src, MA, NBc, K, kps, epi, f->tg_err);
   PF_LAUNCH_CHECK(f);
   return PF_OK;
