@@ -20,6 +20,35 @@
 
 namespace pf {
 
+// Launch of a kernel on the training dependency chain: with programmatic dependent launch (tensor-core tier) the grid
+// may start while its predecessor in the stream drains; such kernels execute griddepcontrol.wait before their first
+// global read (a no-op under a normal launch).
+template <class... KArgs, class... Args>
+static pf_status launch_chain(pf_flow* f, void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, Args... args) {
+  if (f->train_tc && f->train_pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    PF_CUDA(cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...));
+    f->launches++;
+    return PF_OK;
+  }
+  kernel<<<grid, block, 0, st>>>(KArgs(args)...);
+  PF_LAUNCH_CHECK(f);
+  return PF_OK;
+}
+__device__ __forceinline__ void chain_kernel_entry() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
 // ------------------------------------------------------------------------------------------------
 // workspace carving
 // ------------------------------------------------------------------------------------------------
@@ -92,6 +121,7 @@ struct EpiGluResidual {
 __global__ void initial_kernel(const float* __restrict__ X, int ldx, int reversed, int D, const float* __restrict__ W0,
                                int DP, const float* __restrict__ b0, const float* __restrict__ c0, int64_t ldc,
                                CtxMap cm, int R, int u0, int nu, int kmax, float* __restrict__ Hout, int ldh) {
+  chain_kernel_entry();
   int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (int64_t)R * nu) return;
   int r = (int)(idx / nu), u = u0 + (int)(idx % nu);
@@ -114,6 +144,7 @@ template <int NB>
 __global__ void __launch_bounds__(256)
 spline_fwd_kernel(const float* __restrict__ Xin, const float* __restrict__ P, int PLD, int D, float B, int R,
                   float* __restrict__ Y, float* __restrict__ logdet, int accumulate) {
+  chain_kernel_entry();
   constexpr int MULT = 3 * NB - 1;
   const int j = threadIdx.x;
   const int r = blockIdx.x * 16 + threadIdx.y;
@@ -316,10 +347,8 @@ template <int NB>
 static pf_status launch_spline_fwd(pf_flow* f, cudaStream_t st, const float* Xin, const float* P, int R, float* Y,
                                    float* logdet, int accumulate) {
   dim3 block(16, 16);
-  spline_fwd_kernel<NB><<<cdiv(R, 16), block, 0, st>>>(Xin, P, f->PLD, f->D, f->desc.tail_bound, R, Y, logdet,
-                                                       accumulate);
-  PF_LAUNCH_CHECK(f);
-  return PF_OK;
+  return launch_chain(f, spline_fwd_kernel<NB>, dim3(cdiv(R, 16)), block, st, Xin, P, f->PLD, f->D, f->desc.tail_bound, R,
+                      Y, logdet, accumulate);
 }
 
 extern "C" pf_status pf_flow_forward(pf_flow* f, const float* x, const float* ctx, const int64_t* row2ctx,
@@ -404,10 +433,8 @@ extern "C" pf_status pf_flow_forward(pf_flow* f, const float* x, const float* ct
       const float* pl = proj + (size_t)l * 3 * H;
       {
         int64_t n = (int64_t)rows * H;
-        initial_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(xin, D, 1, D, f->W0 + (size_t)l * H * f->DP, f->DP,
-                                                                   f->b0 + (size_t)l * H, pl, ldproj, cm, rows, 0, H, D,
-                                                                   H0, H);
-        PF_LAUNCH_CHECK(f);
+        PF_TRY(launch_chain(f, initial_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), st, xin, D, 1, D,
+                            f->W0 + (size_t)l * H * f->DP, f->DP, f->b0 + (size_t)l * H, pl, ldproj, cm, rows, 0, H, D, H0, H));
       }
       const float* Wa1 = f->Wa + ((size_t)l * 2 + 0) * H * H; const float* ba1 = f->ba + ((size_t)l * 2 + 0) * H;
       const float* Wb1 = f->Wb + ((size_t)l * 2 + 0) * H * H; const float* bb1 = f->bb + ((size_t)l * 2 + 0) * H;
@@ -594,6 +621,7 @@ __global__ void __launch_bounds__(256)
 spline_bwd_kernel(const float* __restrict__ Xin, const float* __restrict__ P, int PLD, int D, float B, int R,
                   const float* __restrict__ GY, const float* __restrict__ GL, float* __restrict__ GP,
                   float* __restrict__ GXd) {
+  chain_kernel_entry();
   constexpr int MULT = 3 * NB - 1;
   const int j = threadIdx.x;
   const int r = blockIdx.x * 16 + threadIdx.y;
@@ -766,9 +794,8 @@ template <int NB>
 static pf_status launch_spline_bwd(pf_flow* f, cudaStream_t st, const float* Xin, const float* P, int R,
                                    const float* GY, const float* GL, float* GP, float* GXd) {
   dim3 block(16, 16);
-  spline_bwd_kernel<NB><<<cdiv(R, 16), block, 0, st>>>(Xin, P, f->PLD, f->D, f->desc.tail_bound, R, GY, GL, GP, GXd);
-  PF_LAUNCH_CHECK(f);
-  return PF_OK;
+  return launch_chain(f, spline_bwd_kernel<NB>, dim3(cdiv(R, 16)), block, st, Xin, P, f->PLD, f->D, f->desc.tail_bound, R,
+                      GY, GL, GP, GXd);
 }
 
 }  // namespace pf
