@@ -5,10 +5,12 @@
 // Accuracy: operands arrive as fp32 and are split on the fly into TWO bf16 terms, a = a_hi + a_lo
 // (a_lo = bf16(a - a_hi): 16 significand bits survive), and every K=16 chunk issues three MMAs
 //     acc += a_hi b_hi + a_hi b_lo + a_lo b_hi            (the a_lo b_lo term, ~2^-18 |ab|, is dropped)
-// so gradients keep ~1e-5 relative accuracy: the training step can use the tensor pipe without giving up the
-// weight-gradient tolerance that a plain bf16 product (2^-9) would.
+// so a product keeps ~1e-5 relative accuracy against 2^-9 for a plain bf16 one.  Measured on the training step
+// (tests/test_gpu_parity.py, tier="bf16"): median error of the gradients 5-7x the float32 reference's own distance from
+// float64; gradients of x / context within 2e-3 of their scale, weight-gradient norms within 1e-3.
 //
-// Shape of one CTA (288 threads, 80-96 KB of shared memory, two per SM): a 128-row x BN-column output tile, the
+// Shape of one CTA (288 threads; 80-96 KB of shared memory and two CTAs per SM with 32- / 64-column tiles, 128 KB and
+// one per SM with 128-column tiles): a 128-row x BN-column output tile, the
 // accumulator is BN columns of tensor memory (lane = output row).  The contraction advances through a 4-stage ring
 // of 32-element stages: eight producer warps convert operands into the UMMA canonical K-major no-swizzle layout
 // (8-row x 16-byte core matrices; element (row, k) at (k/8) * ROWS*16 + row*16 + (k%8)*2, i.e. LBO = ROWS*16 along K,
