@@ -33,6 +33,8 @@ constexpr int TG_STAGES = 4;       // ring depth
 constexpr int TG_PRODUCERS = 256;  // warps 0-7: operand producers during the main loop, epilogue afterwards
 constexpr int TG_THREADS = TG_PRODUCERS + 32;   // + warp 8: MMA issuer, owns the TMEM allocation
 constexpr int TG_EU = 8;           // epilogue elements per thread whose global reads are in flight together
+                                   // (16 for the 32-column tiles -- their whole share in one batch -- measured slower:
+                                   //  2.61 vs 2.28 ms per 948-row training step)
 template <class E, class = void>
 struct tg_has_fetch : std::false_type {};
 template <class E>
