@@ -11,8 +11,9 @@
  *   - every pointer is a DEVICE pointer on the device given at pf_flow_create, unless it is
  *     marked [host]; all tensors are dense row-major float32 unless stated.
  *   - the caller allocates every input, output and workspace buffer; the library owns only the
- *     opaque packed-weights handle.  No call synchronises the stream except pf_flow_pack
- *     (mask validation) and pf_flow_create/destroy.
+ *     opaque packed-weights handle.  No call synchronises the stream except pf_flow_create/destroy,
+ *     pf_flow_check, and pf_flow_pack when mask buffers are handed in (validation) or a source
+ *     pointer changed since the previous pack (its job table is re-uploaded).
  *   - all work is enqueued on the given cudaStream_t (passed as void*; 0 = legacy default).
  *   - return value: PF_OK (0) or a negative pf_status; never throws, never exits.
  *   - one in-flight call per (handle, stream); handles are independent of each other.
@@ -138,8 +139,17 @@ void pf_flow_destroy(pf_flow* flow);
  * implicit weight layout: masks are pre-multiplied, hidden units are sorted by autoregressive
  * degree (block-triangular masks), transposed copies are made for the backward GEMMs and the
  * sampler's per-degree weight blocks are laid out in streaming order.  Call again after every
- * optimizer step / load_state_dict.  `layers` is a [host] array of L structs. */
+ * optimizer step / load_state_dict: a re-pack from unchanged pointers is three kernel launches, does not
+ * synchronise and may be captured in a CUDA graph.  `layers` is a [host] array of L structs. */
 pf_status pf_flow_pack(pf_flow* flow, const pf_layer_ptrs* layers, void* stream);
+
+/* Barrier-timeout flag of the handle's tensor-core kernels.  A tcgen05 kernel whose internal producer/consumer
+ * protocol times out (a bug, or a wedged SM) raises a flag in pinned host memory, writes NaN into every output row
+ * of the tiles it abandons, and exits; the call that launched it has long returned PF_OK by then.  The flag is
+ * reported -- PF_ERR_CUDA, text in pf_last_cuda_error() -- by the NEXT compute call on the handle (without any
+ * synchronisation) and by pf_flow_check, which synchronises `stream` first.  Reading clears it.
+ * (No reference counterpart: PyTorch kernels cannot fail this way.) */
+pf_status pf_flow_check(pf_flow* flow, void* stream);
 
 /* ---- context projection -------------------------------------------------------------------- */
 

@@ -57,6 +57,13 @@ __host__ __device__ __forceinline__ float rule_mask(int rule, int r, int c, int 
   }
 }
 
+// Raise the handle's error flag from a kernel (pinned mapped host memory: plain store + system fence; the first
+// code to land wins often enough -- the flag only has to be non-zero).
+__device__ __forceinline__ void raise_flag(int* err, int code) {
+  *reinterpret_cast<volatile int*>(err) = code;
+  __threadfence_system();
+}
+
 // Row -> context-row addressing shared by every kernel (see header comment in the public .h).
 struct CtxMap {
   const int64_t* row2ctx;
@@ -105,8 +112,15 @@ struct pf_flow {
   // training path of the tensor-core tier (pf_tc_gemm.cuh): split-bf16 tcgen05 GEMMs instead of the FP32-FMA ones
   bool train_tc;         // tier == PF_TIER_BF16 and PF_TRAIN_TC != 0
   int train_tc_min_rows; // calls with fewer flow rows stay on the FP32-FMA GEMMs (PF_TRAIN_TC_MIN_ROWS, default 512)
-  bool train_debug;      // PF_TC_DEBUG=1: synchronise and check tg_err after every training call
-  int* tg_err;           // device error flag of those kernels (barrier timeout)
+  bool train_debug;      // PF_TC_DEBUG=1: synchronise and check the error flag after every tensor-core call
+  // Error flag of every tcgen05 kernel of this handle (barrier timeout = protocol bug or a wedged SM).  It lives in
+  // pinned, mapped HOST memory: a kernel raises it with a system-scope store, the host reads it WITHOUT a stream
+  // synchronisation at the start of the next call on the handle and in pf_flow_check().  `tg_err` is the device
+  // alias of `h_err`.
+  int* tg_err;
+  volatile int* h_err;
+  void* pack_state;      // host-side packer state (pf_pack.cu: cached job table)
+  bool arena_zeroed;     // the packed arena's pad entries are zero-filled once (first pf_flow_pack)
   // backward: side stream for the gradients that are off the layer-to-layer chain (fork / join with events)
   static constexpr int NSIDE = 4;   // final layer | residual block 1 | residual block 0 | initial layer + context path
   cudaStream_t side[NSIDE];
@@ -114,6 +128,10 @@ struct pf_flow {
   bool train_streams;    // PF_TRAIN_STREAMS != 0
   bool train_pdl;        // PF_TRAIN_PDL != 0: programmatic dependent launch of the tcgen05 training GEMMs
 };
+
+// Host side of the error flag: non-blocking read (+ clear).  PF_ERR_CUDA with a message when a kernel of an EARLIER,
+// already finished call on this handle hit a barrier timeout.
+pf_status pf_check_flag(pf_flow* f, const char* where);
 
 // bf16 tensor-core tier entry points (pf_tc.cu)
 pf_status pf_tc_pack(pf_flow* f, cudaStream_t st);

@@ -263,15 +263,8 @@ static pf_status train_tc_check(pf_flow* f, cudaStream_t st, const char* where) 
   if (!f->train_tc || !f->train_debug) return PF_OK;
   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
   if (cudaStreamIsCapturing(st, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) return PF_OK;  // no sync inside a capture
-  int herr = 0;
   PF_CUDA(cudaStreamSynchronize(st));
-  PF_CUDA(cudaMemcpy(&herr, f->tg_err, sizeof(int), cudaMemcpyDeviceToHost));
-  if (herr) {
-    snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: tensor-core GEMM barrier timeout, code %d", where, herr);
-    cudaMemset(f->tg_err, 0, sizeof(int));
-    return PF_ERR_CUDA;
-  }
-  return PF_OK;
+  return pf_check_flag(f, where);
 }
 
 static pf_status check_call(pf_flow* f, int64_t R, int64_t E, const int64_t* row2ctx, int64_t n_per_ctx) {
@@ -283,7 +276,8 @@ static pf_status check_call(pf_flow* f, int64_t R, int64_t E, const int64_t* row
     if (R > 0 && (R - 1) / n_per_ctx >= E) return PF_ERR_INVALID;  // not enough context rows
   }
   if (E > 8000000) return PF_ERR_INVALID;
-  return PF_OK;
+  // a barrier timeout of an earlier, finished call on this handle surfaces here (no stream synchronisation)
+  return pf_check_flag(f, "previous call");
 }
 
 extern "C" pf_status pf_flow_ctxproj(pf_flow* f, const float* ctx, int64_t E, uint32_t flags, float* proj,

@@ -3,13 +3,18 @@
 // (lean_npe.py:326-332) for tiles of 128 flow rows, with every conditioner matrix product on tcgen05.mma
 // (bf16 operands, fp32 accumulation in tensor memory) and the rational-quadratic spline in fp32 registers.
 //
-// Per CTA (one per SM, 192 threads):
-//   warps 0-3  "row" warps: thread t owns flow row t of the tile = TMEM lane t.  They read accumulators with
-//              tcgen05.ld, apply bias / context / GLU / residual / relu or the spline inverse, and write the
-//              next stage's A operand (bf16) back to tensor memory (tcgen05.st) or shared memory.
-//   warp 4     lane 0 issues every tcgen05.mma + tcgen05.commit; the warp also owns the TMEM allocation.
-//   warp 5     lane 0 streams the pre-laid-out bf16 weight blobs (UMMA canonical K-major layout, built by
-//              pf_tc_pack) from L2 into a shared-memory ring with cp.async.bulk + mbarrier complete_tx.
+// Per CTA (one per SM, 352 threads = 11 warps):
+//   warps 0-7  "row" warps, TWO threads per flow row (warps 0-3 = half 0, 4-7 = half 1; both halves cover TMEM lanes
+//              0..127, lane window = warp % 4).  They read accumulators with tcgen05.ld, apply bias / context / GLU /
+//              residual / relu or the spline inverse, and write the next stage's A operand (bf16) back to tensor
+//              memory (tcgen05.st) or shared memory.  Hidden stages: each half owns half of the group's bf16 words;
+//              spline stage: half 1 turns the width logits into knots while half 0 searches the bin and solves.
+//   warp 8     MMA issuer: stays converged, one elect.sync lane issues every tcgen05.mma + tcgen05.commit; the warp
+//              also owns the TMEM allocation.
+//   warp 9     weight loader: streams the pre-laid-out bf16 weight blobs (UMMA canonical K-major layout, built by
+//              pf_tc_pack) from L2 into a 3-slot shared-memory ring with cp.async.bulk + mbarrier complete_tx.
+//   warp 10    constants stager: up to 3 steps ahead, copies the step's biases and the tile's (<= 2) events' context
+//              terms into shared memory so that no global-load latency sits on the dependency chain.
 //
 // Hidden units are sorted by autoregressive degree and every degree group is padded to GSP (even) slots, so
 // a masked matrix restricted to "rows of degree d" is a dense [GSP x GSP*d] block: step d of a layer needs
@@ -65,7 +70,6 @@ struct TcState {
   float* arena;          // padded-order fp32 side arrays
   float *b0p, *bap, *bbp;   // [L][KTOT], [L][2][KTOT], [L][2][KTOT]
   float *Wctxp, *bctxp;     // [L*3*KTOT][C], [L*3*KTOT]
-  int* err;              // device error flag (protocol timeouts)
   TcItem* d_items; int n_items;
   int kernel_smem;
   bool debug_sync;
@@ -82,11 +86,48 @@ __device__ __forceinline__ int tc_slot_to_sorted(const TcShape& s, int slot) {
   return i < n ? s.off[g] + i : -1;
 }
 
-__global__ void tc_pack_image_kernel(TcShape s, const TcItem* __restrict__ items, uint8_t* __restrict__ image,
+// padded-order side arrays of one layer: dst[row][slot] = src[row][sorted(slot)] or 0
+struct TcPadArgs {
+  const float *b0, *ba, *bb, *bctx, *Wctx;   // packed (degree-sorted) fp32 arrays of the handle
+  float *b0p, *bap, *bbp, *bctxp, *Wctxp;    // padded-slot copies
+  int H, C;
+};
+constexpr int TC_PAD_BLOCKS = 48;
+
+// blockIdx.y = layer.  Blocks [0, n_items): one weight blob each (UMMA canonical K-major layout, program order).
+// Blocks [n_items, n_items + TC_PAD_BLOCKS): the layer's slices of the padded side arrays (biases, context weights).
+__global__ void tc_pack_image_kernel(TcShape s, const TcItem* __restrict__ items, int n_items, uint8_t* __restrict__ image,
                                      const float* __restrict__ W0, int DP, const float* __restrict__ Wa,
-                                     const float* __restrict__ Wb, const float* __restrict__ Wf, int H) {
-  const TcItem it = items[blockIdx.x];
+                                     const float* __restrict__ Wb, const float* __restrict__ Wf, int H, TcPadArgs pa) {
   const int l = blockIdx.y;
+  if ((int)blockIdx.x >= n_items) {
+    const int KT = s.KTOT, C = pa.C;
+    // vector rows of this layer: b0 (1 row), ba (2), bb (2), bctx (3) = 8 rows of KT; then 3*KT context-weight rows of C
+    const int nvec = 8 * KT;
+    const int64_t total = (int64_t)nvec + (int64_t)3 * KT * C;
+    for (int64_t i = (int64_t)(blockIdx.x - n_items) * blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)TC_PAD_BLOCKS * blockDim.x) {
+      if (i < nvec) {
+        const int row = (int)(i / KT), col = tc_slot_to_sorted(s, (int)(i % KT));
+        const float* src; float* dst; int srow, nrow;
+        if (row < 1) { src = pa.b0; dst = pa.b0p; srow = row; nrow = 1; }
+        else if (row < 3) { src = pa.ba; dst = pa.bap; srow = row - 1; nrow = 2; }
+        else if (row < 5) { src = pa.bb; dst = pa.bbp; srow = row - 3; nrow = 2; }
+        else { src = pa.bctx; dst = pa.bctxp; srow = row - 5; nrow = 3; }
+        const size_t r = (size_t)l * nrow + srow;
+        dst[r * KT + i % KT] = col >= 0 ? src[r * pa.H + col] : 0.f;
+      } else {
+        const int64_t k = i - nvec;
+        const int c = (int)(k % C);
+        const int rs = (int)(k / C);                   // sec * KT + slot
+        const int sec = rs / KT, col = tc_slot_to_sorted(s, rs % KT);
+        const size_t srow = ((size_t)l * 3 + sec);
+        pa.Wctxp[(srow * KT + rs % KT) * C + c] = col >= 0 ? pa.Wctx[(srow * pa.H + col) * C + c] : 0.f;
+      }
+    }
+    return;
+  }
+  const TcItem it = items[blockIdx.x];
   __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(image + (size_t)l * s.layer_bytes + it.off);
   const int K = it.nc * 16, N = it.N;
   const int gsz = it.d <= s.G ? s.off[it.d] - s.off[it.d - 1] : 0;
@@ -108,24 +149,6 @@ __global__ void tc_pack_image_kernel(TcShape s, const TcItem* __restrict__ items
     }
     dst[(k / 8) * (N * 8) + (n / 8) * 64 + (n % 8) * 8 + (k % 8)] = __float2bfloat16(v);
   }
-}
-
-// padded-order side arrays: dst[row][slot] = src[row][sorted(slot)] or 0
-__global__ void tc_pad_vec_kernel(TcShape s, const float* __restrict__ src, int H, float* __restrict__ dst, int rows) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= rows * s.KTOT) return;
-  int row = i / s.KTOT, col = tc_slot_to_sorted(s, i % s.KTOT);
-  dst[i] = col >= 0 ? src[(size_t)row * H + col] : 0.f;
-}
-// dst[(sec*KTOT + slot)][c] = src[(sec*H + sorted(slot))][c]
-__global__ void tc_pad_rows_kernel(TcShape s, const float* __restrict__ src, int H, int C, float* __restrict__ dst,
-                                   int sections) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= (int64_t)sections * s.KTOT * C) return;
-  int c = (int)(i % C);
-  int64_t rs = i / C;
-  int sec = (int)(rs / s.KTOT), col = tc_slot_to_sorted(s, (int)(rs % s.KTOT));
-  dst[i] = col >= 0 ? src[((size_t)sec * H + col) * C + c] : 0.f;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -246,7 +269,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
       if ((i & 255) == 255 && *abort_s) return false;
     }
     *abort_s = 1;
-    atomicExch(a.err, code);
+    raise_flag(a.err, code);
     return false;
   };
 
@@ -310,7 +333,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
       }
     };
     bool ok = !(lvl == -12 || lvl == -13);
-    for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
+    int tile = blockIdx.x;
+    for (; tile < a.n_tiles && ok; tile += gridDim.x) {
       const int64_t grow = (int64_t)tile * TC_ROWS + r;
       const bool valid = grow < a.R;
       float* y0 = ybuf + r * D;                 // ybuf[0][r][:]
@@ -635,6 +659,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
         if (a.logdet) a.logdet[grow] = ld_acc;
       }
     }
+    if (!ok && half == 0) {
+      // The CTA gave up (barrier timeout, flag raised): a timeout must never pass as data -- every row of the tile it
+      // abandoned and of the tiles it will not reach is written as NaN.
+      for (; tile < a.n_tiles; tile += gridDim.x) {
+        const int64_t grow = (int64_t)tile * TC_ROWS + r;
+        if (grow >= a.R) continue;
+        for (int jj = 0; jj < D; ++jj) a.x[grow * D + jj] = __int_as_float(0x7fc00000);
+        if (a.logdet) a.logdet[grow] = __int_as_float(0x7fc00000);
+        if (a.railed) a.railed[grow] = 0;
+      }
+    }
     if (prof) {
       for (int i = 0; i < 6; ++i) { a.prof[i] = pw[i]; a.prof[6 + i] = pc[i]; }
       a.prof[15] = clock64() - t_begin;
@@ -663,7 +698,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
               const int ngrp = ms == 0 ? 2 : 1;            // stage 0 has two item groups: F then I
               const int n0 = tc_nchunks(s, d, st0), n1 = ms == 0 ? tc_nchunks(s, d, ST_I) : 0;
               if (n0 + n1 == 0) continue;                 // step 1: bias-only F, fp32-only I
-              if (nstage++ == a.dbg_stop) { *abort_s = 1; ok = false; break; }
+              if (nstage++ == a.dbg_stop) {      // PF_TC_STOP: forced protocol failure (tests, bring-up)
+                *abort_s = 1;
+                ok = false;
+                if (elect_one_sync()) raise_flag(a.err, 99);
+                __syncwarp();
+                break;
+              }
               long long t0 = mprof ? clock64() : 0;
               if (!(ok = wait(&full[slot], full_par, 30))) break;   // first item's weights (prefetched long ago)
               if (!(ok = wait(op_bar, op_par, 20 + st0))) break;
@@ -900,14 +941,11 @@ pf_status pf_tc_pack(pf_flow* f, cudaStream_t st) {
     size_t nf = L * KT + 2 * (L * 2 * KT) + L * 3 * KT * C + L * 3 * KT;
     cudaError_t e = cudaMalloc(&t->image, L * s.layer_bytes);
     if (e == cudaSuccess) e = cudaMalloc(&t->arena, nf * sizeof(float));
-    if (e == cudaSuccess) e = cudaMalloc(&t->err, sizeof(int));
     if (e == cudaSuccess) e = cudaMalloc(&t->d_items, items.size() * sizeof(TcItem));
     if (e == cudaSuccess) e = cudaMemcpy(t->d_items, items.data(), items.size() * sizeof(TcItem), cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = cudaMemset(t->err, 0, sizeof(int));
     if (e != cudaSuccess) {
       if (t->image) cudaFree(t->image);
       if (t->arena) cudaFree(t->arena);
-      if (t->err) cudaFree(t->err);
       if (t->d_items) cudaFree(t->d_items);
       delete t;
       return cuda_fail(e, "tensor-core tier allocation", __FILE__, __LINE__);
@@ -920,31 +958,17 @@ pf_status pf_tc_pack(pf_flow* f, cudaStream_t st) {
     t->bctxp = p;
     f->tc = t;
   }
-  dim3 grid(t->n_items, f->L);
-  tc_pack_image_kernel<<<grid, 256, 0, st>>>(s, t->d_items, t->image, f->W0, f->DP, f->Wa, f->Wb, f->Wf, f->H);
+  dim3 grid(t->n_items + TC_PAD_BLOCKS, f->L);
+  TcPadArgs pa{f->b0, f->ba, f->bb, f->bctx, f->Wctx, t->b0p, t->bap, t->bbp, t->bctxp, t->Wctxp, f->H, f->C};
+  tc_pack_image_kernel<<<grid, 256, 0, st>>>(s, t->d_items, t->n_items, t->image, f->W0, f->DP, f->Wa, f->Wb, f->Wf, f->H, pa);
   PF_LAUNCH_CHECK(f);
-  auto padvec = [&](const float* src, float* dst, int rows) -> pf_status {
-    int n = rows * s.KTOT;
-    tc_pad_vec_kernel<<<(n + 255) / 256, 256, 0, st>>>(s, src, f->H, dst, rows);
-    PF_LAUNCH_CHECK(f);
-    return PF_OK;
-  };
-  PF_TRY(padvec(f->b0, t->b0p, f->L));
-  PF_TRY(padvec(f->ba, t->bap, f->L * 2));
-  PF_TRY(padvec(f->bb, t->bbp, f->L * 2));
-  PF_TRY(padvec(f->bctx, t->bctxp, f->L * 3));
-  {
-    int64_t n = (int64_t)f->L * 3 * s.KTOT * f->C;
-    tc_pad_rows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(s, f->Wctx, f->H, f->C, t->Wctxp, f->L * 3);
-    PF_LAUNCH_CHECK(f);
-  }
   return PF_OK;
 }
 
 void pf_tc_destroy(pf_flow* f) {
   TcState* t = reinterpret_cast<TcState*>(f->tc);
   if (!t) return;
-  cudaFree(t->image); cudaFree(t->arena); cudaFree(t->err); cudaFree(t->d_items);
+  cudaFree(t->image); cudaFree(t->arena); cudaFree(t->d_items);
   if (t->prof) cudaFree(t->prof);
   delete t;
   f->tc = nullptr;
@@ -1046,7 +1070,7 @@ static pf_status tc_run(pf_flow* f, cudaStream_t st, bool inverse, const float* 
     a.railed = railed ? railed + r0 : nullptr;
     a.flags = flags; a.tail = f->desc.tail_bound; a.clamp = f->desc.clamp_bound;
     a.sc = sc;
-    a.err = t->err;
+    a.err = f->tg_err;
     a.prof = t->prof;
     {
       const char* stop = getenv("PF_TC_STOP");
@@ -1073,14 +1097,8 @@ static pf_status tc_run(pf_flow* f, cudaStream_t st, bool inverse, const float* 
     fprintf(stderr, "[pf_tc prof] MMA thread: issue loops %lld cycles for %lld MMAs, commits %lld\n", h[16], h[18], h[17]);
   }
   if (t->debug_sync) {
-    int herr = 0;
     PF_CUDA(cudaStreamSynchronize(st));
-    PF_CUDA(cudaMemcpy(&herr, t->err, sizeof(int), cudaMemcpyDeviceToHost));
-    if (herr) {
-      snprintf(g_cuda_err, sizeof(g_cuda_err), "tensor-core sampler: barrier timeout, code %d", herr);
-      cudaMemset(t->err, 0, sizeof(int));
-      return PF_ERR_CUDA;
-    }
+    PF_TRY(pf_check_flag(f, "tensor-core sampler"));
   }
   return PF_OK;
 }
@@ -1104,16 +1122,10 @@ pf_status pf_tc_forward(pf_flow* f, cudaStream_t st, const float* x, const float
   TcState* t = reinterpret_cast<TcState*>(f->tc);
   const char* dn = getenv("PF_TC_DENSE");
   if (f->dense && t && !(fl & PF_FLAG_CTX_IS_PROJ) && !(dn && dn[0] == '0')) {
-    PF_TRY(pf_dn_forward(f, st, x, ctx, row2ctx, n_per_ctx, R, E, z, logdet, fl, workspace, workspace_bytes, t->err));
+    PF_TRY(pf_dn_forward(f, st, x, ctx, row2ctx, n_per_ctx, R, E, z, logdet, fl, workspace, workspace_bytes, f->tg_err));
     if (t->debug_sync) {
-      int herr = 0;
       PF_CUDA(cudaStreamSynchronize(st));
-      PF_CUDA(cudaMemcpy(&herr, t->err, sizeof(int), cudaMemcpyDeviceToHost));
-      if (herr) {
-        snprintf(g_cuda_err, sizeof(g_cuda_err), "dense density kernel: barrier timeout, code %d", herr);
-        cudaMemset(t->err, 0, sizeof(int));
-        return PF_ERR_CUDA;
-      }
+      PF_TRY(pf_check_flag(f, "dense density kernel"));
     }
     return PF_OK;
   }

@@ -217,7 +217,7 @@ __global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const D
       if ((i & 255) == 255 && *abort_s) return false;
     }
     *abort_s = 1;
-    atomicExch(a.err, code);
+    raise_flag(a.err, code);
     return false;
   };
 
@@ -252,7 +252,8 @@ __global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const D
       *reinterpret_cast<__nv_bfloat16*>(sXT + (jn / 8) * 2048 + rowoff + (jn % 8) * 2) = hi;
       *reinterpret_cast<__nv_bfloat16*>(sXT + (2 + jn / 8) * 2048 + rowoff + (jn % 8) * 2) = lo;
     };
-    for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
+    int tile = blockIdx.x;
+    for (; tile < a.n_tiles && ok; tile += gridDim.x) {
       const int64_t grow = (int64_t)tile * DN_ROWS + r;
       const bool valid = grow < a.R;
       const int64_t first_row = (int64_t)tile * DN_ROWS;
@@ -472,6 +473,14 @@ __global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const D
         if (half == 0 && a.logdet) a.logdet[grow] = anybad ? __int_as_float(0x7fc00000) : ld_acc + red[r];
       }
       bar_sync(2, 256);                                         // red / ybuf are reused by the next tile
+    }
+    if (!ok && half == 0) {   // barrier timeout (flag raised): abandoned and unreached tiles come back as NaN rows
+      for (; tile < a.n_tiles; tile += gridDim.x) {
+        const int64_t grow = (int64_t)tile * DN_ROWS + r;
+        if (grow >= a.R) continue;
+        for (int jj = 0; jj < D; ++jj) a.z[grow * D + jj] = __int_as_float(0x7fc00000);
+        if (a.logdet) a.logdet[grow] = __int_as_float(0x7fc00000);
+      }
     }
     if (prof) {
       for (int i = 0; i < 5; ++i) a.prof[i] = pc[i];

@@ -221,7 +221,7 @@ tc_gemm_kernel(const Src src, int MA, int NBc, int K, int k_per_slice, Epi epi, 
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // the successor may set itself up during our epilogue
   if (nst > 0 && ok) ok = mbar_wait(acc_bar, 0);
   tc_fence_after();
-  if (!ok && (tid & 31) == 0) atomicExch(err, 60 + (warp == 8));
+  if (!ok && (tid & 31) == 0) raise_flag(err, 60 + (warp == 8));
   ok = __syncthreads_and(ok);
   if (ok && nst > 0 && warp < 8) {
     // ============================ epilogue ============================

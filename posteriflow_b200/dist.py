@@ -67,7 +67,15 @@ def allreduce_gradients(params: Iterable[torch.nn.Parameter], bucket_bytes: int 
     r, w = _world()
     if w == 1:
         return 0
-    grads: List[torch.Tensor] = [p.grad for p in params if p.grad is not None]
+    # A rank whose batch produced no gradient for a parameter (no signal in its shard) contributes zeros: the list of
+    # collectives and their sizes must be identical on every rank.
+    grads: List[torch.Tensor] = []
+    for p in params:
+        if not getattr(p, "requires_grad", True):
+            continue
+        if p.grad is None:
+            p.grad = torch.zeros_like(p)
+        grads.append(p.grad)
     n_coll, i = 0, 0
     while i < len(grads):
         j, size = i, 0

@@ -134,15 +134,26 @@ class NSFPosteriorFlow(nn.Module):
         self.register_buffer("_ar_perm", torch.arange(features, dtype=torch.long))
         self.register_buffer("_ar_inv_perm", torch.arange(features, dtype=torch.long))
         self._handle: Optional[ops.FlowHandle] = None
+        self._weights: Optional[List[Tensor]] = None
+        self._ar_identity = True
 
     # -- plumbing ----------------------------------------------------------------------------------
     def layer_weights(self) -> List[Tensor]:
-        """Flat [L * 18] parameter list in ops.LAYER_KEYS order."""
-        out: List[Tensor] = []
-        for l in range(self.num_layers):
-            net = self.transform._transforms[2 * l + 1].autoregressive_net
-            sd = dict(net.named_parameters())
-            out.extend(sd[k] for k in ops.LAYER_KEYS)
+        """Flat [L * 18] parameter list in ops.LAYER_KEYS order.  The list of Parameter OBJECTS is cached: `.to()`,
+        `load_state_dict` and optimizers all write into the same objects, and a moved / rewritten storage is caught
+        by the (data_ptr, _version) key of FlowHandle.ensure_packed -- no per-call walk over the module tree."""
+        if self._weights is None:
+            out: List[Tensor] = []
+            for l in range(self.num_layers):
+                net = self.transform._transforms[2 * l + 1].autoregressive_net
+                sd = dict(net.named_parameters())
+                out.extend(sd[k] for k in ops.LAYER_KEYS)
+            self._weights = out
+        return self._weights
+
+    def _apply(self, fn, *args, **kwargs):   # .to() / .cuda() / .double(): parameter objects may be replaced
+        out = super()._apply(fn, *args, **kwargs)
+        self._weights = None
         return out
 
     def handle(self) -> ops.FlowHandle:
@@ -174,36 +185,53 @@ class NSFPosteriorFlow(nn.Module):
         return context, 1
 
     # -- reference surface -------------------------------------------------------------------------
-    def forward(self, x: Tensor, context: Tensor = None, n_per_ctx: Optional[int] = None) -> Tuple[Tensor, Tensor]:
-        """flows.py:610-618: x (params) -> (z, log|det dz/dx|); differentiable wrt x, context, weights."""
+    def forward(self, x: Tensor, context: Tensor = None, n_per_ctx: Optional[int] = None,
+                row2ctx: Optional[Tensor] = None) -> Tuple[Tensor, Tensor]:
+        """flows.py:610-618: x (params) -> (z, log|det dz/dx|); differentiable wrt x, context, weights.
+        `row2ctx` ([R] int64): explicit context row per flow row (several ranks / repeated events in one call)."""
         fh = self.handle()
-        context, n = self._ctx_form(context, x.shape[0], n_per_ctx)
+        if not self._ar_identity:
+            x = x.index_select(1, self._ar_perm)               # flows.py:612
+        if row2ctx is None:
+            context, n = self._ctx_form(context, x.shape[0], n_per_ctx)
+        else:
+            n = 1
         w = self.layer_weights()
         need = torch.is_grad_enabled() and (x.requires_grad or context.requires_grad or any(p.requires_grad for p in w))
-        z, logdet, _ = torch.ops.posteriflow.nsf_forward(x, context, w, fh.id, n, bool(need))
+        z, logdet, _ = torch.ops.posteriflow.nsf_forward(x, context, w, fh.id, n, bool(need), row2ctx)
         return z, logdet
 
     def inverse(self, z: Tensor, context: Tensor = None, n_overlaps: Optional[Tensor] = None,
-                n_per_ctx: Optional[int] = None) -> Tuple[Tensor, Tensor]:
+                n_per_ctx: Optional[int] = None, row2ctx: Optional[Tensor] = None) -> Tuple[Tensor, Tensor]:
         """flows.py:620-655: z -> (x clamped to +-3, log_det), context sanitised in-kernel."""
         fh = self.handle()
-        context, n = self._ctx_form(context, z.shape[0], n_per_ctx)
+        if row2ctx is None:
+            context, n = self._ctx_form(context, z.shape[0], n_per_ctx)
+        else:
+            n = 1
         flags = A.PF_FLAG_SANITIZE_CTX | A.PF_FLAG_CLAMP
         with torch.no_grad():
-            x, logdet = torch.ops.posteriflow.nsf_inverse(z, context, fh.id, n, flags, None, None, None, None)
+            x, logdet = torch.ops.posteriflow.nsf_inverse(z, context, fh.id, n, flags, None, None, None, None, row2ctx)
+            if not self._ar_identity:                          # flows.py:648 (nan_to_num / clamp are per element:
+                x = x.index_select(1, self._ar_inv_perm)       #  they commute with the column gather)
         return x, logdet
 
     def compute_psd_aware_nll(self, x: Tensor, context: Tensor, log_sigma_psd: Optional[Tensor] = None,
-                              n_per_ctx: Optional[int] = None) -> Tensor:
+                              n_per_ctx: Optional[int] = None, row2ctx: Optional[Tensor] = None) -> Tensor:
         """flows.py:727-779 with the PSDScaledNormal base (flows.py:73-85)."""
         fh = self.handle()
-        ctx, n = self._ctx_form(context, x.shape[0], n_per_ctx)
+        if not self._ar_identity:
+            x = x.index_select(1, self._ar_perm)               # through self.forward, flows.py:752
+        if row2ctx is None:
+            ctx, n = self._ctx_form(context, x.shape[0], n_per_ctx)
+        else:
+            ctx, n = context, 1
         w = self.layer_weights()
         need = torch.is_grad_enabled() and (x.requires_grad or ctx.requires_grad or any(p.requires_grad for p in w)
                                             or (log_sigma_psd is not None and log_sigma_psd.requires_grad))
         if not need:
-            return torch.ops.posteriflow.nsf_nll(x, ctx, log_sigma_psd, fh.id, n)
-        z, logdet, _ = torch.ops.posteriflow.nsf_forward(x, ctx, w, fh.id, n, True)
+            return torch.ops.posteriflow.nsf_nll(x, ctx, log_sigma_psd, fh.id, n, row2ctx)
+        z, logdet, _ = torch.ops.posteriflow.nsf_forward(x, ctx, w, fh.id, n, True, row2ctx)
         const = self.features * math.log(2 * math.pi)
         if log_sigma_psd is None:
             logp = -0.5 * ((z * z).sum(dim=1) + const)
@@ -211,5 +239,19 @@ class NSFPosteriorFlow(nn.Module):
             logp = -0.5 * (((z / torch.exp(log_sigma_psd)) ** 2).sum(dim=1) + 2 * log_sigma_psd.sum(dim=1) + const)
         return -(logp + logdet)
 
-    def set_autoregressive_order(self, order) -> None:  # flows.py:560-575: no-op without masked context
-        return None
+    def set_autoregressive_order(self, order) -> None:
+        """flows.py:550-586: `order[i]` = original feature index placed at autoregressive position i.  A fixed column
+        gather in front of forward() and its inverse behind inverse(); the kernels are untouched.  (The per-position
+        tail-bound re-patching of flows.py:577-584 belongs to the per-parameter-tail-bound branch, not built here.)"""
+        order = [int(i) for i in order]
+        if sorted(order) != list(range(self.features)):
+            raise ValueError(f"order must be a permutation of range({self.features}), got {order}")
+        perm = torch.tensor(order, dtype=torch.long, device=self._ar_perm.device)
+        self._ar_perm = perm
+        self._ar_inv_perm = torch.argsort(perm)
+        self._ar_identity = order == list(range(self.features))
+
+    def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
+        super()._load_from_state_dict(state_dict, prefix, *args, **kwargs)
+        # a checkpoint written after set_autoregressive_order carries the permutation in its buffers
+        self._ar_identity = bool((self._ar_perm.cpu() == torch.arange(self.features)).all())

@@ -73,6 +73,9 @@ def sample_fused(flow: NSFPosteriorFlow, scaler: ParamScaler, ctx_full: Tensor, 
     """lean_npe.py:326-332 in one C-ABI call: (theta [E, n, D] physical, logdet [E*n], railed [E*n]).
     The context is NOT repeated: row e of `ctx_full` serves samples [e*n, (e+1)*n)."""
     fh = flow.handle()
+    if not flow._ar_identity and (flags & (A.PF_FLAG_WRAP | A.PF_FLAG_DENORMALIZE)):
+        raise NotImplementedError("the fused sampler applies ParamScaler per autoregressive POSITION in-kernel; with a "
+                                  "non-identity set_autoregressive_order call flow.inverse and the scaler separately")
     with torch.no_grad():
         return torch.ops.posteriflow.nsf_sample_fused(ctx_full, z, int(seed), int(n_samples), fh.id, int(flags),
                                                       scaler.lo, scaler.hi, scaler.log_mask, scaler.circ_mask)

@@ -29,7 +29,9 @@ LAYER_KEYS = [
 ]
 NW = len(LAYER_KEYS)
 
-_HANDLES: Dict[int, "FlowHandle"] = {}
+# id -> handle, WEAK: the owning NSFPosteriorFlow holds the only strong reference, so dropping the module (or moving
+# it to another device) lets weakref.finalize release the arena, weight images, side streams and events
+_HANDLES: "weakref.WeakValueDictionary[int, FlowHandle]" = weakref.WeakValueDictionary()
 _NEXT_ID = [1]
 
 
@@ -71,6 +73,7 @@ class FlowHandle:
         A.check(self.lib.pf_flow_create(C.byref(desc), C.byref(h)), "pf_flow_create")
         self.h = h
         self.pack_key = None
+        self.pack_ptrs = None
         self.id = _NEXT_ID[0]
         _NEXT_ID[0] += 1
         _HANDLES[self.id] = self
@@ -85,13 +88,22 @@ class FlowHandle:
         except Exception:
             pass
 
+    def check(self) -> None:
+        """Synchronise the current stream and raise if a tensor-core kernel of this handle hit a barrier timeout
+        (pf_flow_check; such a kernel also writes NaN into the rows it abandons)."""
+        with torch.cuda.device(self.index):
+            A.check(self.lib.pf_flow_check(self.h, _stream()), "pf_flow_check")
+
     # -- packing ---------------------------------------------------------------------------------
     def ensure_packed(self, weights: Sequence[Tensor]) -> None:
-        key = tuple((w.data_ptr(), w._version) for w in weights)
-        if key == self.pack_key:
+        """Re-pack iff a weight tensor moved or was written in place since the last pack (optimizer step,
+        load_state_dict).  The key is two integers per tensor; `weights` is the module's cached parameter list."""
+        key = [w._version for w in weights]
+        ptrs = [w.data_ptr() for w in weights]
+        if key == self.pack_key and ptrs == self.pack_ptrs:
             return
         self.pack(weights)
-        self.pack_key = key
+        self.pack_key, self.pack_ptrs = key, ptrs
 
     def pack(self, weights: Sequence[Tensor], masks: Optional[Sequence[Dict[str, Tensor]]] = None) -> None:
         L = self.shape[3]
@@ -147,11 +159,19 @@ def get_handle(hid: int) -> FlowHandle:
         raise RuntimeError(f"posteriflow_b200: unknown flow handle {hid}") from None
 
 
-def _rows(x: Tensor, ctx: Tensor, n_per_ctx: int) -> Tuple[int, int]:
+def _rows(x: Tensor, ctx: Tensor, n_per_ctx: int, row2ctx: Optional[Tensor] = None) -> Tuple[int, int]:
     R, E = x.shape[0], ctx.shape[0]
+    if row2ctx is not None:
+        if row2ctx.dtype != torch.int64 or row2ctx.dim() != 1 or row2ctx.shape[0] != R or not row2ctx.is_cuda:
+            raise ValueError(f"row2ctx must be a CUDA int64 tensor with one context index per flow row ({R})")
+        return R, E
     if n_per_ctx < 1 or (R > 0 and (R - 1) // n_per_ctx >= E):
         raise ValueError(f"context rows ({E}) do not cover {R} flow rows at {n_per_ctx} rows per context")
     return R, E
+
+
+def _r2c(row2ctx: Optional[Tensor]) -> Optional[Tensor]:
+    return None if row2ctx is None else row2ctx.contiguous()
 
 
 # ------------------------------------------------------------------------------------------------
@@ -159,18 +179,19 @@ def _rows(x: Tensor, ctx: Tensor, n_per_ctx: int) -> Tuple[int, int]:
 # ------------------------------------------------------------------------------------------------
 @torch.library.custom_op("posteriflow::nsf_forward", mutates_args=())
 def nsf_forward(x: Tensor, ctx: Tensor, weights: Sequence[Tensor], handle: int, n_per_ctx: int,
-                save: bool) -> Tuple[Tensor, Tensor, Tensor]:
-    """NSFPosteriorFlow.forward (flows.py:610-618): (z [R,D], logdet [R], saved activations)."""
+                save: bool, row2ctx: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor]:
+    """NSFPosteriorFlow.forward (flows.py:610-618): (z [R,D], logdet [R], saved activations).
+    `row2ctx` ([R] int64) addresses the context row of every flow row explicitly instead of `row // n_per_ctx`."""
     _require_cuda(x, ctx)
     fh = get_handle(handle)
-    x, ctx = _f32c(x), _f32c(ctx)
-    R, E = _rows(x, ctx, n_per_ctx)
+    x, ctx, row2ctx = _f32c(x), _f32c(ctx), _r2c(row2ctx)
+    R, E = _rows(x, ctx, n_per_ctx, row2ctx)
     z = torch.empty_like(x)
     logdet = torch.empty(R, dtype=torch.float32, device=x.device)
     saved = torch.empty(fh.saved_bytes(R, E) if save else 0, dtype=torch.uint8, device=x.device)
     ws = fh.workspace(A.PF_OP_FORWARD, R, E)
     with torch.cuda.device(fh.index):
-        A.check(fh.lib.pf_flow_forward(fh.h, x.data_ptr(), ctx.data_ptr(), None, n_per_ctx, R, E, z.data_ptr(),
+        A.check(fh.lib.pf_flow_forward(fh.h, x.data_ptr(), ctx.data_ptr(), _ptr(row2ctx), n_per_ctx, R, E, z.data_ptr(),
                                        logdet.data_ptr(), None, None, 0, saved.data_ptr() if save else None,
                                        ws.data_ptr(), ws.numel(), _stream()), "pf_flow_forward")
     fh._note_launches()
@@ -178,18 +199,18 @@ def nsf_forward(x: Tensor, ctx: Tensor, weights: Sequence[Tensor], handle: int, 
 
 
 @nsf_forward.register_fake
-def _(x, ctx, weights, handle, n_per_ctx, save):
+def _(x, ctx, weights, handle, n_per_ctx, save, row2ctx=None):
     return torch.empty_like(x), x.new_empty(x.shape[0]), x.new_empty(0, dtype=torch.uint8)
 
 
 @torch.library.custom_op("posteriflow::nsf_backward", mutates_args=())
 def nsf_backward(saved: Tensor, ctx: Tensor, gz: Tensor, glogdet: Tensor, weights: Sequence[Tensor], handle: int,
-                 n_per_ctx: int) -> List[Tensor]:
+                 n_per_ctx: int, row2ctx: Optional[Tensor] = None) -> List[Tensor]:
     """Backward of nsf_forward: [gx, gctx, *gweights] (weights in the nflows layout, masked entries zero)."""
     _require_cuda(saved, ctx, gz, glogdet)
     fh = get_handle(handle)
-    ctx, gz, glogdet = _f32c(ctx), _f32c(gz), _f32c(glogdet)
-    R, E = _rows(gz, ctx, n_per_ctx)
+    ctx, gz, glogdet, row2ctx = _f32c(ctx), _f32c(gz), _f32c(glogdet), _r2c(row2ctx)
+    R, E = _rows(gz, ctx, n_per_ctx, row2ctx)
     L = fh.shape[3]
     gx = torch.empty_like(gz)
     gctx = torch.empty_like(ctx)
@@ -208,7 +229,7 @@ def nsf_backward(saved: Tensor, ctx: Tensor, gz: Tensor, glogdet: Tensor, weight
         p.final_w, p.final_b = _ptr(g[16]), _ptr(g[17])
     ws = fh.workspace(A.PF_OP_BACKWARD, R, E)
     with torch.cuda.device(fh.index):
-        A.check(fh.lib.pf_flow_backward(fh.h, saved.data_ptr(), ctx.data_ptr(), None, n_per_ctx, R, E, gz.data_ptr(),
+        A.check(fh.lib.pf_flow_backward(fh.h, saved.data_ptr(), ctx.data_ptr(), _ptr(row2ctx), n_per_ctx, R, E, gz.data_ptr(),
                                         glogdet.data_ptr(), gx.data_ptr(), gctx.data_ptr(), arr, ws.data_ptr(),
                                         ws.numel(), _stream()), "pf_flow_backward")
     fh._note_launches()
@@ -216,40 +237,43 @@ def nsf_backward(saved: Tensor, ctx: Tensor, gz: Tensor, glogdet: Tensor, weight
 
 
 @nsf_backward.register_fake
-def _(saved, ctx, gz, glogdet, weights, handle, n_per_ctx):
+def _(saved, ctx, gz, glogdet, weights, handle, n_per_ctx, row2ctx=None):
     return [torch.empty_like(gz), torch.empty_like(ctx)] + [torch.empty_like(w) for w in weights]
 
 
 def _fwd_setup(ctx, inputs, output):
-    x, c, weights, handle, n_per_ctx, save = inputs
+    x, c, weights, handle, n_per_ctx, save, row2ctx = inputs
     _, _, saved = output
     if not save:
         raise RuntimeError("nsf_forward was called with save=False but a gradient is required")
-    ctx.save_for_backward(saved, c, *weights)
+    ctx.has_r2c = row2ctx is not None
+    ctx.save_for_backward(saved, c, *([row2ctx] if ctx.has_r2c else []), *weights)
     ctx.handle, ctx.n_per_ctx = handle, n_per_ctx
 
 
 def _fwd_backward(ctx, gz, glogdet, gsaved):
-    saved, c, *weights = ctx.saved_tensors
-    outs = torch.ops.posteriflow.nsf_backward(saved, c, gz, glogdet, weights, ctx.handle, ctx.n_per_ctx)
-    return outs[0], outs[1], list(outs[2:]), None, None, None
+    saved, c, *rest = ctx.saved_tensors
+    row2ctx = rest.pop(0) if ctx.has_r2c else None
+    outs = torch.ops.posteriflow.nsf_backward(saved, c, gz, glogdet, rest, ctx.handle, ctx.n_per_ctx, row2ctx)
+    return outs[0], outs[1], list(outs[2:]), None, None, None, None
 
 
 nsf_forward.register_autograd(_fwd_backward, setup_context=_fwd_setup)
 
 
 @torch.library.custom_op("posteriflow::nsf_nll", mutates_args=())
-def nsf_nll(x: Tensor, ctx: Tensor, log_sigma: Optional[Tensor], handle: int, n_per_ctx: int) -> Tensor:
+def nsf_nll(x: Tensor, ctx: Tensor, log_sigma: Optional[Tensor], handle: int, n_per_ctx: int,
+            row2ctx: Optional[Tensor] = None) -> Tensor:
     """compute_psd_aware_nll (flows.py:727-779) fused, inference only (no autograd)."""
     _require_cuda(x, ctx)
     fh = get_handle(handle)
-    x, ctx = _f32c(x), _f32c(ctx)
+    x, ctx, row2ctx = _f32c(x), _f32c(ctx), _r2c(row2ctx)
     ls = _f32c(log_sigma) if log_sigma is not None else None
-    R, E = _rows(x, ctx, n_per_ctx)
+    R, E = _rows(x, ctx, n_per_ctx, row2ctx)
     nll = torch.empty(R, dtype=torch.float32, device=x.device)
     ws = fh.workspace(A.PF_OP_FORWARD, R, E)
     with torch.cuda.device(fh.index):
-        A.check(fh.lib.pf_flow_forward(fh.h, x.data_ptr(), ctx.data_ptr(), None, n_per_ctx, R, E, None, None,
+        A.check(fh.lib.pf_flow_forward(fh.h, x.data_ptr(), ctx.data_ptr(), _ptr(row2ctx), n_per_ctx, R, E, None, None,
                                        nll.data_ptr(), _ptr(ls), 0, None, ws.data_ptr(), ws.numel(), _stream()),
                 "pf_flow_forward(nll)")
     fh._note_launches()
@@ -257,7 +281,7 @@ def nsf_nll(x: Tensor, ctx: Tensor, log_sigma: Optional[Tensor], handle: int, n_
 
 
 @nsf_nll.register_fake
-def _(x, ctx, log_sigma, handle, n_per_ctx):
+def _(x, ctx, log_sigma, handle, n_per_ctx, row2ctx=None):
     return x.new_empty(x.shape[0])
 
 
@@ -274,19 +298,19 @@ def _scaler_struct(lo, hi, log_mask, circ_mask):
 
 @torch.library.custom_op("posteriflow::nsf_inverse", mutates_args=())
 def nsf_inverse(z: Tensor, ctx: Tensor, handle: int, n_per_ctx: int, flags: int, lo: Optional[Tensor],
-                hi: Optional[Tensor], log_mask: Optional[Tensor], circ_mask: Optional[Tensor]
-                ) -> Tuple[Tensor, Tensor]:
+                hi: Optional[Tensor], log_mask: Optional[Tensor], circ_mask: Optional[Tensor],
+                row2ctx: Optional[Tensor] = None) -> Tuple[Tensor, Tensor]:
     """NSFPosteriorFlow.inverse (flows.py:620-655), optionally fused with ParamScaler.wrap/denormalize."""
     _require_cuda(z, ctx)
     fh = get_handle(handle)
-    z, ctx = _f32c(z), _f32c(ctx)
-    R, E = _rows(z, ctx, n_per_ctx)
+    z, ctx, row2ctx = _f32c(z), _f32c(ctx), _r2c(row2ctx)
+    R, E = _rows(z, ctx, n_per_ctx, row2ctx)
     x = torch.empty_like(z)
     logdet = torch.empty(R, dtype=torch.float32, device=z.device)
     sc, keep = _scaler_struct(lo, hi, log_mask, circ_mask)
     ws = fh.workspace(A.PF_OP_INVERSE, R, E)
     with torch.cuda.device(fh.index):
-        A.check(fh.lib.pf_flow_inverse(fh.h, z.data_ptr(), ctx.data_ptr(), None, n_per_ctx, R, E, x.data_ptr(),
+        A.check(fh.lib.pf_flow_inverse(fh.h, z.data_ptr(), ctx.data_ptr(), _ptr(row2ctx), n_per_ctx, R, E, x.data_ptr(),
                                        logdet.data_ptr(), flags, C.byref(sc) if sc is not None else None,
                                        ws.data_ptr(), ws.numel(), _stream()), "pf_flow_inverse")
     fh._note_launches()
@@ -294,7 +318,7 @@ def nsf_inverse(z: Tensor, ctx: Tensor, handle: int, n_per_ctx: int, flags: int,
 
 
 @nsf_inverse.register_fake
-def _(z, ctx, handle, n_per_ctx, flags, lo, hi, log_mask, circ_mask):
+def _(z, ctx, handle, n_per_ctx, flags, lo, hi, log_mask, circ_mask, row2ctx=None):
     return torch.empty_like(z), z.new_empty(z.shape[0])
 
 

@@ -38,7 +38,12 @@ def batch_nll(model, strain: Optional[Tensor], params: Tensor, nsig: Tensor, asd
     event, rank = signal_rows(nsig.to(context.device), int(model.max_signals))
     count = event.numel()
     if count == 0:
-        return context.sum() * 0.0
+        # a rank without signals still takes part in the count all-reduce (and, through dist.allreduce_gradients'
+        # zero-fill of missing .grad tensors, in the gradient exchange): no rank may skip a collective
+        zero = context.sum() * 0.0
+        if distributed:
+            return global_mean_loss(zero, torch.tensor(0.0, device=zero.device))
+        return zero
     nll = model.nll(None, params[event, rank, :], rank, context=context[event])
     total = nll.sum()
     if distributed:
@@ -119,11 +124,34 @@ class GraphedNLLStep:
         st["launches"] = fh.launches - l0      # library kernels inside one replay
         return st
 
+    def _ensure_flat(self):
+        """Views of ONE flat buffer, one per flow parameter: the data-parallel all-reduce is a single collective."""
+        if self._gbuf is None:
+            dev = self.flow_params[0].device
+            self.flat_grad = torch.zeros(sum(p.numel() for p in self.flow_params), dtype=torch.float32, device=dev)
+            self._gbuf, o = [], 0
+            for p in self.flow_params:
+                self._gbuf.append(self.flat_grad[o:o + p.numel()].view(p.shape))
+                o += p.numel()
+
     def __call__(self, params: Tensor, nsig: Tensor, context: Tensor) -> Tensor:
         m = self.model
         event, rank = signal_rows(nsig.to(context.device), int(m.max_signals))
         R = int(event.numel())
         if R == 0:
+            # No signal on this rank: contribute zero gradients, but issue the same collectives as every other rank
+            # (the count all-reduce here, the flat gradient all-reduce in allreduce()).
+            if self.distributed:
+                from .dist import _world
+                import torch.distributed as dist
+                if _world()[1] > 1:
+                    dist.all_reduce(torch.zeros((), device=context.device))
+            self._ensure_flat()
+            fresh = [i for i, p in enumerate(self.flow_params) if p.requires_grad and p.grad is None]
+            if fresh:
+                torch._foreach_zero_([self._gbuf[i] for i in fresh])
+                for i in fresh:
+                    self.flow_params[i].grad = self._gbuf[i]
             return context.sum() * 0.0
         # re-pack if an optimizer step changed the weights (the cached parameter list skips NSFPosteriorFlow.handle()'s
         # per-call walk over the module tree: ~0.3 ms of host time per step)
@@ -155,12 +183,7 @@ class GraphedNLLStep:
         st["graph"].replay()
         self.last_launches = st["launches"]
         # the graph's gradient tensors are overwritten by the next replay: hand out copies (two multi-tensor kernels)
-        if self._gbuf is None:      # views of ONE flat buffer: the data-parallel all-reduce is a single collective
-            self.flat_grad = torch.empty(sum(g.numel() for g in st["gw"]), dtype=torch.float32, device=st["gw"][0].device)
-            self._gbuf, o = [], 0
-            for g in st["gw"]:
-                self._gbuf.append(self.flat_grad[o:o + g.numel()].view_as(g))
-                o += g.numel()
+        self._ensure_flat()
         fresh = [i for i, p in enumerate(self.flow_params) if p.requires_grad and p.grad is None]
         accum = [i for i, p in enumerate(self.flow_params) if p.requires_grad and p.grad is not None]
         if fresh:

@@ -111,3 +111,71 @@ def test_graphed_step_allreduce_is_one_collective_on_the_flat_buffer():
         assert n1 == 2                     # flat flow gradients + one bucket for the rank embedding
         assert a == (3.0, 3.0 * nps, 3.0)  # (1 + 2) * (i + 1)
         assert n2 >= 1 and b == (3.0, 3.0 * nps)
+
+
+class _ToyNLL(torch.nn.Module):
+    """LeanNPE.nll's call signature over one Linear layer (CPU)."""
+    max_signals = 5
+
+    def __init__(self):
+        super().__init__()
+        self.lin = torch.nn.Linear(4, 1)
+
+    def nll(self, strain, params_phys, rank, context=None, asd_bands=None):
+        return self.lin(context).squeeze(1) ** 2 + (params_phys ** 2).sum(1) * (rank.float() + 1.0)
+
+
+def _empty_rank_worker(rank, world, port, out):
+    """Rank 1's shard holds no signal at all: it must still issue the count all-reduce and the gradient all-reduce
+    (with zeros), or rank 0 hangs / the collectives mismatch."""
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world, timeout=__import__("datetime").timedelta(seconds=60))
+    try:
+        from posteriflow_b200.train import batch_nll
+        import posteriflow_b200 as P
+        torch.manual_seed(0)
+        m = _ToyNLL()
+        g = torch.Generator().manual_seed(1)
+        params = torch.randn(6, 5, 11, generator=g)
+        ctx = torch.randn(6, 4, generator=g).requires_grad_(True)   # encoder output: carries the graph on every rank
+        nsig = torch.tensor([1, 2, 1, 3, 1, 1]) if rank == 0 else torch.zeros(6, dtype=torch.long)
+        loss = batch_nll(m, None, params, nsig, context=ctx, distributed=True)
+        loss.backward()                                   # rank 1: graph through `context` only, lin gets no grad
+        n = D.allreduce_gradients(m.parameters())
+        # the graphed step's empty-rank path: count all-reduce + zero flat gradients + the single flat all-reduce
+        lean = P.LeanNPE(flow_layers=1, flow_hidden=32, flow_bins=8)
+        step = P.GraphedNLLStep(lean, distributed=True)
+        if rank == 1:
+            l2 = step(params, nsig, torch.zeros(6, 256))
+            assert float(l2) == 0.0
+        else:                                             # what a populated rank does around its graph replay
+            dist.all_reduce(torch.tensor(9.0))
+            step._ensure_flat()
+            step.flat_grad.fill_(2.0)
+            for p, v in zip(step.flow_params, step._gbuf):
+                p.grad = v
+        n2 = step.allreduce()
+        out[rank] = (float(loss), m.lin.weight.grad.clone(), n, n2, float(step.flat_grad.min()), float(step.flat_grad.max()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_rank_without_signals_joins_every_collective():
+    world, port = 2, _free_port()
+    with mp.Manager() as m:
+        out = m.dict()
+        mp.spawn(_empty_rank_worker, args=(world, port, out), nprocs=world, join=True)
+        res = dict(out)
+    torch.manual_seed(0)
+    m = _ToyNLL()
+    g = torch.Generator().manual_seed(1)
+    params = torch.randn(6, 5, 11, generator=g)
+    ctx = torch.randn(6, 4, generator=g)
+    from posteriflow_b200.train import batch_nll
+    ref = batch_nll(m, None, params, torch.tensor([1, 2, 1, 3, 1, 1]), context=ctx)     # global mean = rank 0's mean
+    ref.backward()
+    assert abs(res[0][0] - float(ref)) <= 1e-6 and res[1][0] == 0.0
+    for r in range(world):
+        assert torch.allclose(res[r][1], m.lin.weight.grad, atol=1e-6)
+        assert res[r][2] == 1 and res[r][3] == 1
+        assert res[r][4] == 2.0 and res[r][5] == 2.0      # 2 (rank 0) + 0 (empty rank)

@@ -53,3 +53,30 @@ def test_unsupported_branches_raise():
         P.NSFPosteriorFlow(features=11, context_features=288, use_masked_context=True)
     with pytest.raises(NotImplementedError):
         P.NSFPosteriorFlow(features=11, context_features=288, tail_bound={0: 3.0})
+
+
+def test_autoregressive_order_is_kept_and_travels_with_the_state_dict():
+    """flows.py:550-586: set_autoregressive_order stores a permutation + its inverse; forward gathers x[:, perm],
+    inverse scatters back (GPU arithmetic: tests/test_gpu_glue.py).  A checkpoint carrying a non-identity order must
+    not evaluate as if it were the identity."""
+    import pytest
+    f = P.NSFPosteriorFlow(features=11, context_features=288, num_layers=1)
+    assert f._ar_identity
+    order = [2, 0, 1] + list(range(3, 11))
+    f.set_autoregressive_order(order)
+    assert not f._ar_identity and f._ar_perm.tolist() == order
+    assert f._ar_inv_perm.tolist() == torch.argsort(torch.tensor(order)).tolist()
+    with pytest.raises(ValueError):
+        f.set_autoregressive_order([0, 0, 1] + list(range(3, 11)))
+    g = P.NSFPosteriorFlow(features=11, context_features=288, num_layers=1)
+    g.load_state_dict(f.state_dict(), strict=True)
+    assert not g._ar_identity and g._ar_perm.tolist() == order
+    g.set_autoregressive_order(list(range(11)))
+    assert g._ar_identity
+
+
+def test_flow_handles_are_weakly_registered():
+    """ops._HANDLES must not keep a FlowHandle alive (the arena, weight images, streams and events of every flow ever
+    built would leak): it is a WeakValueDictionary, the module owns the only strong reference."""
+    import weakref
+    assert isinstance(P.ops._HANDLES, weakref.WeakValueDictionary)

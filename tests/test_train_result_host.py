@@ -98,6 +98,43 @@ def test_save_posterior_writes_the_reference_files(tmp_path):
         "mass_1,mass_2,luminosity_distance,ra,dec,theta_jn,psi,phase,geocent_time,a1,a2,log_prob"
 
 
+def test_save_posterior_matches_the_reference_class_itself(tmp_path):
+    """The same three files written by the reference's OWN `PosteriorResult.save` (result.py:242-252), imported
+    unmodified over the nflows shim.  Build-container only: /root/reference does not exist on the GPU box."""
+    import os
+    import sys
+    import pytest
+    ref_src = os.path.join(os.environ.get("POSTERIFLOW_REF", "/root/reference"), "src")
+    if not os.path.isdir(ref_src):
+        pytest.skip("reference tree not present (GPU box)")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for pth in (os.path.join(root, "oracle"), ref_src):
+        if pth not in sys.path:
+            sys.path.insert(0, pth)
+    import logging
+    logging.disable(logging.CRITICAL)
+    try:
+        # the file itself, unmodified (`import ahsd.inference` would pull in the bilby-based pipeline, absent here)
+        import importlib.util
+        sp = importlib.util.spec_from_file_location("ahsd_inference_result",
+                                                    os.path.join(ref_src, "ahsd", "inference", "result.py"))
+        mod = importlib.util.module_from_spec(sp)
+        sys.modules["ahsd_inference_result"] = mod
+        sp.loader.exec_module(mod)
+        PosteriorResult = mod.PosteriorResult
+    finally:
+        logging.disable(logging.NOTSET)
+    g = torch.Generator().manual_seed(5)
+    theta = torch.randn(2, 64, 11, generator=g).abs() + 0.5        # positive: summary() takes logs of nothing, but be safe
+    logq = torch.randn(128, generator=g)
+    ours = save_posterior(tmp_path / "ours", theta, logq)
+    res = PosteriorResult(samples=theta.reshape(-1, 11).numpy().astype(np.float64),
+                          log_prob=logq.numpy().astype(np.float64), param_names=list(PARAM_NAMES), trigger_gps=None)
+    ref = res.save(str(tmp_path / "ref"), plots=False)
+    for name in ("posterior_samples.npy", "posterior_log_prob.npy", "posterior_samples.csv"):
+        assert (ours / name).read_bytes() == (ref / name).read_bytes(), name
+
+
 def test_posterior_arrays_shapes_and_errors():
     s, lp, rm = posterior_arrays(np.zeros((2, 5, 11), np.float32), np.zeros(10, np.float32),
                                  np.array([0, 1] * 5, np.uint8))

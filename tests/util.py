@@ -43,6 +43,7 @@ def rel_err(a, ref):
     return float(np.max(np.abs(a - ref) / np.maximum(1.0, np.abs(ref)))) if a.size else 0.0
 
 
+ARBITRATED = {}   # name -> largest arbitrated fraction seen in this process (printed by the parity tests)
 TOL = 1e-4  # FP32 tier: |d| <= 1e-4 * max(1, |ref|)  (BASELINE.json north_star)
 
 
@@ -57,11 +58,15 @@ def check_parity(name, got, ref32, ref64=None, tol=TOL, scale=None, median_facto
     got, ref32 = np.asarray(got, np.float64), np.asarray(ref32, np.float64)
     assert got.shape == ref32.shape, (name, got.shape, ref32.shape)
     if got.size == 0:
-        return
+        return 0.0
     den = (lambda r: np.maximum(1.0, np.abs(r))) if scale is None else (lambda r: scale)
     e32 = np.abs(got - ref32) / den(ref32)
+    # fraction of entries that are NOT within `tol` of the float32 reference, i.e. that needed the float64 arbiter:
+    # returned so that callers can assert 0 for the well-conditioned weight sets and report it for the stress sets
+    arbitrated = float(np.mean(e32 > tol))
+    ARBITRATED[name] = max(ARBITRATED.get(name, 0.0), arbitrated)
     if e32.max() <= tol:
-        return
+        return 0.0
     assert ref64 is not None, f"{name}: rel err {e32.max():.3e} > {tol} (no float64 arbiter)"
     ref64 = np.asarray(ref64, np.float64)
     e = np.abs(got - ref64) / den(ref64)
@@ -71,3 +76,4 @@ def check_parity(name, got, ref32, ref64=None, tol=TOL, scale=None, median_facto
         ok = ok and np.median(e) <= median_factor * np.median(own) + 1e-6
     assert ok, (f"{name}: vs f32 max {e32.max():.3e}; vs f64 median {np.median(e):.3e} max {e.max():.3e}; "
                 f"f32 reference's own vs f64 median {np.median(own):.3e} max {own.max():.3e}")
+    return arbitrated
