@@ -4,11 +4,13 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--tier fp32|bf16]
 
 Metric (BASELINE.json): NSF posterior samples/s.  One step = one pass of the fused sampler
-(lean_npe.py:326-332: context broadcast -> base noise -> inverse flow -> wrap -> denormalize) over one
-batch of synthetic events: EVENTS_PER_GPU events x 5000 samples per GPU, i.e. BASELINE config #3
-(4096 events x 5000 samples) at 8 GPUs, events sharded contiguously, no data-path collective (weak
-scaling).  Weights are random-init (seeded), contexts synthetic.  The NLL training step (config #4
-shard: forward + backward of the flow head) is timed too and reported under "train".
+(lean_npe.py:326-332: context broadcast -> base noise -> inverse flow -> wrap -> denormalize) over BASELINE
+config #3 -- 4096 synthetic events x 5000 samples, rank 0 -- with the events sharded contiguously over the
+N GPUs (4096 / N events per GPU: STRONG scaling of the fixed problem; at N = 1 the whole 2.048e7-row problem
+runs on one GPU), no data-path collective.  Weights are random-init (seeded), contexts synthetic.  The other
+BASELINE configs are reported in the same line: "configs" (#2 one event x 50 000 samples as sample blocks, #5
+rank-conditioned sampling through one launch, on a stated sub-sample) and "train" (#4: NLL training step of
+the flow head, per-GPU shard and un-sharded, with and without clip + AdamW + re-pack).
 Prints ONE JSON line on rank 0.
 """
 import argparse
@@ -24,8 +26,9 @@ sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
-EVENTS_PER_GPU = 512
+TOTAL_EVENTS = 4096                 # BASELINE config #3
 SAMPLES_PER_EVENT = 5000
+CFG5_EVENTS_PER_GPU = 160           # config #5 sub-sample: 160 of the 1250 events a GPU holds at 8 GPUs (x 3 ranks x 10^4)
 TRAIN_EVENTS_PER_GPU = 512          # config #4: batch 4096 over 8 GPUs
 F_X = 7946240                       # FLOP per flow row, dense single conditioner pass x 10 layers
 F_CTX = 4423680                     # FLOP per distinct context row
@@ -136,28 +139,35 @@ def run_reference(args):
         "impl": "reference", "metric": "posterior_samples_per_sec", "value": v, "unit": "samples/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args.gpus),
+        "config": dict(workload_config(args.gpus), sample="SUB-SAMPLE, EXTRAPOLATED: the CPU arm runs " + sample +
+                       "; its samples/s is quoted for the config above assuming linear scaling in the row count"),
         "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
 
 
 def workload_config(n_gpus):
-    return {"workload": f"BASELINE config #3 shard: {EVENTS_PER_GPU} events x {SAMPLES_PER_EVENT} samples per GPU "
-                        f"({EVENTS_PER_GPU * n_gpus} events total; 4096 at 8 GPUs), rank 0, LeanNPE flow 10x256x16 "
-                        "bins, 11-D, 288-D context",
-            "events_per_gpu": EVENTS_PER_GPU, "samples_per_event": SAMPLES_PER_EVENT,
+    ev = TOTAL_EVENTS // n_gpus
+    return {"workload": f"BASELINE config #3: {TOTAL_EVENTS} events x {SAMPLES_PER_EVENT} samples, rank 0 "
+                        f"({ev} events = {ev * SAMPLES_PER_EVENT} flow rows per GPU), LeanNPE flow 10x256x16 bins, "
+                        "11-D, 288-D context",
+            "events_per_gpu": ev, "samples_per_event": SAMPLES_PER_EVENT,
             "parallelism": f"events sharded over {n_gpus} GPU(s), no data-path collective",
-            "l2": "L2 flushed (256 MB write) between timed steps; each step also streams 126 MB of outputs; the "
-                  "5.5 MB bf16 weight image is re-read from L2 by design"}
+            "l2": "L2 flushed (256 MB write) between timed steps; every step also streams its own outputs "
+                  f"({ev * SAMPLES_PER_EVENT * 49 / 1e6:.0f} MB per GPU) through L2; the 5.5 MB bf16 weight image is "
+                  "re-read from L2 by design"}
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of ONE tc_sampler_kernel launch, from the `ncu --set full` capture
-# summarised in profiles/r01_tc_sampler_ncu_full.txt (taken at 148 events x 1280 samples = 189 440 rows per launch)
-NCU_SAMPLER_DRAM_BYTES = 10.40e6
-NCU_SAMPLER_TRAFFIC_NOTE = ("ncu capture at 189 440 rows/launch (profiles/r01_tc_sampler_ncu_full.txt): 10.4 MB read "
-                            "(5.5 MB bf16 weight image once + context projections), 0 B written back before kernel end; "
-                            "algorithmic 9.3 MB (49 B/row) -- tensor-bound kernel, HBM traffic is not the limiter")
+def ncu_traffic(rows_per_launch):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE tc_sampler_kernel launch at exactly this launch shape, from
+    a committed `ncu --set full` summary (profiles/r02_sampler_traffic.json: {"<rows per launch>": bytes}), else None:
+    a number captured at another shape is not this launch's traffic."""
+    p = os.path.join(ROOT, "profiles", "r02_sampler_traffic.json")
+    if os.path.exists(p):
+        v = json.load(open(p)).get(str(int(rows_per_launch)))
+        if v is not None:
+            return float(v["dram_bytes"]), v.get("note", "")
+    return None, "no ncu capture at this launch shape is committed"
 
 
 # ------------------------------------------------------------------------------------------------
@@ -194,7 +204,8 @@ def run_ours(args):
     torch.manual_seed(0)
     model = P.LeanNPE(tier=args.tier).to(dev)      # random-init weights, identical on every rank
     flow, scaler = model.flow, model.scaler
-    E, n, D = args.events, args.samples, 11
+    E = args.events if args.events is not None else TOTAL_EVENTS // world
+    n, D = args.samples, 11
     R = E * n
     g = torch.Generator().manual_seed(100 + rank)
     ctx_host = torch.randn(E, 256, generator=g).pin_memory()   # stands in for encoder output (encoder stays PyTorch)
@@ -259,6 +270,28 @@ def run_ours(args):
     ms_inf, launches_inf = timed(step_infer, args.steps, args.warmup)
     ms_sum, _ = timed(step_summary, args.steps, args.warmup)
 
+    # ---- BASELINE config #2: ONE event x 50 000 samples, sample blocks over the ranks (dist.shard_sampling), per-rank
+    # disjoint Philox keys; at 8 GPUs a 49-tile launch per GPU -- the latency regime of single-event serving ----
+    from posteriflow_b200 import dist as PD
+    c2_ctx = torch.randn(1, 256, generator=torch.Generator().manual_seed(5)).to(dev)     # same event on every rank
+    (_, _), (s0, s1) = PD.shard_sampling(1, 50000, rank, world)
+
+    def step_cfg2(i):
+        return PD.sample_posterior_sharded(model, c2_ctx, 0, 50000, seed=3000 + i, rank_world=(rank, world))
+
+    ms_c2, launches_c2 = timed(step_cfg2, args.steps, args.warmup)
+    # ---- BASELINE config #5: rank-conditioned sampling, events x ranks 0-2 x 10^4 samples through ONE launch
+    # (P.sample_ranks); bounded sub-sample of a GPU's 1250-event shard, throughput is row-count invariant ----
+    c5_ev = args.cfg5_events
+    c5_ctx = torch.randn(c5_ev, 256, generator=g).to(dev)
+
+    def step_cfg5(i):
+        return P.sample_ranks(model, c5_ctx, 3, 10000, seed=4000 + i)
+
+    ms_c5, launches_c5 = timed(step_cfg5, max(2, args.steps // 2), 3)
+    c5_steps = max(2, args.steps // 2)
+    c5_rows = c5_ev * 3 * 10000
+
     # NLL training step of the flow head (config #4 shard): forward + backward (+ gradient all-reduce)
     Bt = args.train_events
     nsig = torch.multinomial(torch.tensor([.55, .20, .12, .08, .05]), Bt, replacement=True, generator=g) + 1
@@ -275,6 +308,11 @@ def run_ours(args):
     gstep = P.GraphedNLLStep(model, distributed=(world > 1))
     flow_ids = {id(p) for p in gstep.flow_params}
     other_params = [p for p in params if id(p) not in flow_ids]      # rank embedding
+    # AdamW with lr = 0: the full optimizer arithmetic runs and every weight tensor is written in place (its version
+    # counter moves, so the NEXT step re-packs exactly as after a real update), but the benchmarked weights -- and with
+    # them every other number of this line -- stay those of the seeded random init.
+    opt = torch.optim.AdamW(params, lr=0.0, weight_decay=0.0, fused=True)
+    counted = {"kernels": 0}
 
     def step_train(i):
         """public training API: batch_nll forward + backward as one CUDA-graph replay (+ gradient all-reduce)"""
@@ -282,8 +320,17 @@ def run_ours(args):
             p.grad = None
         tctx.grad = None
         loss = gstep(params_b, nsig_dev, tctx)
+        counted["kernels"] += gstep.last_launches
         if world > 1:
             gstep.allreduce(extra_params=other_params)
+        return loss
+
+    def step_train_opt(i):
+        """what train_lean_npe.py:357-369 does around the flow: the step above + clip_grad_norm_(5.0) + AdamW.step();
+        the re-pack the updated weights need is paid by the next step's gstep() call, inside the timed region"""
+        loss = step_train(i)
+        torch.nn.utils.clip_grad_norm_(params, 5.0)
+        opt.step()
         return loss
 
     def step_train_eager(i):
@@ -296,9 +343,19 @@ def run_ours(args):
             allreduce_gradients(params)
         return loss
 
+    counted["kernels"] = 0
     ms_train, _ = timed(step_train, args.steps, args.warmup)
-    launches_train = gstep.last_launches * args.steps
+    launches_train = counted["kernels"] * args.steps // (args.steps + args.warmup)   # counted per call, timed calls only
+    l0 = fh.launches
+    ms_train_opt, pack_launches = timed(step_train_opt, args.steps, args.warmup)
     ms_train_eager, _ = timed(step_train_eager, args.steps, args.warmup)
+
+    def step_repack(i):
+        with torch.no_grad():
+            gstep.flow_params[0].add_(0.0)          # bump one version counter: the next handle() call re-packs
+        flow.handle()
+
+    ms_pack, launches_pack = timed(step_repack, args.steps, args.warmup)
 
     # config #4 un-sharded (4096 events on ONE GPU): reported at N = 1 only, next to the per-GPU shard above
     full = None
@@ -315,11 +372,21 @@ def run_ours(args):
             fctx.grad = None
             return gstep(params_f, nsig_f_dev, fctx)
 
+        def step_train_full_opt(i):
+            loss = step_train_full(i)
+            torch.nn.utils.clip_grad_norm_(params, 5.0)
+            opt.step()
+            return loss
+
         ms_full, _ = timed(step_train_full, args.steps, args.warmup)
+        ms_full_opt, _ = timed(step_train_full_opt, args.steps, args.warmup)
         Rf = int(nsig_f.sum())
+        tf_full = 3 * (F_X + F_CTX) * Rf * args.steps / (ms_full * 1e-3) / 1e12
         full = {"events": Bf, "flow_rows": Rf, "ms_per_step": ms_full / args.steps,
-                "steps_per_sec": args.steps / (ms_full * 1e-3), "gpu_launches": int(gstep.last_launches * args.steps),
-                "roofline_frac": 3 * (F_X + F_CTX) * Rf * args.steps / (ms_full * 1e-3) / 1e12 / float(peaks()[0]["bf16_tflops_sustained"]),
+                "steps_per_sec": args.steps / (ms_full * 1e-3), "kernels_per_step": int(gstep.last_launches),
+                "e2e_ms": ms_full_opt / args.steps,
+                "roofline_frac": tf_full / float(peaks()[0]["bf16_tflops_sustained"]),
+                "roofline_frac_burst": tf_full / float(peaks()[0]["bf16_tflops"]),
                 "kernels": "split-bf16 tcgen05 GEMMs (calls of >= 512 rows)" if args.tier == "bf16" else "FP32-FMA GEMMs"}
 
     pk, pk_kind = peaks()
@@ -327,14 +394,20 @@ def run_ours(args):
     flop_row = F_X + F_CTX / n
     ach = rows_s / world * flop_row / 1e12
     peak = float(pk["bf16_tflops_sustained"])
+    peak_burst = float(pk["bf16_tflops"])
     train_flop = 3 * (F_X + F_CTX) * Rt
     ach_t = train_flop * args.steps / (ms_train * 1e-3) / 1e12
+    traffic, traffic_note = ncu_traffic(R)
+    lp_tf = R * args.steps / (ms_lp * 1e-3) * flop_row / 1e12
+    c2_rows_s = 50000 * args.steps / (ms_c2 * 1e-3)
+    c5_rows_s = c5_rows * world * c5_steps / (ms_c5 * 1e-3)
     out = {
         "metric": "posterior_samples_per_sec", "value": rows_s, "unit": "samples/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32" if args.tier == "fp32" else "bf16 operands, f32 accumulate+spline",
+        "scaling": "strong" if args.events is None else "weak",
+        "vs_baseline": None, "dtype": "f32" if args.tier == "fp32" else "bf16 operands, f32 accumulate+spline",
         "data": "synthetic (random-init weights, N(0,1) contexts standing in for encoder output, in-kernel Philox base noise)",
-        "config": workload_config(world) if (E, n) == (EVENTS_PER_GPU, SAMPLES_PER_EVENT) else
+        "config": workload_config(world) if args.events is None else
         {"workload": f"{E} events x {n} samples per GPU (non-default)", "parallelism": f"events sharded over {world} GPU(s)"},
         "tier": args.tier + (" (sampler + log-prob: tcgen05 bf16 operands, fp32 accumulate + fp32 spline; training step: split-bf16 tcgen05 GEMMs, fp32 accumulate; FP32-FMA GEMMs for calls under 512 flow rows)"
                              if args.tier == "bf16" else ""),
@@ -345,18 +418,18 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                     "traffic": NCU_SAMPLER_DRAM_BYTES, "traffic_note": NCU_SAMPLER_TRAFFIC_NOTE,
-                     "peak_source": f"{pk_kind} bf16_tflops_sustained",
+                     "peak_burst": peak_burst, "frac_burst": ach / peak_burst,
+                     "traffic": traffic, "traffic_note": traffic_note,
+                     "peak_source": f"{pk_kind} bf16_tflops_sustained (frac) / bf16_tflops (frac_burst): the step is "
+                                    "long enough for the sustained figure, but no run so far reached the power cap",
                      "flop_per_row": flop_row,
                      "note": "whole sampler step per GPU (dense single-pass conditioner FLOPs, SURVEY 8d); "
                              "hbm: %.1f GB/s of algorithmic output (49 B/row)" % (rows_s / world * 49 / 1e9)},
         "log_prob": {"metric": "log_prob_rows_per_sec", "value": R * world * args.steps / (ms_lp * 1e-3), "unit": "rows/s",
                      "ms_per_step": ms_lp / args.steps, "gpu_launches": int(launches_lp),
                      "api": "NSFPosteriorFlow.compute_psd_aware_nll(y [R,11], context [E,288], n_per_ctx=n), no gradient",
-                     "roofline": {"bound": "tensor", "achieved": R * args.steps / (ms_lp * 1e-3) * flop_row / 1e12,
-                                  "peak": peak, "unit": "TFLOP/s",
-                                  "frac": R * args.steps / (ms_lp * 1e-3) * flop_row / 1e12 / peak,
-                                  "flop_per_row": flop_row}},
+                     "roofline": {"bound": "tensor", "achieved": lp_tf, "peak": peak, "unit": "TFLOP/s",
+                                  "frac": lp_tf / peak, "frac_burst": lp_tf / peak_burst, "flop_per_row": flop_row}},
         "infer_loop": {"metric": "samples_with_log_prob_per_sec", "value": R * world * args.steps / (ms_inf * 1e-3),
                        "unit": "samples/s", "ms_per_step": ms_inf / args.steps, "gpu_launches": int(launches_inf),
                        "api": "posteriflow_b200.posterior_chunk (pipeline.py:168-186 on the device: sampler -> wrap -> rail "
@@ -368,19 +441,44 @@ def run_ours(args):
                                  "peak": float(pk["hbm_gbs"]), "unit": "GB/s",
                                  "frac": R * D * 4 * args.steps / (ms_sum * 1e-3) / 1e9 / float(pk["hbm_gbs"]),
                                  "bytes_per_row": D * 4}},
+        "configs": {
+            "cfg1": "CPU-runnable smoke config of the reference (train a few steps -> sample): correctness only, its GPU "
+                    "analogue is tests/test_gpu_round2.py::test_three_adamw_steps_then_every_direction_matches_the_oracle",
+            "cfg2": {"workload": "1 event x 50 000 samples, rank 0, sample blocks over the GPUs (dist.shard_sampling), "
+                                 "disjoint Philox keys per rank", "rows_per_gpu": int(s1 - s0),
+                     "tiles_per_gpu": int((s1 - s0 + 127) // 128), "ms_per_call": ms_c2 / args.steps,
+                     "value": c2_rows_s, "unit": "samples/s", "gpu_launches": int(launches_c2),
+                     "roofline_frac": c2_rows_s / world * (F_X + F_CTX / (s1 - s0)) / 1e12 / peak,
+                     "note": "latency regime: one 128-row tile per SM at most, the call is bound by one tile's 660-stage chain"},
+            "cfg3": "the headline of this line",
+            "cfg4": "train (per-GPU shard of the 4096-event batch) and train.full_batch_1gpu",
+            "cfg5": {"workload": f"rank-conditioned overlap sampling through ONE launch (posteriflow_b200.sample_ranks): "
+                                 f"{c5_ev} events x ranks 0-2 x 10 000 samples per GPU -- SUB-SAMPLE of the "
+                                 f"{10000 // max(world, 8)}-event shard a GPU holds at 8 GPUs; throughput is row-count invariant",
+                     "rows_per_gpu": c5_rows, "ms_per_step": ms_c5 / c5_steps, "value": c5_rows_s, "unit": "samples/s",
+                     "gpu_launches": int(launches_c5),
+                     "roofline_frac": c5_rows_s / world * (F_X + F_CTX / 10000) / 1e12 / peak,
+                     "full_config_seconds_extrapolated": 3e8 / max(c5_rows_s, 1.0)}},
         "train": {"metric": "nll_train_steps_per_sec", "value": args.steps / (ms_train * 1e-3), "unit": "steps/s",
                   "events_per_gpu": Bt, "flow_rows_per_gpu": Rt, "ms_per_step": ms_train / args.steps,
-                  "gpu_launches": int(launches_train), "ms_per_step_eager_autograd": ms_train_eager / args.steps,
+                  "gpu_launches": int(launches_train), "kernels_per_step": int(gstep.last_launches),
+                  "e2e_ms": ms_train_opt / args.steps,
+                  "e2e_includes": "flow-only step + torch.nn.utils.clip_grad_norm_(5.0) + fused AdamW.step() over all flow "
+                                  "+ rank-embedding parameters + the re-pack of the updated weights (train_lean_npe.py:363-368); "
+                                  "lr = 0 keeps the benchmarked weights fixed while every tensor is rewritten in place",
+                  "repack_ms": ms_pack / args.steps, "repack_launches": int(launches_pack // max(1, args.steps)),
+                  "ms_per_step_eager_autograd": ms_train_eager / args.steps,
                   "full_batch_1gpu": full,
                   "api": "posteriflow_b200.GraphedNLLStep (batch_nll forward + backward captured in one CUDA graph per "
-                         "row bucket; weight / bias / context gradients on a side stream; split-bf16 tcgen05 GEMMs from "
-                         "512 rows per call)",
+                         "row bucket)",
                   "includes": "batch_nll (one flow call for all signal ranks): row gather, scaler.normalize, rank embedding, flow "
                               "forward+backward (all weights, context), "
                               + ("NCCL gradient all-reduce" if world > 1 else "no all-reduce at 1 GPU")
-                              + "; encoder and optimizer excluded (encoder stays reference PyTorch)",
+                              + "; EXCLUDED: the strain encoder (north_star leaves it in PyTorch; synthetic N(0,1) contexts of "
+                                "its output shape [B,256] stand in for encoder(strain [B,3,16384])) and, in ms_per_step, the "
+                                "optimizer (see e2e_ms)",
                   "roofline": {"bound": "tensor", "achieved": ach_t, "peak": peak, "unit": "TFLOP/s",
-                               "frac": ach_t / peak, "flop_per_row": 3 * (F_X + F_CTX)}},
+                               "frac": ach_t / peak, "frac_burst": ach_t / peak_burst, "flop_per_row": 3 * (F_X + F_CTX)}},
     }
     if rank == 0:
         if not args.no_cpu and world == 1:
@@ -397,7 +495,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--tier", default=os.environ.get("PF_TIER", "bf16"), choices=["fp32", "bf16"])
-    ap.add_argument("--events", type=int, default=EVENTS_PER_GPU)
+    ap.add_argument("--events", type=int, default=None, help="events PER GPU (default: 4096 / N, strong scaling)")
+    ap.add_argument("--cfg5-events", type=int, default=CFG5_EVENTS_PER_GPU)
     ap.add_argument("--samples", type=int, default=SAMPLES_PER_EVENT)
     ap.add_argument("--train-events", type=int, default=TRAIN_EVENTS_PER_GPU)
     ap.add_argument("--train-events-full", type=int, default=4096, help="config #4 un-sharded, timed at N=1 (0 = skip)")

@@ -150,9 +150,46 @@ def glue_case() -> None:
     print("wrote lean_glue.npz")
 
 
+def quantile_case(name: str, seed: int, stress: bool, E: int = 2, n: int = 8000) -> None:
+    """Posterior-scale fixture for the bf16 tier's quantile / KS / log q checks: E events x n samples
+    drawn by the REFERENCE flow (float32, as it runs) from a seeded base noise, plus the reference's own float64
+    log-det and NLL of exactly those samples.  z is regenerated on the test machine from the stored seed (CPU
+    generator, deterministic); only the outputs are stored."""
+    spec = O.FlowSpec()
+    w = O.init_weights(spec, seed=seed, stress=stress)
+    flow32 = reference_flow(spec, w)
+    flow64 = reference_flow(spec, w).double()
+    g = torch.Generator().manual_seed(1000 + seed)
+    ctx = torch.randn(E, spec.context_features, generator=g)
+    z = torch.randn(E * n, spec.features, generator=g)
+    cr = ctx.repeat_interleave(n, dim=0)
+    with torch.no_grad():
+        xs, lds = [], []
+        for i in range(0, E * n, 4096):
+            x, ld = flow32.inverse(z[i:i + 4096], cr[i:i + 4096])
+            xs.append(x); lds.append(ld)
+        x32, ild32 = torch.cat(xs), torch.cat(lds)
+        f64, n64 = [], []
+        for i in range(0, E * n, 4096):
+            xx, cc = x32[i:i + 4096].double(), cr[i:i + 4096].double()
+            f64.append(flow64.forward(xx, cc)[1])
+            n64.append(flow64.compute_psd_aware_nll(xx, cc, torch.zeros_like(xx)))
+    out = {"spec": spec_array(spec), "seed": np.int64(seed), "stress": np.bool_(stress),
+           "weights_checksum": np.float64(O.weights_checksum(w)), "E": np.int64(E), "n": np.int64(n),
+           "noise_seed": np.int64(1000 + seed), "z_checksum": np.float64(float(z.double().abs().sum())),
+           "ctx": ctx.numpy(), "inv_x_f32": x32.numpy(), "inv_logdet_f32": ild32.numpy(),
+           "fwd_logdet_f64": torch.cat(f64).numpy(), "nll_f64": torch.cat(n64).numpy()}
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+    print(f"wrote {name}.npz  E={E} n={n}  clamped fraction {float((x32.abs() >= 3).float().mean()):.4f}")
+
+
 def main() -> None:
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(max(1, os.cpu_count() or 1))
+    if "--quantiles-only" in sys.argv:
+        quantile_case("lean_quantiles_default", seed=0, stress=False)
+        quantile_case("lean_quantiles_stress", seed=1, stress=True)
+        return
     flow_case("lean_default", O.FlowSpec(), seed=0, stress=False, R=64)
     flow_case("lean_stress", O.FlowSpec(), seed=1, stress=True, R=64)
     flow_case("lean_stress_1layer", O.FlowSpec(num_layers=1), seed=5, stress=True, R=64)
@@ -161,6 +198,8 @@ def main() -> None:
     flow_case("head_12x384x24", O.FlowSpec(11, 288, 384, 12, 24, 3.0), seed=3, stress=True, R=32, grads=False)
     flow_case("tiny_explicit", O.FlowSpec(5, 12, 32, 3, 8, 2.0), seed=4, stress=True, R=48, store_weights=True)
     glue_case()
+    quantile_case("lean_quantiles_default", seed=0, stress=False)
+    quantile_case("lean_quantiles_stress", seed=1, stress=True)
 
 
 if __name__ == "__main__":

@@ -40,21 +40,26 @@ def _world() -> Tuple[int, int]:
     return 0, 1
 
 
+def shard_seed(seed: int, rank: int) -> int:
+    """Philox key of a rank's shard: the in-kernel counter is the LOCAL row index, so the key carries the shard --
+    distinct keys give statistically independent, non-overlapping streams (no row can repeat across ranks)."""
+    return (int(seed) * 1000003 + int(rank)) & (2 ** 63 - 1)
+
+
 def sample_posterior_sharded(model, context: torch.Tensor, rank_index: int, n_samples: int, seed: int = 0,
-                             gather: bool = False) -> torch.Tensor:
+                             gather: bool = False, rank_world: Optional[Tuple[int, int]] = None) -> torch.Tensor:
     """This rank's share of `LeanNPE.sample_posterior` for `context` [E, context_dim] (same on every rank).
 
     Returns theta [E_local, n_local, D]; `gather=True` all-gathers the shards (equal shard sizes required)
     into the full [E, n, D] on every rank -- an optional convenience, not part of the hot path."""
-    r, w = _world()
+    r, w = rank_world if rank_world is not None else _world()   # (rank, world) override: single-process tests
     (e0, e1), (s0, s1) = shard_sampling(context.shape[0], n_samples, r, w)
     ctx = context[e0:e1]
     from .lean import sample_fused
     rk = torch.full((ctx.shape[0],), rank_index, dtype=torch.long, device=ctx.device)
     full = model._full_context(ctx, rk)
-    # distinct Philox streams per rank: the counter is the local row index, so the key carries the shard
-    theta = sample_fused(model.flow, model.scaler, full, s1 - s0, z=None, seed=(seed * 1000003 + r) & (2 ** 63 - 1))[0]
-    if not gather or w == 1:
+    theta = sample_fused(model.flow, model.scaler, full, s1 - s0, z=None, seed=shard_seed(seed, r))[0]
+    if not gather or w == 1 or rank_world is not None:
         return theta
     parts = [torch.empty_like(theta) for _ in range(w)]
     dist.all_gather(parts, theta.contiguous())

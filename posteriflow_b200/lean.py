@@ -98,6 +98,38 @@ def posterior_chunk(flow: NSFPosteriorFlow, scaler: ParamScaler, ctx_full: Tenso
     return theta.reshape(E, n, D), logq, railed
 
 
+def sample_ranks(model, context: Tensor, max_rank: int, n_samples: int, z: Optional[Tensor] = None, seed: int = 0,
+                 sort_masses: bool = True) -> Tensor:
+    """scripts/overlap_benchmark.py:40-64 `sample_ranks` after the encoder: posterior draws for ranks
+    0..max_rank-1 of each event, [N, max_rank, K, 11] physical with m1 >= m2 -- as ONE launch of the fused sampler
+    instead of one flow call per rank: the N * max_rank (event, rank) contexts are laid out event-major / rank-minor
+    and each serves its K consecutive flow rows (BASELINE config #5).  `z` ([N*max_rank*K, 11], same order) fixes
+    the base noise; otherwise it is drawn in-kernel."""
+    N = context.shape[0]
+    ev = torch.arange(N, device=context.device).repeat_interleave(max_rank)
+    rk = torch.arange(max_rank, device=context.device).repeat(N)
+    ctx = model._full_context(context.index_select(0, ev), rk)            # [N * max_rank, C]
+    flags = SAMPLE_FLAGS | (A.PF_FLAG_SORT_MASSES if sort_masses else 0)
+    theta, _, _ = sample_fused(model.flow, model.scaler, ctx, n_samples, z=z, seed=seed, flags=flags)
+    return theta.reshape(N, max_rank, n_samples, theta.shape[-1])
+
+
+def symmetrized_log_q(model, theta: Tensor, ctx_full: Tensor, j1: int = 0, j2: int = 1) -> Tensor:
+    """inference/importance.py:69-95 on the device: log[q(m1, m2, ..) + q(m2, m1, ..)] in physical units for
+    theta [N, 11] of ONE event (`ctx_full` [1, C] = `_full_context(encoder(strain), rank)`).  The reference runs two
+    flow passes per batch of 2048; here both mass orderings go through the flow as ONE call of 2N rows that share the
+    event's context projection, followed by the physical-density epilogue and a logaddexp."""
+    sc = model.scaler
+    N, D = theta.shape
+    sw = theta.clone()
+    sw[:, [j1, j2]] = theta[:, [j2, j1]]
+    y = sc.normalize(torch.cat([theta, sw], dim=0))
+    with torch.no_grad():
+        nll = model.flow.compute_psd_aware_nll(y, ctx_full[:1], None, n_per_ctx=2 * N)
+        _, logq = torch.ops.posteriflow.nsf_physical(y, nll, False, sc.lo, sc.hi, sc.log_mask, sc.circ_mask)
+    return torch.logaddexp(logq[:N], logq[N:])
+
+
 class LeanNPE(nn.Module):
     """encoder (caller's PyTorch module) + rank embedding + B200 flow (lean_npe.py:255-338).
 

@@ -72,3 +72,17 @@ def test_masks_and_counts():
     w = O.init_weights(spec)
     n = sum(v.numel() for k, v in w.items() if k.endswith((".weight", ".bias")))
     assert n == 6210610 and n // 10 == 621061
+
+
+def test_quantile_fixture_is_reproduced_by_the_oracle():
+    """The posterior-scale fixture (16 000 samples of the reference flow, oracle/make_golden.py:quantile_case): the base
+    noise regenerates from its seed, and the standalone oracle reproduces a slice of the stored samples."""
+    from util import load_quantile_fixture
+    spec, w, g, ctx, z = load_quantile_fixture("lean_quantiles_default")
+    n = int(g["n"])
+    with torch.no_grad():
+        x, ld = O.flow_inverse(spec, w, z[n:n + 192], ctx[1:2].expand(192, -1))
+        nll = O.flow_nll(spec, w, t(g["inv_x_f32"])[:192], ctx[0:1].expand(192, -1))
+    assert rel_err(x.numpy(), g["inv_x_f32"][n:n + 192]) <= 2e-5
+    assert rel_err(ld.numpy(), g["inv_logdet_f32"][n:n + 192]) <= 2e-5
+    assert rel_err(nll.numpy(), g["nll_f64"][:192]) <= 1e-3      # float32 evaluation against the stored float64 one

@@ -77,3 +77,15 @@ def check_parity(name, got, ref32, ref64=None, tol=TOL, scale=None, median_facto
     assert ok, (f"{name}: vs f32 max {e32.max():.3e}; vs f64 median {np.median(e):.3e} max {e.max():.3e}; "
                 f"f32 reference's own vs f64 median {np.median(own):.3e} max {own.max():.3e}")
     return arbitrated
+
+
+def load_quantile_fixture(name):
+    """(spec, w, g, ctx [E, C], z [E*n, D]) of a `lean_quantiles_*` fixture; z regenerated from its stored seed."""
+    spec, w, g = load_golden(name)
+    E, n = int(g["E"]), int(g["n"])
+    gen = torch.Generator().manual_seed(int(g["noise_seed"]))
+    ctx = torch.randn(E, spec.context_features, generator=gen)
+    z = torch.randn(E * n, spec.features, generator=gen)
+    assert float((ctx - t(g["ctx"])).abs().max()) == 0.0
+    assert abs(float(z.double().abs().sum()) - float(g["z_checksum"])) <= 1e-9 * float(g["z_checksum"])
+    return spec, w, g, ctx, z
