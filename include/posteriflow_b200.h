@@ -55,7 +55,12 @@ enum {
 /* arithmetic tier of the conditioner GEMMs */
 enum {
   PF_TIER_FP32 = 0, /* FP32 FMA everywhere: parity tier, |dtheta|,|dlogq| <= 1e-4 rel      */
-  PF_TIER_BF16 = 1  /* bf16 operands on tcgen05 tensor cores, fp32 accumulate + spline     */
+  PF_TIER_BF16 = 1, /* bf16 operands on tcgen05 tensor cores, fp32 accumulate + spline     */
+  /* Split-bf16 operands on tcgen05 (each factor as a bf16 hi + lo pair, three MMAs per product, fp32 accumulate) and the
+   * exact fp32 spline: the tensor-core tier that meets the FP32 tolerance.  Serves the DENSITY direction (forward /
+   * log-prob / NLL, and the fused training step); the sampling direction of such a handle runs on the FP32-FMA
+   * kernels -- ten split activation arrays of a 128-row tile do not fit in one SM's shared + tensor memory. */
+  PF_TIER_BF16X3 = 2
 };
 
 /* flags for pf_flow_inverse / pf_flow_forward / pf_sample_fused */

@@ -11,7 +11,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(PKG, "lib", "libposteriflow_b200.so")
 
 PF_OK = 0
-PF_TIER_FP32, PF_TIER_BF16 = 0, 1
+PF_TIER_FP32, PF_TIER_BF16, PF_TIER_BF16X3 = 0, 1, 2
 PF_FLAG_SANITIZE_CTX = 1 << 0
 PF_FLAG_CLAMP = 1 << 1
 PF_FLAG_WRAP = 1 << 2

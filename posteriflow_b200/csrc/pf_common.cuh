@@ -109,6 +109,7 @@ struct pf_flow {
   void* tc;              // NULL when tier != PF_TIER_BF16
   int UF;                // padded per-dim parameter count (MULT rounded up to 4)
   void* dense;           // dense density-direction kernel state (pf_tc_dense.cu), NULL when the shape is not covered
+  void* train;           // fused training-step state (pf_tc_train.cu): backward weight images
   // training path of the tensor-core tier (pf_tc_gemm.cuh): split-bf16 tcgen05 GEMMs instead of the FP32-FMA ones
   bool train_tc;         // tier == PF_TIER_BF16 and PF_TRAIN_TC != 0
   int train_tc_min_rows; // calls with fewer flow rows stay on the FP32-FMA GEMMs (PF_TRAIN_TC_MIN_ROWS, default 512)
@@ -151,4 +152,9 @@ pf_status pf_dn_pack(pf_flow* f, cudaStream_t st);
 void pf_dn_destroy(pf_flow* f);
 pf_status pf_dn_forward(pf_flow* f, cudaStream_t st, const float* x, const float* ctx, const int64_t* row2ctx,
                         int64_t n_per_ctx, int64_t R, int64_t E, float* z, float* logdet, uint32_t flags,
-                        void* workspace, size_t workspace_bytes, int* err);
+                        void* workspace, size_t workspace_bytes, int* err, int split);
+pf_status pf_dn_forward_save(pf_flow* f, cudaStream_t st, const float* x, const float* proj, int64_t R, float* z,
+                             float* logdet, uint8_t* img, uint8_t* xt, float* P, float* XS);
+// fused training step, backward side (pf_tc_train.cu)
+pf_status pf_tt_pack(pf_flow* f, cudaStream_t st);
+void pf_tt_destroy(pf_flow* f);

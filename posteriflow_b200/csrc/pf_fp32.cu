@@ -356,14 +356,25 @@ extern "C" pf_status pf_flow_forward(pf_flow* f, const float* x, const float* ct
   PF_CUDA(cudaSetDevice(f->desc.device));
   cudaStream_t st = (cudaStream_t)stream;
   const int D = f->D, H = f->H, L = f->L, PLD = f->PLD, P = f->P;
-  if (f->desc.tier == PF_TIER_BF16 && !saved) {
-    // inference form (no activations kept): the density direction runs on the tensor-core kernel too
+  const bool x3_dense = f->desc.tier == PF_TIER_BF16X3 && f->dense && !(flags & PF_FLAG_CTX_IS_PROJ);
+  if ((f->desc.tier == PF_TIER_BF16 || x3_dense) && !saved) {
+    // inference form (no activations kept): the density direction runs on the tensor-core kernels too -- bf16 operands
+    // (PF_TIER_BF16) or split operands + exact spline (PF_TIER_BF16X3: the dense kernel at the FP32 tolerance)
     const size_t tcb = (pf_tc_workspace_bytes(f, R, E) + 255) / 256 * 256;
     const size_t need = tcb + pad256((size_t)R * D) + pad256((size_t)R);
     if (!workspace || workspace_bytes < need) return PF_ERR_WORKSPACE;
     float* zb = z ? z : reinterpret_cast<float*>((char*)workspace + tcb);
     float* lb = logdet ? logdet : reinterpret_cast<float*>((char*)workspace + tcb + pad256((size_t)R * D));
-    PF_TRY(pf_tc_forward(f, st, x, ctx, row2ctx, n_per_ctx, R, E, zb, lb, flags, workspace, tcb));
+    if (x3_dense) {
+      PF_TRY(pf_dn_forward(f, st, x, ctx, row2ctx, n_per_ctx, R, E, zb, lb, flags & PF_FLAG_SANITIZE_CTX, workspace, tcb,
+                           f->tg_err, 3));
+      if (f->train_debug) {
+        PF_CUDA(cudaStreamSynchronize(st));
+        PF_TRY(pf_check_flag(f, "split dense density kernel"));
+      }
+    } else {
+      PF_TRY(pf_tc_forward(f, st, x, ctx, row2ctx, n_per_ctx, R, E, zb, lb, flags, workspace, tcb));
+    }
     if (nll) {
       if (R > 0x7fffffff) return PF_ERR_INVALID;
       nll_kernel<<<(unsigned)((R + 255) / 256), 256, 0, st>>>(zb, lb, log_sigma, D, (int)R, nll);
@@ -919,7 +930,7 @@ extern "C" size_t pf_flow_workspace_bytes(const pf_flow* f, int32_t op, int64_t 
     case PF_OP_CTXPROJ: return 0;
     case PF_OP_FORWARD: {  // + full-length z / logdet scratch for the saved (training) form
       size_t b = FwdWs(f, nullptr, 0, chunk, prow, true).bytes + pad256((size_t)R * f->D) + pad256((size_t)R) + 256;
-      if (f->desc.tier == PF_TIER_BF16) {
+      if (f->desc.tier == PF_TIER_BF16 || f->desc.tier == PF_TIER_BF16X3) {
         size_t t = (pf_tc_workspace_bytes(f, R, E) + 255) / 256 * 256 + pad256((size_t)R * f->D) + pad256((size_t)R) + 256;
         if (t > b) b = t;
       }

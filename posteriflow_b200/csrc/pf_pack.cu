@@ -74,7 +74,7 @@ extern "C" pf_status pf_flow_create(const pf_flow_desc* d, pf_flow** out) {
       d->hidden_features < d->features - 1 || d->hidden_features % 4 != 0 || d->hidden_features > 1024 ||
       d->context_features < 1 || d->num_layers < 1 || d->num_blocks != 2 || !(d->tail_bound > 0.f))
     return PF_ERR_INVALID;
-  if (d->tier != PF_TIER_FP32 && d->tier != PF_TIER_BF16) return PF_ERR_INVALID;
+  if (d->tier != PF_TIER_FP32 && d->tier != PF_TIER_BF16 && d->tier != PF_TIER_BF16X3) return PF_ERR_INVALID;
   // nflows raises when min_bin_width * num_bins > 1
   if (1e-3 * d->num_bins > 1.0) return PF_ERR_INVALID;
   int ndev = 0;
@@ -92,7 +92,7 @@ extern "C" pf_status pf_flow_create(const pf_flow_desc* d, pf_flow** out) {
   {
     const char* tt = getenv("PF_TRAIN_TC");
     const char* dbg = getenv("PF_TC_DEBUG");
-    f->train_tc = d->tier == PF_TIER_BF16 && !(tt && tt[0] == '0');
+    f->train_tc = (d->tier == PF_TIER_BF16 || d->tier == PF_TIER_BF16X3) && !(tt && tt[0] == '0');
     f->train_debug = dbg && dbg[0] == '1';
     const char* mr = getenv("PF_TRAIN_TC_MIN_ROWS");
     f->train_tc_min_rows = mr ? atoi(mr) : 512;

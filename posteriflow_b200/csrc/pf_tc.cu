@@ -1122,7 +1122,7 @@ pf_status pf_tc_forward(pf_flow* f, cudaStream_t st, const float* x, const float
   TcState* t = reinterpret_cast<TcState*>(f->tc);
   const char* dn = getenv("PF_TC_DENSE");
   if (f->dense && t && !(fl & PF_FLAG_CTX_IS_PROJ) && !(dn && dn[0] == '0')) {
-    PF_TRY(pf_dn_forward(f, st, x, ctx, row2ctx, n_per_ctx, R, E, z, logdet, fl, workspace, workspace_bytes, f->tg_err));
+    PF_TRY(pf_dn_forward(f, st, x, ctx, row2ctx, n_per_ctx, R, E, z, logdet, fl, workspace, workspace_bytes, f->tg_err, 1));
     if (t->debug_sync) {
       PF_CUDA(cudaStreamSynchronize(st));
       PF_TRY(pf_check_flag(f, "dense density kernel"));

@@ -95,7 +95,8 @@ class _FlowAlias(nn.Module):
 class NSFPosteriorFlow(nn.Module):
     """Conditional masked-autoregressive RQ-spline flow, B200-native (flows.py:363-548 replaced).
 
-    Extra, non-reference keyword: `tier` ("fp32" parity tier | "bf16" tensor-core tier).
+    Extra, non-reference keyword: `tier` ("fp32" parity tier | "bf16" tensor-core tier | "bf16x3" split-bf16
+    tensor-core tier at the FP32 tolerance for the density direction / training; it samples on the FP32-FMA kernels).
     Extra, non-reference argument on `inverse` / `forward`: `n_per_ctx` -- context row e serves flow
     rows [e*n, (e+1)*n) so the context is projected once per event instead of being repeated
     (lean_npe.py:328).  With n_per_ctx=None the reference's dense [R, C] form is used; a context that
@@ -121,7 +122,7 @@ class NSFPosteriorFlow(nn.Module):
         self.tail_bound = float(tail_bound)
         self.max_overlaps = max_overlaps
         self.use_masked_context = False
-        self.tier = {"fp32": A.PF_TIER_FP32, "bf16": A.PF_TIER_BF16}[tier]
+        self.tier = {"fp32": A.PF_TIER_FP32, "bf16": A.PF_TIER_BF16, "bf16x3": A.PF_TIER_BF16X3}[tier]
         self.temperature = nn.Parameter(torch.tensor(temperature_scale, dtype=torch.float32))
         self.temperature_scale_init = temperature_scale
         mult = 3 * num_bins - 1
@@ -198,7 +199,8 @@ class NSFPosteriorFlow(nn.Module):
             n = 1
         w = self.layer_weights()
         need = torch.is_grad_enabled() and (x.requires_grad or context.requires_grad or any(p.requires_grad for p in w))
-        z, logdet, _ = torch.ops.posteriflow.nsf_forward(x, context, w, fh.id, n, bool(need), row2ctx)
+        z, logdet, _ = torch.ops.posteriflow.nsf_forward(x, context, w, fh.id, n, bool(need),
+                                                         row2ctx if row2ctx is not None else ops.no_row2ctx(x))
         return z, logdet
 
     def inverse(self, z: Tensor, context: Tensor = None, n_overlaps: Optional[Tensor] = None,
@@ -231,7 +233,8 @@ class NSFPosteriorFlow(nn.Module):
                                             or (log_sigma_psd is not None and log_sigma_psd.requires_grad))
         if not need:
             return torch.ops.posteriflow.nsf_nll(x, ctx, log_sigma_psd, fh.id, n, row2ctx)
-        z, logdet, _ = torch.ops.posteriflow.nsf_forward(x, ctx, w, fh.id, n, True, row2ctx)
+        z, logdet, _ = torch.ops.posteriflow.nsf_forward(x, ctx, w, fh.id, n, True,
+                                                         row2ctx if row2ctx is not None else ops.no_row2ctx(x))
         const = self.features * math.log(2 * math.pi)
         if log_sigma_psd is None:
             logp = -0.5 * ((z * z).sum(dim=1) + const)

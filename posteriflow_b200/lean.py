@@ -199,8 +199,10 @@ class LeanNPE(nn.Module):
         seed = 0 if z is not None else int(torch.randint(0, 2 ** 62, (1,)).item())
         return posterior_chunk(self.flow, self.scaler, ctx, n_samples, z=z, seed=seed, sort_masses=sort_masses)
 
-    def to(self, *args, **kwargs):
-        out = super().to(*args, **kwargs)
+    def _apply(self, fn, *args, **kwargs):
+        # .to() / .cuda() / .cpu(): the ParamScaler tensors are plain attributes (lean_npe.py:87-98), they follow the
+        # parameters (the reference moves them in its own `to`, lean_npe.py:334-338)
+        out = super()._apply(fn, *args, **kwargs)
         self.scaler.to(next(self.parameters()).device)
         return out
 

@@ -179,12 +179,13 @@ def _r2c(row2ctx: Optional[Tensor]) -> Optional[Tensor]:
 # ------------------------------------------------------------------------------------------------
 @torch.library.custom_op("posteriflow::nsf_forward", mutates_args=())
 def nsf_forward(x: Tensor, ctx: Tensor, weights: Sequence[Tensor], handle: int, n_per_ctx: int,
-                save: bool, row2ctx: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor]:
+                save: bool, row2ctx: Tensor) -> Tuple[Tensor, Tensor, Tensor]:
     """NSFPosteriorFlow.forward (flows.py:610-618): (z [R,D], logdet [R], saved activations).
-    `row2ctx` ([R] int64) addresses the context row of every flow row explicitly instead of `row // n_per_ctx`."""
+    `row2ctx` ([R] int64) addresses the context row of every flow row explicitly instead of `row // n_per_ctx`;
+    an EMPTY tensor means "not given" (this op is differentiable: its inputs keep a fixed tensor structure)."""
     _require_cuda(x, ctx)
     fh = get_handle(handle)
-    x, ctx, row2ctx = _f32c(x), _f32c(ctx), _r2c(row2ctx)
+    x, ctx, row2ctx = _f32c(x), _f32c(ctx), (_r2c(row2ctx) if row2ctx.numel() else None)
     R, E = _rows(x, ctx, n_per_ctx, row2ctx)
     z = torch.empty_like(x)
     logdet = torch.empty(R, dtype=torch.float32, device=x.device)
@@ -199,8 +200,12 @@ def nsf_forward(x: Tensor, ctx: Tensor, weights: Sequence[Tensor], handle: int, 
 
 
 @nsf_forward.register_fake
-def _(x, ctx, weights, handle, n_per_ctx, save, row2ctx=None):
+def _(x, ctx, weights, handle, n_per_ctx, save, row2ctx):
     return torch.empty_like(x), x.new_empty(x.shape[0]), x.new_empty(0, dtype=torch.uint8)
+
+
+def no_row2ctx(like: Tensor) -> Tensor:
+    return torch.empty(0, dtype=torch.int64, device=like.device)
 
 
 @torch.library.custom_op("posteriflow::nsf_backward", mutates_args=())
@@ -246,15 +251,14 @@ def _fwd_setup(ctx, inputs, output):
     _, _, saved = output
     if not save:
         raise RuntimeError("nsf_forward was called with save=False but a gradient is required")
-    ctx.has_r2c = row2ctx is not None
-    ctx.save_for_backward(saved, c, *([row2ctx] if ctx.has_r2c else []), *weights)
+    ctx.save_for_backward(saved, c, row2ctx, *weights)
     ctx.handle, ctx.n_per_ctx = handle, n_per_ctx
 
 
 def _fwd_backward(ctx, gz, glogdet, gsaved):
-    saved, c, *rest = ctx.saved_tensors
-    row2ctx = rest.pop(0) if ctx.has_r2c else None
-    outs = torch.ops.posteriflow.nsf_backward(saved, c, gz, glogdet, rest, ctx.handle, ctx.n_per_ctx, row2ctx)
+    saved, c, row2ctx, *weights = ctx.saved_tensors
+    outs = torch.ops.posteriflow.nsf_backward(saved, c, gz, glogdet, weights, ctx.handle, ctx.n_per_ctx,
+                                              row2ctx if row2ctx.numel() else None)
     return outs[0], outs[1], list(outs[2:]), None, None, None, None
 
 

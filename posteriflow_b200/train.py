@@ -101,9 +101,11 @@ class GraphedNLLStep:
         fh = m.flow.handle()
         weights = [p.detach() for p in self.flow_params]
         const = D * math.log(2 * math.pi)
+        from .ops import no_row2ctx
+        no_r2c = no_row2ctx(st["x"])
 
         def body():
-            z, ld, saved = torch.ops.posteriflow.nsf_forward(st["x"], st["ctx"], weights, fh.id, 1, True)
+            z, ld, saved = torch.ops.posteriflow.nsf_forward(st["x"], st["ctx"], weights, fh.id, 1, True, no_r2c)
             nll = 0.5 * ((z * z).sum(dim=1) + const) - ld
             loss = (nll * st["w"]).sum()
             outs = torch.ops.posteriflow.nsf_backward(saved, st["ctx"], z * st["w"].unsqueeze(1), -st["w"], weights,

@@ -13,7 +13,7 @@ E = int(sys.argv[1]) if len(sys.argv) > 1 else 512
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 5000
 dev = torch.device("cuda:0")
 torch.manual_seed(0)
-m = P.LeanNPE(tier="bf16").to(dev)
+m = P.LeanNPE(tier=os.environ.get("PF_TIER", "bf16")).to(dev)
 ctx = m._full_context(torch.randn(E, 256, device=dev), torch.zeros(E, dtype=torch.long, device=dev))
 y = (torch.rand(E * n, 11, device=dev) * 2 - 1)
 with torch.no_grad():

@@ -55,7 +55,7 @@ def main():
 
     def step_raw():
         fh.ensure_packed(weights)
-        z, ld, saved = torch.ops.posteriflow.nsf_forward(x, ctx, weights, fh.id, 1, True)
+        z, ld, saved = torch.ops.posteriflow.nsf_forward(x, ctx, weights, fh.id, 1, True, P.ops.no_row2ctx(x))
         return torch.ops.posteriflow.nsf_backward(saved, ctx, gz, gl, weights, fh.id, 1)
 
     def timeit(fn, steps=20, warm=5):
