@@ -128,6 +128,7 @@ struct pf_flow {
   cudaEvent_t ev_main[2], ev_side[2][NSIDE];
   bool train_streams;    // PF_TRAIN_STREAMS != 0
   bool train_pdl;        // PF_TRAIN_PDL != 0: programmatic dependent launch of the tcgen05 training GEMMs
+  bool train_fused;      // PF_TRAIN_FUSED != 0: forward-with-saves / backward / weight gradients as three persistent kernels
 };
 
 // Host side of the error flag: non-blocking read (+ clear).  PF_ERR_CUDA with a message when a kernel of an EARLIER,

@@ -17,6 +17,7 @@
 #include "pf_tc_gemm.cuh"
 #include "pf_spline.cuh"
 #include "pf_tail.cuh"
+#include "pf_train.cuh"
 
 namespace pf {
 
@@ -310,9 +311,20 @@ struct SavedLayout {
   float* a(const pf_flow* f, int64_t R, int l, int which) const { return act + ((size_t)l * 7 + which) * R * f->H; }
 };
 
+// The fused training step (pf_train.cuh) serves the dense-context form (one context row per flow row: what batch_nll /
+// LeanNPE.nll pass) of handles whose shape the dense tensor-core kernels cover.
+static inline bool fused_train(const pf_flow* f, const int64_t* row2ctx, int64_t n_per_ctx) {
+  return f->train_fused && f->train && f->dense && !row2ctx && n_per_ctx == 1;
+}
+
 extern "C" size_t pf_flow_saved_bytes(const pf_flow* f, int64_t R, int64_t E) {
   if (!f || R < 0 || E < 0) return 0;
-  return SavedLayout(f, nullptr, R, E).bytes;
+  size_t b = SavedLayout(f, nullptr, R, E).bytes;
+  if (f->train_fused && f->train && f->dense) {
+    const size_t t = TtSaved(f, nullptr, R).bytes;
+    if (t > b) b = t;
+  }
+  return b;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -381,6 +393,29 @@ extern "C" pf_status pf_flow_forward(pf_flow* f, const float* x, const float* ct
       PF_LAUNCH_CHECK(f);
     }
     return PF_OK;
+  }
+  if (saved && fused_train(f, row2ctx, n_per_ctx)) {
+    // ---- fused training forward: context projection GEMM + ONE persistent kernel over all layers (pf_tc_dense.cu) ----
+    if (R > 8000000) return PF_ERR_INVALID;
+    TtSaved sv(f, saved, R);
+    const int64_t ldp = (int64_t)L * 3 * H;
+    if (flags & PF_FLAG_CTX_IS_PROJ) {
+      const int64_t n = R * ldp;
+      copy_rows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(ctx, sv.proj, n);
+      PF_LAUNCH_CHECK(f);
+    } else {
+      PF_TRY(ctxproj_impl(f, st, ctx, R, flags, sv.proj));
+    }
+    const size_t need = pad256((size_t)R * D) + pad256((size_t)R);
+    if ((!z || !logdet) && (!workspace || workspace_bytes < need)) return PF_ERR_WORKSPACE;
+    float* zb = z ? z : reinterpret_cast<float*>(workspace);
+    float* lb = logdet ? logdet : reinterpret_cast<float*>((char*)workspace + pad256((size_t)R * D));
+    PF_TRY(pf_dn_forward_save(f, st, x, sv.proj, R, zb, lb, sv.img, sv.xt, sv.P, sv.XS));
+    if (nll) {
+      nll_kernel<<<(unsigned)((R + 255) / 256), 256, 0, st>>>(zb, lb, log_sigma, D, (int)R, nll);
+      PF_LAUNCH_CHECK(f);
+    }
+    return train_tc_check(f, st, "pf_flow_forward (fused)");
   }
   const bool is_proj = flags & PF_FLAG_CTX_IS_PROJ;
   const bool dense = !row2ctx && n_per_ctx == 1;
@@ -754,6 +789,39 @@ struct EpiWgradCtx {  // rows = [3][H] sections of the three context Linear laye
     if (d) atomicAdd(d + (int64_t)perm[n1 % H] * C + n2, acc);
   }
 };
+// all layers at once: row n1 of gproj^T . ctx belongs to layer n1 / 3H, context Linear (n1 / H) % 3
+struct EpiWgradCtxAll {
+  float* dst[TT_MAX_L * 3]; int C; int H; const int* perm;
+  __device__ __forceinline__ void operator()(int n1, int n2, float acc) const {
+    float* d = dst[n1 / H];
+    if (d) atomicAdd(d + (int64_t)perm[n1 % H] * C + n2, acc);
+  }
+};
+struct ColMapAll {
+  const int* perm; int H;
+  float* dst[TT_MAX_L * 3];
+  __device__ __forceinline__ float* operator()(int c) const {
+    float* d = dst[c / H];
+    return d ? d + perm[c % H] : nullptr;
+  }
+};
+__global__ void colsum_all_kernel(const float* __restrict__ src, int ld, int R, int ncols, int rows_per_slab, ColMapAll map) {
+  __shared__ float red[8][33];
+  int c = blockIdx.x * 32 + threadIdx.x;
+  int rbeg = blockIdx.y * rows_per_slab, rend = min(R, rbeg + rows_per_slab);
+  float s = 0.f;
+  if (c < ncols)
+    for (int r = rbeg + threadIdx.y; r < rend; r += 8) s += src[(int64_t)r * ld + c];
+  red[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < ncols) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += red[i][threadIdx.x];
+    float* d = map(c);
+    if (d) atomicAdd(d, t);
+  }
+}
 struct LoadRev {  // X[m, D-1-n]
   const float* p; int D;
   __device__ __forceinline__ float operator()(int m, int n) const { return p[(int64_t)m * D + (D - 1 - n)]; }
@@ -818,6 +886,44 @@ extern "C" pf_status pf_flow_backward(pf_flow* f, const void* saved, const float
   if (R64 == 0) return PF_OK;
   const int R = (int)R64, D = f->D, H = f->H, L = f->L, PLD = f->PLD, P = f->P, C = f->C, MULT = f->MULT;
   const int64_t ldproj = (int64_t)L * 3 * H;
+  if (fused_train(f, row2ctx, n_per_ctx)) {
+    // ---- fused training backward (pf_tc_train.cu): data-gradient chain kernel, weight-gradient kernel, and the context
+    // path as three calls over ALL layers at once (the gate / context gradients of every layer sit side by side in gproj)
+    TtSaved sv(f, const_cast<void*>(saved), R);
+    TtWork ws(f, workspace, R);
+    if (!workspace || ws.bytes > workspace_bytes) return PF_ERR_WORKSPACE;
+    PF_TRY(pf_tt_backward(f, st, sv, ws, R, gz, glogdet, gx, grads));
+    PF_TRY(pf_tt_wgrad(f, st, sv, ws, R, grads));
+    CtxMap cmd{nullptr, 1, 0};
+    const int NL = L * 3 * H;
+    if (gctx)      // d ctx [R, C] = gproj [R, L*3H] . Wctx [L*3H, C]   (WctxT is [C][L*3H]: the "N x K" operand)
+      PF_TRY((gemm_nt<EpiCtxAtomic, A_PLAIN, 64>(f, st, ws.gproj, NL, f->WctxT, NL, R, C, NL, EpiCtxAtomic{gctx, C, cmd})));
+    if (grads) {
+      EpiWgradCtxAll ew;
+      ColMapAll cmap;
+      memset(&ew, 0, sizeof(ew));
+      memset(&cmap, 0, sizeof(cmap));
+      ew.C = C; ew.H = H; ew.perm = f->d_perm;
+      cmap.H = H; cmap.perm = f->d_perm;
+      bool any_w = false, any_b = false;
+      for (int l = 0; l < L; ++l) {
+        ew.dst[l * 3] = grads[l].ctx_w; ew.dst[l * 3 + 1] = grads[l].blk_ctx_w[0]; ew.dst[l * 3 + 2] = grads[l].blk_ctx_w[1];
+        cmap.dst[l * 3] = grads[l].ctx_b; cmap.dst[l * 3 + 1] = grads[l].blk_ctx_b[0]; cmap.dst[l * 3 + 2] = grads[l].blk_ctx_b[1];
+        for (int k = 0; k < 3; ++k) { any_w = any_w || ew.dst[l * 3 + k]; any_b = any_b || cmap.dst[l * 3 + k]; }
+      }
+      if (any_w)
+        PF_TRY((gemm_tn(f, st, LoadPlain{ws.gproj, NL}, LoadCtx{ctx, C, cmd}, R, NL, C, ew)));
+      if (any_b) {
+        int slabs = cdiv(R, 64);
+        if (slabs > 2 * f->sm_count) slabs = 2 * f->sm_count;
+        const int rps = cdiv(R, slabs);
+        dim3 grid(cdiv(NL, 32), cdiv(R, rps)), block(32, 8);
+        colsum_all_kernel<<<grid, block, 0, st>>>(ws.gproj, NL, R, NL, rps, cmap);
+        PF_LAUNCH_CHECK(f);
+      }
+    }
+    return train_tc_check(f, st, "pf_flow_backward (fused)");
+  }
   SavedLayout sv(f, const_cast<void*>(saved), R, E);
   BwdWs ws(f, workspace, workspace_bytes, R);
   if (!ws.ok) return PF_ERR_WORKSPACE;
@@ -940,7 +1046,14 @@ extern "C" size_t pf_flow_workspace_bytes(const pf_flow* f, int32_t op, int64_t 
     case PF_OP_SAMPLE:
       if (f->desc.tier == PF_TIER_BF16) return pf_tc_workspace_bytes(f, R, E);
       return InvWs(f, nullptr, 0, chunk, prow).bytes + 256;
-    case PF_OP_BACKWARD: return BwdWs(f, nullptr, 0, R).bytes + 256;
+    case PF_OP_BACKWARD: {
+      size_t b = BwdWs(f, nullptr, 0, R).bytes + 256;
+      if (f->train_fused && f->train && f->dense) {
+        const size_t t = TtWork(f, nullptr, R).bytes + 256;
+        if (t > b) b = t;
+      }
+      return b;
+    }
   }
   return 0;
 }

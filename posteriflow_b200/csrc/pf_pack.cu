@@ -100,6 +100,8 @@ extern "C" pf_status pf_flow_create(const pf_flow_desc* d, pf_flow** out) {
     f->train_streams = !(ts && ts[0] == '0');
     const char* pd = getenv("PF_TRAIN_PDL");
     f->train_pdl = !(pd && pd[0] == '0');
+    const char* fu = getenv("PF_TRAIN_FUSED");
+    f->train_fused = !(fu && fu[0] == '0');
   }
 
   // degree-sorted hidden permutation (stable): slot s <- nflows unit perm[s]

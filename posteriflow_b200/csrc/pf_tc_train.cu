@@ -1,5 +1,797 @@
-// Fused training step of the tensor-core tier, backward side (placeholder until the kernels land).
-#include "pf_common.cuh"
+// Fused training step of the tensor-core tiers, backward side (A12 of SURVEY.md 8a: what loss.backward() does through
+// nflows at experiments/train_lean_npe.py:365, for the flow head):
+//
+//   tt_backward_kernel   ONE persistent kernel for the whole data-gradient chain.  A CTA keeps a 128-row tile on chip from
+//                        the last layer to the first: per layer the spline VJP (fp32, in the epilogue) and seven tcgen05
+//                        MMA stages  d h2 = d p . Wf  (two groups) -> d relu(u2) = (g2 d h2) . Wb2 -> d h1 += [h1>0] (. Wa2)
+//                        -> block 1 likewise -> d x = d h0 . W0,  every product as hi*hi + lo*hi + hi*lo of bf16 pairs
+//                        (gradients span many decades: bf16 keeps fp32's exponent range), fp32 accumulation and the fp32
+//                        residual gradient in tensor memory.  Relu masks, gates and pre-gate values come from the images
+//                        the forward saved; the gradient operand tiles it builds in shared memory are written out once
+//                        (bulk copy shared -> global) as the images the weight-gradient kernel contracts.
+//   tt_wgrad_kernel      one CTA per (layer, weight matrix, 128-row block of the matrix): D[out, in] = sum over ALL flow rows
+//                        of G[row, out] A[row, in] -- both operands are the saved row-major tile images, fed to tcgen05.mma
+//                        as MN-major operands (the contraction index is the tile row), double-buffered bulk loads; bias
+//                        gradients are the column sums of the same G tiles.  Plain read-modify-write stores into nflows'
+//                        own weight layout: every output entry has exactly one owner CTA (no atomics).
+#include <stdlib.h>
 
-pf_status pf_tt_pack(pf_flow* f, cudaStream_t st) { (void)f; (void)st; return PF_OK; }
-void pf_tt_destroy(pf_flow* f) { (void)f; }
+#include "pf_common.cuh"
+#include "pf_sm100.cuh"
+#include "pf_spline.cuh"
+#include "pf_train.cuh"
+
+namespace pf {
+using namespace pf::sm100;
+
+constexpr int TT_THREADS = 320;
+constexpr int TT_NSLOT = 3;
+constexpr int TT_SLOT = 16384;
+constexpr int TT_H = 256;
+constexpr int TT_NB = 16;
+constexpr int TT_MULT = 3 * TT_NB - 1;
+
+struct TtShape {
+  int D, L, PLD, DP;
+  int ga, gb;        // dims 1..ga in parameter group A, ga+1..ga+gb in group B (dim 0 has no hidden input: bias only)
+  int NA, NBn;       // padded parameter counts of the groups (multiples of 16, <= 256)
+  uint32_t layer_bytes;
+};
+
+struct TtState {
+  TtShape s;
+  uint8_t* wimg;     // [L][layer_bytes] backward weight image
+};
+
+// ------------------------------------------------------------------------------------------------
+// backward weight image: 16 KB slots, each the bf16 (hi | lo) pair of one K = 16 chunk of a TRANSPOSED matrix in the
+// UMMA K-major no-swizzle layout, in the order the backward consumes them:
+//   FA^T  NA/16 slots   B[n = hidden unit][k = parameter of dims 1..ga]
+//   FB^T  NBn/16 slots
+//   Wb2^T, Wa2^T, Wb1^T, Wa1^T   16 slots each   B[n = input unit][k = output unit]
+//   W0^T  1 slot = 16 chunks of ([16 x 16] hi 512 B | lo 512 B)   B[n = x column][k = hidden unit]
+// ------------------------------------------------------------------------------------------------
+__global__ void tt_pack_kernel(TtShape s, uint8_t* __restrict__ image, const float* __restrict__ WfT,
+                               const float* __restrict__ WaT, const float* __restrict__ WbT, const float* __restrict__ W0T) {
+  const int l = blockIdx.y, slot = blockIdx.x;
+  const int nA = s.NA / 16, nB = s.NBn / 16;
+  __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(image + (size_t)l * s.layer_bytes + (size_t)slot * TT_SLOT);
+  const int H = TT_H;
+  if (slot < nA + nB + 64) {
+    int kind, c;   // 0 FA, 1 FB, 2.. hidden
+    if (slot < nA) { kind = 0; c = slot; }
+    else if (slot < nA + nB) { kind = 1; c = slot - nA; }
+    else { kind = 2 + (slot - nA - nB) / 16; c = (slot - nA - nB) % 16; }
+    for (int e = threadIdx.x; e < 256 * 16; e += blockDim.x) {
+      const int n = e / 16, kk = e % 16, k = c * 16 + kk;
+      float v = 0.f;
+      if (kind <= 1) {
+        const int first = kind == 0 ? 1 : 1 + s.ga, cnt = kind == 0 ? s.ga : s.gb;
+        if (k < cnt * TT_MULT) v = WfT[((size_t)l * H + n) * s.PLD + (size_t)first * TT_MULT + k];
+      } else {
+        const int hs = kind - 2;                    // 0 Wb2, 1 Wa2, 2 Wb1, 3 Wa1
+        const int blk = hs < 2 ? 1 : 0;
+        const float* W = (hs & 1) ? WaT : WbT;
+        v = W[(((size_t)l * 2 + blk) * H + n) * H + k];
+      }
+      const int o = (kk / 8) * (256 * 8) + (n / 8) * 64 + (n % 8) * 8 + (kk % 8);
+      const __nv_bfloat16 hi = __float2bfloat16(v);
+      dst[o] = hi;
+      dst[256 * 16 + o] = __float2bfloat16(v - __bfloat162float(hi));
+    }
+  } else {
+    for (int e = threadIdx.x; e < 16 * 16 * 16; e += blockDim.x) {
+      const int c = e / 256, n = (e / 16) % 16, kk = e % 16;
+      const float v = n < s.D ? W0T[((size_t)l * s.DP + n) * H + c * 16 + kk] : 0.f;
+      const int o = c * 512 + (kk / 8) * (16 * 8) + (n / 8) * 64 + (n % 8) * 8 + (kk % 8);
+      const __nv_bfloat16 hi = __float2bfloat16(v);
+      dst[o] = hi;
+      dst[o + 256] = __float2bfloat16(v - __bfloat162float(hi));
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// the backward chain kernel
+// ------------------------------------------------------------------------------------------------
+struct TtArgs {
+  TtShape s;
+  const uint8_t* wimg;
+  const float* proj; int64_t ldproj;    // [R][L*3*H]
+  const float* P; const float* XS;      // saved by the forward
+  const uint8_t* img;                   // [L][TT_NA][tiles][TT_IMG]
+  const float* gz; const float* gl;     // upstream gradients [R, D], [R] (either may be NULL = 0)
+  uint8_t* gimg;                        // [L][TT_NG][tiles][TT_IMG]
+  float* gproj;                         // [R][L*3*H]
+  float* gx;                            // [R, D] or NULL
+  float* dbf[TT_MAX_L];                 // final_layer.bias gradient of each layer (dim 0's 47 entries) or NULL
+  int64_t R; int n_tiles; float tail; int* err;
+};
+
+constexpr int TT_OFF_ACT = 0;
+constexpr int TT_OFF_ACTLO = 65536;
+constexpr int TT_OFF_RING = 131072;
+constexpr int TT_OFF_GY = TT_OFF_RING + TT_NSLOT * TT_SLOT;     // [128][12] d loss / d layer output
+constexpr int TT_OFF_GXD = TT_OFF_GY + TT_ROWS * 12 * 4;        // [128][12] direct d/dx of the spline
+constexpr int TT_OFF_BAR = TT_OFF_GXD + TT_ROWS * 12 * 4;
+constexpr int TT_SMEM = TT_OFF_BAR + 256;
+
+__device__ __forceinline__ void bulk_s2g(void* gdst, const void* ssrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+__device__ __forceinline__ void split_bf16(float a, float b, uint32_t& hi, uint32_t& lo) {
+  hi = pack_bf16(a, b);
+  lo = pack_bf16(a - __uint_as_float(hi << 16), b - __uint_as_float(hi & 0xffff0000u));
+}
+__device__ __forceinline__ uint4 ldg128(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+
+struct TtRegQ {
+  const float* q;
+  __device__ __forceinline__ float operator()(int i) const { return q[i]; }
+};
+struct TtGradOut {
+  float* g;
+  __device__ __forceinline__ void operator()(int i, float v) const { g[i] = v; }
+};
+
+__global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const TtShape& s = a.s;
+  const int D = s.D;
+  uint8_t* sACT = smem + TT_OFF_ACT;
+  uint8_t* sACTLO = smem + TT_OFF_ACTLO;
+  uint8_t* ring = smem + TT_OFF_RING;
+  float* gy_s = reinterpret_cast<float*>(smem + TT_OFF_GY);
+  float* gxd_s = reinterpret_cast<float*>(smem + TT_OFF_GXD);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TT_OFF_BAR);
+  uint64_t* full = bars;                     // [NSLOT]
+  uint64_t* empty = bars + TT_NSLOT;         // [NSLOT]
+  uint64_t* acc_bar = bars + 2 * TT_NSLOT;   // MMAs of the current stage complete
+  uint64_t* op_bar = acc_bar + 1;            // operand tile of the next stage written (8 warp arrivals)
+  volatile int* abort_s = reinterpret_cast<volatile int*>(acc_bar + 2);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 3);
+
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  if (tid == 0) {
+    for (int i = 0; i < TT_NSLOT; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(acc_bar, 1);
+    mbar_init(op_bar, 8);
+    *abort_s = 0;
+    fence_mbar_init();
+  }
+  if (warp == 8) tmem_alloc(tmem_slot, 512);
+  for (int i = tid; i < 131072 / 16; i += TT_THREADS) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  auto wait = [&](uint64_t* bar, uint32_t parity, int code) -> bool {
+    for (uint32_t i = 0; i < (1u << 22); ++i) {
+      if (mbar_try_wait(bar, parity)) return true;
+      if ((i & 255) == 255 && *abort_s) return false;
+    }
+    *abort_s = 1;
+    raise_flag(a.err, code);
+    return false;
+  };
+
+  if (warp < 8) {
+    // ============================ row warps: two threads per flow row ============================
+    const int half = warp >> 2, q4 = warp & 3;
+    const int r = q4 * 32 + lane;
+    const int rt = half * 128 + r;
+    const uint32_t tl = tmem + ((uint32_t)(q4 * 32) << 16);
+    const uint32_t rowoff = (uint32_t)(r / 8) * 128 + (uint32_t)(r % 8) * 16;
+    const int ch = half * 128;
+    uint32_t acc_par = 0;
+    bool ok = true;
+    // operand tile complete: make it visible to the async proxy, start the bulk copy of its hi half to `gdst` (the
+    // gradient image the weight-gradient kernel reads), hand it to the MMA warp
+    auto publish = [&](uint8_t* gdst) {
+      fence_proxy_async_smem();
+      bar_sync(3, 256);
+      if (rt == 0) {
+        bulk_s2g(gdst, sACT, TT_IMG);
+        bulk_commit();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(op_bar);
+    };
+    // before the operand tile is overwritten: the MMAs reading it are complete (the caller waited on acc_bar) and the
+    // bulk copy has finished reading shared memory
+    auto reopen = [&]() {
+      if (rt == 0) bulk_wait_read0();
+      bar_sync(3, 256);
+    };
+    for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
+      const int64_t grow = (int64_t)tile * TT_ROWS + r;
+      const bool valid = grow < a.R;
+      const int64_t growc = valid ? grow : a.R - 1;               // clamped row for loads of per-row constants
+      const float glr = (valid && a.gl) ? a.gl[grow] : 0.f;
+      if (half == 0)
+        for (int j = 0; j < D; ++j) gy_s[r * 12 + j] = (valid && a.gz) ? a.gz[grow * D + j] : 0.f;
+      bar_sync(3, 256);
+      for (int l = s.L - 1; l >= 0 && ok; --l) {
+        const float* projr = a.proj + growc * a.ldproj + (size_t)l * 3 * TT_H;
+        float* gprojr = a.gproj + growc * a.ldproj + (size_t)l * 3 * TT_H;
+        // ---------------- E0: spline VJP -> d params (two operand tiles: dims 1..ga, then ga+1..) ----------------
+#pragma unroll 1
+        for (int ps = 0; ps < 2 && ok; ++ps) {
+          const int gfirst = ps == 0 ? 1 : 1 + s.ga, gcnt = ps == 0 ? s.ga : s.gb;
+          const int h0n = (gcnt + 1) / 2;
+          const int jbeg = gfirst + (half ? h0n : 0);
+          const int jcnt = (half ? gcnt - h0n : h0n) + ((ps == 0 && half == 1) ? 1 : 0);   // + dim 0 (bias only)
+          bool opened = false;
+#pragma unroll 1
+          for (int jj = 0; jj < jcnt; ++jj) {
+            const bool is0 = (ps == 0 && half == 1 && jj == jcnt - 1);
+            const int j = is0 ? 0 : jbeg + jj;
+            float q[TT_MULT], gp[TT_MULT];
+            const float* pr = a.P + ((size_t)l * a.R + growc) * s.PLD + j * TT_MULT;
+#pragma unroll
+            for (int i = 0; i < TT_MULT; ++i) q[i] = __ldg(pr + i);
+            const float xin = a.XS[((size_t)l * a.R + growc) * D + (D - 1 - j)];
+            const float gyj = gy_s[r * 12 + j];
+            const float gxd = rqs_forward_backward<TT_NB>(TtRegQ{q}, xin, a.tail, gyj, glr, TtGradOut{gp});
+            gxd_s[r * 12 + j] = valid ? gxd : 0.f;
+            if (is0) {
+              // dim 0's parameters are bias only: their gradient goes straight to final_layer.bias[0:47]
+              float* dst = a.dbf[l];
+              float keep0 = 0.f, keep1 = 0.f;
+#pragma unroll
+              for (int i = 0; i < TT_MULT; ++i) {
+                float v = valid ? gp[i] : 0.f;
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane == (i & 31)) { if (i < 32) keep0 = v; else keep1 = v; }
+              }
+              if (dst) {
+                atomicAdd(dst + lane, keep0);
+                if (lane + 32 < TT_MULT) atomicAdd(dst + lane + 32, keep1);
+              }
+              continue;
+            }
+            if (!opened) {
+              if (ps == 1) {   // the MMAs of group A must be done with the operand tile
+                if (!(ok = wait(acc_bar, acc_par, 50))) break;
+                acc_par ^= 1;
+              }
+              reopen();
+              opened = true;
+            }
+            const int cbase = (j - gfirst) * TT_MULT;
+#pragma unroll
+            for (int i = 0; i < TT_MULT; ++i) {
+              const int c = cbase + i;
+              const float v = valid ? gp[i] : 0.f;
+              const __nv_bfloat16 hi = __float2bfloat16(v);
+              const uint32_t o = (uint32_t)(c / 8) * 2048 + rowoff + (uint32_t)(c % 8) * 2;
+              *reinterpret_cast<__nv_bfloat16*>(sACT + o) = hi;
+              *reinterpret_cast<__nv_bfloat16*>(sACTLO + o) = __float2bfloat16(v - __bfloat162float(hi));
+            }
+          }
+          if (!ok) break;
+          if (!opened) {     // a half without a parameter dim in this group (tiny D): still take part in the protocol
+            if (ps == 1) {
+              if (!(ok = wait(acc_bar, acc_par, 51))) break;
+              acc_par ^= 1;
+            }
+            reopen();
+          }
+          publish(a.gimg + tt_img_off(l, ps == 0 ? TT_G_PA : TT_G_PB, TT_NG, tile, a.n_tiles));
+        }
+        if (!ok) break;
+        // ---------------- E2 .. E6: the five hidden data-gradient epilogues ----------------
+        // k = 0: d h2 complete -> g2 d h2 (operand), gate-2 gradient, residual := d h2
+        // k = 1: [u2 > 0] acc  (operand)
+        // k = 2: d h1 = residual + [h1 > 0] acc -> g1 d h1 (operand), gate-1 gradient, residual := d h1
+        // k = 3: [u1 > 0] acc  (operand)
+        // k = 4: d h0 = residual + [h0 > 0] acc (operand), relu(context) gradient
+#pragma unroll 1
+        for (int k = 0; k < 5 && ok; ++k) {
+          if (!(ok = wait(acc_bar, acc_par, 52 + k))) break;
+          acc_par ^= 1;
+          tc_fence_after();
+          reopen();
+          const bool res_in = (k == 2 || k == 4), gate = (k == 0 || k == 2), has_mask = k >= 1;
+          const int mimg = k == 1 ? TT_A_U2 : (k == 2 ? TT_A_H1 : (k == 3 ? TT_A_U1 : TT_A_H0));
+          const uint8_t* mbase = a.img + tt_img_off(l, mimg, TT_NA, tile, a.n_tiles);
+          const int vimg = k == 0 ? TT_A_V2 : TT_A_V1;
+          const uint8_t* vbase = a.img + tt_img_off(l, vimg, TT_NA, tile, a.n_tiles);
+          const uint8_t* vlbase = a.img + tt_img_off(l, vimg + 1, TT_NA, tile, a.n_tiles);
+          const int sec = k == 0 ? 2 : (k == 2 ? 1 : 0);
+#pragma unroll 1
+          for (int b = 0; b < 4; ++b) {
+            const int c0 = ch + 32 * b;
+            uint32_t v[32], hr[32];
+            tmem_ld32(tl + c0, v);
+            if (res_in) tmem_ld32(tl + 256 + c0, hr);
+            uint32_t mkw[16], vhw[16], vlw[16];      // 32 bf16 each: relu mask source, pre-gate value hi / lo
+            float g[32];
+            if (has_mask) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const uint4 t4 = ldg128(mbase + (size_t)(c0 / 8 + i) * 2048 + rowoff);
+                mkw[4 * i] = t4.x; mkw[4 * i + 1] = t4.y; mkw[4 * i + 2] = t4.z; mkw[4 * i + 3] = t4.w;
+              }
+            }
+            if (gate) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const uint4 h4 = ldg128(vbase + (size_t)(c0 / 8 + i) * 2048 + rowoff);
+                const uint4 l4 = ldg128(vlbase + (size_t)(c0 / 8 + i) * 2048 + rowoff);
+                vhw[4 * i] = h4.x; vhw[4 * i + 1] = h4.y; vhw[4 * i + 2] = h4.z; vhw[4 * i + 3] = h4.w;
+                vlw[4 * i] = l4.x; vlw[4 * i + 1] = l4.y; vlw[4 * i + 2] = l4.z; vlw[4 * i + 3] = l4.w;
+              }
+            }
+            if (gate || k == 4) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 4) {
+                const float4 t4 = __ldg(reinterpret_cast<const float4*>(projr + sec * TT_H + c0 + i));
+                g[i] = t4.x; g[i + 1] = t4.y; g[i + 2] = t4.z; g[i + 3] = t4.w;
+              }
+            }
+            tmem_wait_ld();
+            float o[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              float x = __uint_as_float(v[i]);
+              if (has_mask) {
+                const uint32_t w = mkw[i / 2];
+                const uint32_t hbits = (i & 1) ? (w >> 16) : (w & 0xffffu);
+                if ((hbits & 0x7fffu) == 0u) x = 0.f;
+              }
+              if (res_in) x += __uint_as_float(hr[i]);
+              o[i] = x;
+            }
+            if (k == 0 || k == 2) {          // residual gradient stays in tensor memory
+              uint32_t ow[32];
+#pragma unroll
+              for (int i = 0; i < 32; ++i) ow[i] = __float_as_uint(o[i]);
+              tmem_st16(tl + 256 + c0, ow);
+              tmem_st16(tl + 256 + c0 + 16, ow + 16);
+            }
+            if (gate) {                      // d gate (pre-sigmoid) = d h * v * g (1 - g); operand = g * d h
+              float gp4[32];
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                const uint32_t wh = vhw[i / 2], wl = vlw[i / 2];
+                const float vv = (i & 1) ? __uint_as_float(wh & 0xffff0000u) + __uint_as_float(wl & 0xffff0000u)
+                                         : __uint_as_float(wh << 16) + __uint_as_float(wl << 16);
+                gp4[i] = o[i] * vv * g[i] * (1.f - g[i]);
+                o[i] *= g[i];
+              }
+              if (valid) {
+#pragma unroll
+                for (int i = 0; i < 32; i += 4)
+                  *reinterpret_cast<float4*>(gprojr + sec * TT_H + c0 + i) = make_float4(gp4[i], gp4[i + 1], gp4[i + 2], gp4[i + 3]);
+              }
+            } else if (k == 4) {             // relu(context_layer) backward: g[] holds the relu'd context term
+              if (valid) {
+#pragma unroll
+                for (int i = 0; i < 32; i += 4)
+                  *reinterpret_cast<float4*>(gprojr + c0 + i) =
+                      make_float4(g[i] > 0.f ? o[i] : 0.f, g[i + 1] > 0.f ? o[i + 1] : 0.f, g[i + 2] > 0.f ? o[i + 2] : 0.f,
+                                  g[i + 3] > 0.f ? o[i + 3] : 0.f);
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              uint4 w4, l4;
+              split_bf16(o[8 * i], o[8 * i + 1], w4.x, l4.x); split_bf16(o[8 * i + 2], o[8 * i + 3], w4.y, l4.y);
+              split_bf16(o[8 * i + 4], o[8 * i + 5], w4.z, l4.z); split_bf16(o[8 * i + 6], o[8 * i + 7], w4.w, l4.w);
+              const size_t io = (size_t)(c0 / 8 + i) * 2048 + rowoff;
+              *reinterpret_cast<uint4*>(sACT + io) = w4;
+              *reinterpret_cast<uint4*>(sACTLO + io) = l4;
+            }
+          }
+          if (k == 0 || k == 2) tmem_wait_st();
+          publish(a.gimg + tt_img_off(l, TT_G_V2 + k, TT_NG, tile, a.n_tiles));
+        }
+        if (!ok) break;
+        // ---------------- E7: d x of this layer -> d output of the layer below ----------------
+        if (!(ok = wait(acc_bar, acc_par, 58))) break;
+        acc_par ^= 1;
+        tc_fence_after();
+        if (half == 0) {
+          uint32_t v[16];
+          tmem_ld16(tl, v);
+          tmem_wait_ld();
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
+            if (k < D) {
+              const float gxin = __uint_as_float(v[k]) + gxd_s[r * 12 + k];
+              gy_s[r * 12 + (D - 1 - k)] = gxin;          // undo the layer's ReversePermutation
+              if (l == 0 && a.gx && valid) a.gx[grow * D + (D - 1 - k)] = gxin;
+            }
+          }
+        }
+        tc_fence_before();
+        bar_sync(3, 256);
+      }
+    }
+    if (rt == 0) bulk_wait0();      // the last gradient image is in global memory before the CTA exits
+  } else if (warp == 8) {
+    // ============================ MMA issuer ============================
+    uint32_t op_par = 0, slot = 0, full_par = 0;
+    const uint32_t idesc256 = umma_idesc_bf16(TT_ROWS, 256), idesc16 = umma_idesc_bf16(TT_ROWS, 16);
+    const uint32_t aACT = smem_u32(sACT), aACTLO = smem_u32(sACTLO), aRing = smem_u32(ring);
+    bool ok = true;
+    for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
+      for (int l = s.L - 1; l >= 0 && ok; --l) {
+        for (int m = 0; m < 7 && ok; ++m) {          // FA^T, FB^T, Wb2^T, Wa2^T, Wb1^T, Wa1^T, W0^T
+          const int nk = m == 0 ? s.NA / 16 : (m == 1 ? s.NBn / 16 : 16);
+          if (!(ok = wait(&full[slot], full_par, 30))) break;
+          if (!(ok = wait(op_bar, op_par, 20 + m))) break;
+          op_par ^= 1;
+          tc_fence_after();
+          if (m < 6) {
+            for (int c = 0; c < nk && ok; ++c) {
+              if (!(ok = wait(&full[slot], full_par, 31))) break;
+              tc_fence_after();
+              const uint32_t bbase = aRing + slot * TT_SLOT;
+              if (elect_one_sync()) {
+                const uint64_t bh = umma_smem_desc(bbase, 256 * 16, 128);
+                const uint64_t bl = umma_smem_desc(bbase + 8192u, 256 * 16, 128);
+                const uint64_t ah = umma_smem_desc(aACT + (uint32_t)c * 4096u, 2048, 128);
+                const uint64_t al = umma_smem_desc(aACTLO + (uint32_t)c * 4096u, 2048, 128);
+                umma_ss(tmem, ah, bh, idesc256, (m == 1 || c > 0) ? 1u : 0u);
+                umma_ss(tmem, al, bh, idesc256, 1u);
+                umma_ss(tmem, ah, bl, idesc256, 1u);
+                umma_commit(&empty[slot]);
+                if (c + 1 >= nk) umma_commit(acc_bar);
+              }
+              __syncwarp();
+              if (++slot == TT_NSLOT) { slot = 0; full_par ^= 1; }
+            }
+          } else {
+            const uint32_t bbase = aRing + slot * TT_SLOT;
+            if (elect_one_sync()) {
+              for (int c = 0; c < 16; ++c) {
+                const uint64_t bh = umma_smem_desc(bbase + (uint32_t)c * 1024u, 16 * 16, 128);
+                const uint64_t bl = umma_smem_desc(bbase + (uint32_t)c * 1024u + 512u, 16 * 16, 128);
+                const uint64_t ah = umma_smem_desc(aACT + (uint32_t)c * 4096u, 2048, 128);
+                const uint64_t al = umma_smem_desc(aACTLO + (uint32_t)c * 4096u, 2048, 128);
+                umma_ss(tmem, ah, bh, idesc16, c > 0 ? 1u : 0u);
+                umma_ss(tmem, al, bh, idesc16, 1u);
+                umma_ss(tmem, ah, bl, idesc16, 1u);
+              }
+              umma_commit(&empty[slot]);
+              umma_commit(acc_bar);
+            }
+            __syncwarp();
+            if (++slot == TT_NSLOT) { slot = 0; full_par ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 9) {
+    // ============================ weight loader ============================
+    uint32_t slot = 0, empty_par = 1;
+    bool ok = true;
+    const int nslots = s.NA / 16 + s.NBn / 16 + 65;
+    for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
+      for (int l = s.L - 1; l >= 0 && ok; --l) {
+        const uint8_t* src = a.wimg + (size_t)l * s.layer_bytes;
+        for (int i = 0; i < nslots; ++i) {
+          if (!(ok = wait(&empty[slot], empty_par, 40))) break;
+          if (elect_one_sync()) {
+            mbar_arrive_expect_tx(&full[slot], TT_SLOT);
+            bulk_g2s(ring + (size_t)slot * TT_SLOT, src, TT_SLOT, &full[slot]);
+          }
+          __syncwarp();
+          src += TT_SLOT;
+          if (++slot == TT_NSLOT) { slot = 0; empty_par ^= 1; }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------------------------------------
+// the weight-gradient kernel
+// ------------------------------------------------------------------------------------------------
+struct TtWgArgs {
+  TtShape s;
+  const uint8_t* img;      // forward images
+  const uint8_t* xt;       // x-tile images
+  const uint8_t* gimg;     // gradient images
+  int tiles;
+  int64_t R;
+  const int* perm;         // [H] sorted slot -> nflows unit
+  int mn_swap;             // descriptor convention switch (PF_MN_SWAP; bring-up aid)
+  int* err;
+  pf_layer_grads g[TT_MAX_L];
+};
+
+constexpr int WG_THREADS = 192;       // 4 epilogue / column-sum warps, MMA issuer, loader
+constexpr int WG_STAGES = 2;
+constexpr int WG_GBYTES = 32768;      // [128 rows x 128 columns] of a gradient image
+constexpr int WG_ABYTES = 65536;      // [128 rows x 256 columns] activation image
+constexpr int WG_STAGE = WG_GBYTES + WG_ABYTES;
+constexpr int WG_OFF_BAR = WG_STAGES * WG_STAGE;
+constexpr int WG_SMEM = WG_OFF_BAR + 128;
+constexpr int WG_JOBS = 14;           // per layer
+
+// instruction descriptor, kind::f16: bf16 x bf16 -> fp32, BOTH operands MN-major (bits 15 / 16), dense
+__host__ __device__ constexpr uint32_t umma_idesc_bf16_mn(int M, int N) {
+  return umma_idesc_bf16(M, N) | (1u << 15) | (1u << 16);
+}
+
+__global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const TtShape& s = a.s;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + WG_OFF_BAR);
+  uint64_t* full = bars;                    // [STAGES] tile images landed
+  uint64_t* empty = bars + WG_STAGES;       // [STAGES] MMAs + column sums done with the stage (1 commit + 4 warps)
+  uint64_t* acc_bar = bars + 2 * WG_STAGES;
+  volatile int* abort_s = reinterpret_cast<volatile int*>(acc_bar + 1);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 2);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  // ---- decode the job ----
+  const int l = blockIdx.x / WG_JOBS, jk = blockIdx.x % WG_JOBS;
+  const int mat = jk < 4 ? 0 : 1 + (jk - 4) / 2;       // 0 final | 1 Wb2 | 2 Wa2 | 3 Wb1 | 4 Wa1 | 5 W0
+  const int mt = jk < 4 ? (jk & 1) : ((jk - 4) & 1);   // 128-column block of the gradient image
+  const int gwhich = jk < 2 ? TT_G_PA : (jk < 4 ? TT_G_PB : TT_G_V2 + (mat - 1));
+  const int awhich = mat == 0 ? TT_A_H2 : (mat == 1 ? TT_A_U2 : (mat == 2 ? TT_A_H1 : (mat == 3 ? TT_A_U1 : TT_A_H0)));
+  const int N = mat == 5 ? 16 : 256;
+  const uint32_t abytes = mat == 5 ? TT_XT : WG_ABYTES;
+  const uint8_t* gsrc = a.gimg + tt_img_off(l, gwhich, TT_NG, 0, a.tiles) + (size_t)mt * WG_GBYTES;
+  const uint8_t* asrc = mat == 5 ? a.xt + (size_t)l * a.tiles * TT_XT : a.img + tt_img_off(l, awhich, TT_NA, 0, a.tiles);
+  const size_t astride = mat == 5 ? TT_XT : TT_IMG;
+
+  if (tid == 0) {
+    for (int i = 0; i < WG_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 5); }
+    mbar_init(acc_bar, 1);
+    *abort_s = 0;
+    fence_mbar_init();
+  }
+  if (warp == 4) tmem_alloc(tmem_slot, 256);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  auto wait = [&](uint64_t* bar, uint32_t parity, int code) -> bool {
+    for (uint32_t i = 0; i < (1u << 22); ++i) {
+      if (mbar_try_wait(bar, parity)) return true;
+      if ((i & 255) == 255 && *abort_s) return false;
+    }
+    *abort_s = 1;
+    raise_flag(a.err, code);
+    return false;
+  };
+
+  if (warp < 4) {
+    // ---- column sums of the gradient tiles (bias gradients), then the epilogue ----
+    const int m = warp * 32 + lane;                 // column of this CTA's 128-column block = row of the weight block
+    float bsum = 0.f;
+    uint32_t st = 0, par = 0;
+    bool ok = true;
+    for (int t = 0; t < a.tiles && ok; ++t) {
+      if (!(ok = wait(&full[st], par, 70))) break;
+      const uint8_t* gb = smem + st * WG_STAGE + (size_t)(m / 8) * 2048 + (m % 8) * 2;
+      float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll 4
+      for (int rg = 0; rg < 16; ++rg) {
+#pragma unroll
+        for (int rr = 0; rr < 8; rr += 2) {
+          acc0 += __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(gb + rg * 128 + rr * 16));
+          acc1 += __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(gb + rg * 128 + rr * 16 + 16));
+        }
+      }
+      bsum += acc0 + acc1;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[st]);
+      if (++st == WG_STAGES) { st = 0; par ^= 1; }
+    }
+    if (ok) ok = wait(acc_bar, 0, 71);
+    tc_fence_after();
+    if (ok) {
+      const pf_layer_grads& g = a.g[l];
+      const int gm = mt * 128 + m;                  // column within the gradient image
+      // destination row / bias slot of this thread
+      float* wrow = nullptr;
+      float* bdst = nullptr;
+      int ld = 0;
+      int wr = -1;                                  // row index in nflows' space (mask rule)
+      if (mat == 0) {
+        const int first = jk < 2 ? 1 : 1 + s.ga, cnt = jk < 2 ? s.ga : s.gb;
+        if (gm < cnt * TT_MULT) {
+          wr = first * TT_MULT + gm;
+          if (g.final_w) wrow = g.final_w + (size_t)wr * TT_H;
+          if (g.final_b) bdst = g.final_b + wr;
+          ld = TT_H;
+        }
+      } else if (mat <= 4) {
+        const int blk = mat <= 2 ? 1 : 0, j = (mat & 1) ? 1 : 0;      // Wb = linear_layers.1, Wa = linear_layers.0
+        wr = a.perm[gm];
+        if (g.blk_lin_w[blk][j]) wrow = g.blk_lin_w[blk][j] + (size_t)wr * TT_H;
+        if (g.blk_lin_b[blk][j]) bdst = g.blk_lin_b[blk][j] + wr;
+        ld = TT_H;
+      } else {
+        wr = a.perm[gm];
+        if (g.initial_w) wrow = g.initial_w + (size_t)wr * s.D;
+        if (g.initial_b) bdst = g.initial_b + wr;
+        ld = s.D;
+      }
+      (void)ld;
+      if (bdst) *bdst += bsum;
+      const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16);
+      const int rule = mat == 0 ? RULE_FINAL : (mat == 5 ? RULE_INITIAL : RULE_HIDDEN);
+      for (int c0 = 0; c0 < N; c0 += 16) {
+        uint32_t v[16];
+        tmem_ld16(tl + c0, v);
+        tmem_wait_ld();
+        if (wrow) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int n = c0 + i;
+            if (mat == 5) {
+              if (n < s.D && rule_mask(rule, wr, n, s.D, TT_MULT) != 0.f) wrow[n] += __uint_as_float(v[i]);
+            } else {
+              const int wc = a.perm[n];
+              if (rule_mask(rule, wr, wc, s.D, TT_MULT) != 0.f) wrow[wc] += __uint_as_float(v[i]);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 4) {
+    // ---- MMA issuer ----
+    const uint32_t idesc = umma_idesc_bf16_mn(128, N);
+    const uint32_t lbo = a.mn_swap ? 2048u : 128u, sbo = a.mn_swap ? 128u : 2048u;
+    uint32_t st = 0, par = 0;
+    bool ok = true;
+    for (int t = 0; t < a.tiles && ok; ++t) {
+      if (!(ok = wait(&full[st], par, 72))) break;
+      tc_fence_after();
+      const uint32_t gb = smem_u32(smem + st * WG_STAGE), ab = gb + WG_GBYTES;
+      if (elect_one_sync()) {
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          const uint64_t ad = umma_smem_desc(gb + (uint32_t)ks * 256u, lbo, sbo);
+          const uint64_t bd = umma_smem_desc(ab + (uint32_t)ks * 256u, lbo, sbo);
+          umma_ss(tmem, ad, bd, idesc, (t > 0 || ks > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty[st]);
+        if (t + 1 == a.tiles) umma_commit(acc_bar);
+      }
+      __syncwarp();
+      if (++st == WG_STAGES) { st = 0; par ^= 1; }
+    }
+  } else {
+    // ---- loader ----
+    uint32_t st = 0, par = 1;
+    bool ok = true;
+    for (int t = 0; t < a.tiles && ok; ++t) {
+      if (!(ok = wait(&empty[st], par, 73))) break;
+      if (elect_one_sync()) {
+        mbar_arrive_expect_tx(&full[st], WG_GBYTES + abytes);
+        bulk_g2s(smem + st * WG_STAGE, gsrc + (size_t)t * TT_IMG, WG_GBYTES, &full[st]);
+        bulk_g2s(smem + st * WG_STAGE + WG_GBYTES, asrc + (size_t)t * astride, abytes, &full[st]);
+      }
+      __syncwarp();
+      if (++st == WG_STAGES) { st = 0; par ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) tmem_dealloc(tmem, 256);
+}
+
+}  // namespace pf
+using namespace pf;
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+static bool tt_plan(const pf_flow* f, TtShape& s) {
+  memset(&s, 0, sizeof(s));
+  if (f->H != TT_H || f->NB != TT_NB || f->D < 2 || f->D > 11 || f->desc.num_blocks != 2 || f->L > TT_MAX_L) return false;
+  if (f->desc.tier != PF_TIER_BF16 && f->desc.tier != PF_TIER_BF16X3) return false;
+  s.D = f->D; s.L = f->L; s.PLD = f->PLD; s.DP = f->DP;
+  s.ga = (f->D - 1 + 1) / 2;
+  s.gb = f->D - 1 - s.ga;
+  s.NA = round_up(s.ga * TT_MULT, 16);
+  s.NBn = s.gb > 0 ? round_up(s.gb * TT_MULT, 16) : 16;
+  if (s.NA > 256 || s.NBn > 256) return false;
+  s.layer_bytes = (uint32_t)(s.NA / 16 + s.NBn / 16 + 65) * TT_SLOT;
+  return true;
+}
+
+bool pf_tt_supported(const pf_flow* f) { return f->train != nullptr; }
+
+pf_status pf_tt_pack(pf_flow* f, cudaStream_t st) {
+  TtShape s;
+  if (!tt_plan(f, s)) return PF_OK;
+  TtState* t = reinterpret_cast<TtState*>(f->train);
+  if (!t) {
+    t = new TtState();
+    t->s = s;
+    t->wimg = nullptr;
+    cudaError_t e = cudaMalloc(&t->wimg, (size_t)s.L * s.layer_bytes);
+    if (e != cudaSuccess) {
+      delete t;
+      return cuda_fail(e, "backward weight image allocation", __FILE__, __LINE__);
+    }
+    f->train = t;
+  }
+  dim3 grid(s.NA / 16 + s.NBn / 16 + 65, s.L);
+  tt_pack_kernel<<<grid, 256, 0, st>>>(s, t->wimg, f->WfT, f->WaT, f->WbT, f->W0T);
+  PF_LAUNCH_CHECK(f);
+  return PF_OK;
+}
+
+void pf_tt_destroy(pf_flow* f) {
+  TtState* t = reinterpret_cast<TtState*>(f->train);
+  if (!t) return;
+  cudaFree(t->wimg);
+  delete t;
+  f->train = nullptr;
+}
+
+pf_status pf_tt_backward(pf_flow* f, cudaStream_t st, const TtSaved& sv, const TtWork& ws, int64_t R, const float* gz,
+                         const float* glogdet, float* gx, const pf_layer_grads* grads) {
+  TtState* t = reinterpret_cast<TtState*>(f->train);
+  if (!t) return PF_ERR_NOT_PACKED;
+  static bool attr_done[64] = {};
+  const int dev = f->desc.device;
+  if (dev < 64 && !attr_done[dev]) {
+    PF_CUDA(cudaFuncSetAttribute(tt_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TT_SMEM));
+    PF_CUDA(cudaFuncSetAttribute(tt_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
+    attr_done[dev] = true;
+  }
+  TtArgs a;
+  memset(&a, 0, sizeof(a));
+  a.s = t->s;
+  a.wimg = t->wimg;
+  a.proj = sv.proj;
+  a.ldproj = (int64_t)f->L * 3 * TT_H;
+  a.P = sv.P; a.XS = sv.XS; a.img = sv.img;
+  a.gz = gz; a.gl = glogdet;
+  a.gimg = ws.gimg; a.gproj = ws.gproj;
+  a.gx = gx;
+  for (int l = 0; l < f->L; ++l) a.dbf[l] = grads ? grads[l].final_b : nullptr;
+  a.R = R;
+  a.n_tiles = (int)((R + TT_ROWS - 1) / TT_ROWS);
+  a.tail = f->desc.tail_bound;
+  a.err = f->tg_err;
+  const int grid = a.n_tiles < f->sm_count ? a.n_tiles : f->sm_count;
+  tt_backward_kernel<<<grid, TT_THREADS, TT_SMEM, st>>>(a);
+  PF_LAUNCH_CHECK(f);
+  return PF_OK;
+}
+
+pf_status pf_tt_wgrad(pf_flow* f, cudaStream_t st, const TtSaved& sv, const TtWork& ws, int64_t R,
+                      const pf_layer_grads* grads) {
+  TtState* t = reinterpret_cast<TtState*>(f->train);
+  if (!t) return PF_ERR_NOT_PACKED;
+  if (!grads) return PF_OK;
+  TtWgArgs a;
+  memset(&a, 0, sizeof(a));
+  a.s = t->s;
+  a.img = sv.img; a.xt = sv.xt; a.gimg = ws.gimg;
+  a.tiles = (int)((R + TT_ROWS - 1) / TT_ROWS);
+  a.R = R;
+  a.perm = f->d_perm;
+  const char* sw = getenv("PF_MN_SWAP");
+  a.mn_swap = sw && sw[0] == '1';
+  a.err = f->tg_err;
+  for (int l = 0; l < f->L; ++l) a.g[l] = grads[l];
+  tt_wgrad_kernel<<<f->L * WG_JOBS, WG_THREADS, WG_SMEM, st>>>(a);
+  PF_LAUNCH_CHECK(f);
+  return PF_OK;
+}

@@ -1,0 +1,81 @@
+// Fused training step of the tensor-core tiers: shared definitions of the forward-with-saves kernel
+// (pf_tc_dense.cu, SAVE instantiation), the backward chain kernel and the weight-gradient kernel (pf_tc_train.cu),
+// and the host orchestration (pf_fp32.cu: pf_flow_forward(saved) / pf_flow_backward).
+//
+// Replaces, for one NLL training step of the flow head (experiments/train_lean_npe.py:357-369, flows.py:727-779):
+// 70 forward + 200 backward kernel launches of the GEMM-per-launch form by
+//   1  context projection GEMM            [R,288] x [288, L*3*256]                       (pf_tc_gemm.cuh)
+//   1  forward kernel                      all L layers per 128-row tile on chip, activations saved as bf16 images
+//   1  backward chain kernel               all L layers per tile: spline VJP -> 7 data-gradient MMA stages per layer
+//   1  weight-gradient kernel              one CTA per (layer, matrix, 128-row block of the output): contraction over
+//                                          ALL flow rows by MN-major tcgen05.mma on the saved images, bias gradients
+//                                          as column sums of the same tiles, plain stores (no atomics, no zero fill)
+//   3  context-path kernels                d ctx (GEMM), d Wctx (GEMM), d bctx (column sums) over the fp32 gate gradients
+#pragma once
+#include "pf_common.cuh"
+
+namespace pf {
+
+constexpr int TT_ROWS = 128;
+constexpr int TT_IMG = 65536;      // one [128 x 256] bf16 tile image (8-row x 16-byte core matrices, 2048 B per 8 columns)
+constexpr int TT_XT = 4096;        // one [128 x 16] bf16 x-tile image
+constexpr int TT_MAX_L = 32;
+
+// forward images (written by tc_dense_forward_kernel<3, true>)
+enum { TT_A_H0 = 0, TT_A_U1 = 1, TT_A_H1 = 2, TT_A_U2 = 3, TT_A_H2 = 4, TT_A_V1 = 5, TT_A_V1L = 6, TT_A_V2 = 7, TT_A_V2L = 8,
+       TT_NA = 9 };
+// gradient images (written by tt_backward_kernel): d params of dims 1..ga | ga+1.. , then the five hidden gradients
+enum { TT_G_PA = 0, TT_G_PB = 1, TT_G_V2 = 2, TT_G_U2 = 3, TT_G_V1 = 4, TT_G_U1 = 5, TT_G_H0 = 6, TT_NG = 7 };
+
+__host__ __device__ inline size_t tt_img_off(int l, int which, int nwhich, int tile, int tiles) {
+  return (((size_t)l * nwhich + which) * (size_t)tiles + tile) * TT_IMG;
+}
+
+static inline size_t tt_align(size_t b) { return (b + 255) / 256 * 256; }
+
+// carve of the `saved` buffer handed from pf_flow_forward to pf_flow_backward (fused form)
+struct TtSaved {
+  float* proj;    // [R][L*3*H]  relu(c0) | gate 1 | gate 2 per layer (sorted hidden order)
+  float* XS;      // [L][R][D]
+  float* P;       // [L][R][PLD]
+  uint8_t* img;   // [L][TT_NA][tiles][TT_IMG]
+  uint8_t* xt;    // [L][tiles][TT_XT]
+  size_t bytes;
+  TtSaved(const pf_flow* f, void* base, int64_t R) {
+    const size_t tiles = (size_t)((R + TT_ROWS - 1) / TT_ROWS);
+    char* p = reinterpret_cast<char*>(base);
+    size_t o = 0;
+    auto take = [&](size_t b) { char* r = p ? p + o : nullptr; o += tt_align(b); return r; };
+    proj = reinterpret_cast<float*>(take((size_t)R * f->L * 3 * f->H * 4));
+    XS = reinterpret_cast<float*>(take((size_t)f->L * R * f->D * 4));
+    P = reinterpret_cast<float*>(take((size_t)f->L * R * f->PLD * 4));
+    img = reinterpret_cast<uint8_t*>(take((size_t)f->L * TT_NA * tiles * TT_IMG));
+    xt = reinterpret_cast<uint8_t*>(take((size_t)f->L * tiles * TT_XT));
+    bytes = o;
+  }
+};
+
+// carve of the backward workspace (fused form)
+struct TtWork {
+  uint8_t* gimg;   // [L][TT_NG][tiles][TT_IMG]  bf16 gradient images
+  float* gproj;    // [R][L*3*H]  d loss / d (pre-activation of the context layers)
+  size_t bytes;
+  TtWork(const pf_flow* f, void* base, int64_t R) {
+    const size_t tiles = (size_t)((R + TT_ROWS - 1) / TT_ROWS);
+    char* p = reinterpret_cast<char*>(base);
+    size_t o = 0;
+    auto take = [&](size_t b) { char* r = p ? p + o : nullptr; o += tt_align(b); return r; };
+    gimg = reinterpret_cast<uint8_t*>(take((size_t)f->L * TT_NG * tiles * TT_IMG));
+    gproj = reinterpret_cast<float*>(take((size_t)R * f->L * 3 * f->H * 4));
+    bytes = o;
+  }
+};
+
+}  // namespace pf
+
+// pf_tc_train.cu
+bool pf_tt_supported(const pf_flow* f);
+pf_status pf_tt_backward(pf_flow* f, cudaStream_t st, const pf::TtSaved& sv, const pf::TtWork& ws, int64_t R, const float* gz,
+                         const float* glogdet, float* gx, const pf_layer_grads* grads);
+pf_status pf_tt_wgrad(pf_flow* f, cudaStream_t st, const pf::TtSaved& sv, const pf::TtWork& ws, int64_t R,
+                      const pf_layer_grads* grads);
