@@ -81,6 +81,17 @@ struct EpiCtxProj {
     out[(int64_t)m * ld + n] = sec == 0 ? fmaxf(v, 0.f) : 1.f / (1.f + expf(-v));
   }
 };
+// The same values in the tile-transposed layout of the fused training step (pf_train.cuh): out[tile][n][row in tile].
+// kLanesAlongRows: the tensor-core GEMM's epilogue then runs its lanes along m, so these stores are coalesced.
+struct EpiCtxProjT {
+  static constexpr bool kLanesAlongRows = true;
+  float* out; int ld; const float* bias; int H;
+  __device__ __forceinline__ void operator()(int m, int n, float acc) const {
+    float v = acc + bias[n];
+    int sec = (n / H) % 3;
+    out[((int64_t)(m / TT_ROWS) * ld + n) * TT_ROWS + (m % TT_ROWS)] = sec == 0 ? fmaxf(v, 0.f) : 1.f / (1.f + expf(-v));
+  }
+};
 // Epilogues may split into fetch(m, n) -> operands read from global memory, and apply(m, n, acc, fetched): a caller
 // that handles several elements per thread (pf_tc_gemm.cuh) issues all fetches of a batch before the first apply, so
 // the loads overlap instead of costing one memory latency per element.  operator() stays the single-call form.
@@ -251,6 +262,18 @@ using namespace pf;
 // ------------------------------------------------------------------------------------------------
 // context projection (A3)
 // ------------------------------------------------------------------------------------------------
+static pf_status ctxproj_tiled(pf_flow* f, cudaStream_t st, const float* ctx, int64_t E, uint32_t flags, float* proj) {
+  const int N = f->L * 3 * f->H;
+  if (E % TT_ROWS) {   // rows past E of the last tile are read (never used) by the chain kernels: keep them finite
+    const int64_t t = E / TT_ROWS;
+    PF_CUDA(cudaMemsetAsync(proj + t * N * TT_ROWS, 0, (size_t)N * TT_ROWS * sizeof(float), st));
+  }
+  EpiCtxProjT epi{proj, N, f->bctx, f->H};
+  if (flags & PF_FLAG_SANITIZE_CTX)
+    return gemm_nt<EpiCtxProjT, A_SANITIZE, 64>(f, st, ctx, f->C, f->Wctx, f->C, (int)E, N, f->C, epi);
+  return gemm_nt<EpiCtxProjT, A_PLAIN, 64>(f, st, ctx, f->C, f->Wctx, f->C, (int)E, N, f->C, epi);
+}
+
 static pf_status ctxproj_impl(pf_flow* f, cudaStream_t st, const float* ctx, int64_t E, uint32_t flags, float* proj) {
   const int N = f->L * 3 * f->H;
   EpiCtxProj epi{proj, N, f->bctx, f->H};
@@ -399,13 +422,9 @@ extern "C" pf_status pf_flow_forward(pf_flow* f, const float* x, const float* ct
     if (R > 8000000) return PF_ERR_INVALID;
     TtSaved sv(f, saved, R);
     const int64_t ldp = (int64_t)L * 3 * H;
-    if (flags & PF_FLAG_CTX_IS_PROJ) {
-      const int64_t n = R * ldp;
-      copy_rows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(ctx, sv.proj, n);
-      PF_LAUNCH_CHECK(f);
-    } else {
-      PF_TRY(ctxproj_impl(f, st, ctx, R, flags, sv.proj));
-    }
+    (void)ldp;
+    if (flags & PF_FLAG_CTX_IS_PROJ) return PF_ERR_UNSUPPORTED;   // a pre-projected context is row-major: GEMM-per-launch form only
+    PF_TRY(ctxproj_tiled(f, st, ctx, R, flags, sv.proj));
     const size_t need = pad256((size_t)R * D) + pad256((size_t)R);
     if ((!z || !logdet) && (!workspace || workspace_bytes < need)) return PF_ERR_WORKSPACE;
     float* zb = z ? z : reinterpret_cast<float*>(workspace);
@@ -805,23 +824,39 @@ struct ColMapAll {
     return d ? d + perm[c % H] : nullptr;
   }
 };
-__global__ void colsum_all_kernel(const float* __restrict__ src, int ld, int R, int ncols, int rows_per_slab, ColMapAll map) {
-  __shared__ float red[8][33];
-  int c = blockIdx.x * 32 + threadIdx.x;
-  int rbeg = blockIdx.y * rows_per_slab, rend = min(R, rbeg + rows_per_slab);
+// column sums of a tile-transposed [tiles][ncols][128] array: one warp per column, float4 per lane and tile
+__global__ void __launch_bounds__(256) colsum_tiled_kernel(const float* __restrict__ src, int ncols, int tiles, ColMapAll map) {
+  const int c = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (c >= ncols) return;
   float s = 0.f;
-  if (c < ncols)
-    for (int r = rbeg + threadIdx.y; r < rend; r += 8) s += src[(int64_t)r * ld + c];
-  red[threadIdx.y][threadIdx.x] = s;
-  __syncthreads();
-  if (threadIdx.y == 0 && c < ncols) {
-    float t = 0.f;
+  for (int t = 0; t < tiles; ++t) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(src + ((size_t)t * ncols + c) * TT_ROWS) + lane);
+    s += (v.x + v.y) + (v.z + v.w);
+  }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) t += red[i][threadIdx.x];
+  for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) {
     float* d = map(c);
-    if (d) atomicAdd(d, t);
+    if (d) atomicAdd(d, s);
   }
 }
+// element (flow row m, column n) of a tile-transposed array; as the TN source's (contraction m, output n) loader ...
+struct LoadTileTk {   // ... with the flow rows as the contraction index: la(m = row, n = column)
+  const float* p; int ncols;
+  __device__ __forceinline__ float operator()(int m, int n) const {
+    return p[((int64_t)(m / TT_ROWS) * ncols + n) * TT_ROWS + (m % TT_ROWS)];
+  }
+};
+struct LoadTileT {    // ... with the columns as the contraction index: la(m = column, n = row) -- lanes along the rows
+  const float* p; int ncols;
+  __device__ __forceinline__ float operator()(int m, int n) const {
+    return p[((int64_t)(n / TT_ROWS) * ncols + m) * TT_ROWS + (n % TT_ROWS)];
+  }
+};
+struct EpiAccum {     // out[m, n] += acc   (the tensor-core TN kernel splits the contraction over CTAs: atomic)
+  float* out; int ld;
+  __device__ __forceinline__ void operator()(int m, int n, float acc) const { atomicAdd(out + (int64_t)m * ld + n, acc); }
+};
 struct LoadRev {  // X[m, D-1-n]
   const float* p; int D;
   __device__ __forceinline__ float operator()(int m, int n) const { return p[(int64_t)m * D + (D - 1 - n)]; }
@@ -894,10 +929,10 @@ extern "C" pf_status pf_flow_backward(pf_flow* f, const void* saved, const float
     if (!workspace || ws.bytes > workspace_bytes) return PF_ERR_WORKSPACE;
     PF_TRY(pf_tt_backward(f, st, sv, ws, R, gz, glogdet, gx, grads));
     PF_TRY(pf_tt_wgrad(f, st, sv, ws, R, grads));
-    CtxMap cmd{nullptr, 1, 0};
     const int NL = L * 3 * H;
-    if (gctx)      // d ctx [R, C] = gproj [R, L*3H] . Wctx [L*3H, C]   (WctxT is [C][L*3H]: the "N x K" operand)
-      PF_TRY((gemm_nt<EpiCtxAtomic, A_PLAIN, 64>(f, st, ws.gproj, NL, f->WctxT, NL, R, C, NL, EpiCtxAtomic{gctx, C, cmd})));
+    if (gctx)      // d ctx [R, C] = gproj [R, L*3H] . Wctx [L*3H, C]: contraction over the L*3H columns, read from the
+                   // tile-transposed gproj with the lanes along the flow rows
+      PF_TRY((gemm_tn(f, st, LoadTileT{ws.gproj, NL}, LoadPlain{f->Wctx, C}, NL, R, C, EpiAccum{gctx, C})));
     if (grads) {
       EpiWgradCtxAll ew;
       ColMapAll cmap;
@@ -911,14 +946,11 @@ extern "C" pf_status pf_flow_backward(pf_flow* f, const void* saved, const float
         cmap.dst[l * 3] = grads[l].ctx_b; cmap.dst[l * 3 + 1] = grads[l].blk_ctx_b[0]; cmap.dst[l * 3 + 2] = grads[l].blk_ctx_b[1];
         for (int k = 0; k < 3; ++k) { any_w = any_w || ew.dst[l * 3 + k]; any_b = any_b || cmap.dst[l * 3 + k]; }
       }
-      if (any_w)
-        PF_TRY((gemm_tn(f, st, LoadPlain{ws.gproj, NL}, LoadCtx{ctx, C, cmd}, R, NL, C, ew)));
+      if (any_w)   // d Wctx [L*3H, C] = gproj^T . ctx: contraction over the flow rows
+        PF_TRY((gemm_tn(f, st, LoadTileTk{ws.gproj, NL}, LoadPlain{ctx, C}, R, NL, C, ew)));
       if (any_b) {
-        int slabs = cdiv(R, 64);
-        if (slabs > 2 * f->sm_count) slabs = 2 * f->sm_count;
-        const int rps = cdiv(R, slabs);
-        dim3 grid(cdiv(NL, 32), cdiv(R, rps)), block(32, 8);
-        colsum_all_kernel<<<grid, block, 0, st>>>(ws.gproj, NL, R, NL, rps, cmap);
+        const int tiles = (R + TT_ROWS - 1) / TT_ROWS;
+        colsum_tiled_kernel<<<cdiv(NL, 8), 256, 0, st>>>(ws.gproj, NL, tiles, cmap);
         PF_LAUNCH_CHECK(f);
       }
     }

@@ -60,8 +60,8 @@ enum { DN_IMG_H0 = 0, DN_IMG_U1 = 1, DN_IMG_H1 = 2, DN_IMG_U2 = 3, DN_IMG_H2 = 4
 struct DnSave {
   uint8_t* img;      // [L][DN_NIMG][tiles][65536]
   uint8_t* xt;       // [L][tiles][4096]  bf16 x tile of the layer, [128 x 16] in the same layout (columns = reversed dims)
-  float* P;          // [L][R][PLD]  spline parameters (final-layer output incl. bias)
-  float* XS;         // [L][R][D]    input of layer l (before its ReversePermutation)
+  float* P;          // [L][tiles][PLD][128]  spline parameters (final-layer output incl. bias), tile-transposed: row minor
+  float* XS;         // [L][tiles][D][128]    input of layer l (before its ReversePermutation), tile-transposed
   int64_t R;         // rows of the whole call
   int tiles;         // tiles of the whole call
 };
@@ -374,7 +374,7 @@ __global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const D
           const float v = valid ? a.x[grow * D + j] : 0.f;
           yin[j] = v;
           put_x(D - 1 - j, v, 0, tile);
-          if constexpr (SAVE) if (valid) a.sv.XS[grow * D + j] = v;
+          if constexpr (SAVE) a.sv.XS[((size_t)tile * D + j) * DN_ROWS + r] = v;
         }
       }
       arrive_ops();                                             // x tile of layer 0
@@ -418,6 +418,9 @@ __global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const D
         mark(0);
         const float* cctx = cst + DN_CST_CTX + esel * 5 * DN_H;
         const float* pl = projr + (size_t)l * 3 * DN_H;
+        // SAVE (training): the projection is tile-transposed [tile][L*3*H][128]: column c of this row at plt[c * 128]
+        const float* plt = a.proj + ((size_t)tile * a.ldproj + (size_t)l * 3 * DN_H) * DN_ROWS + r;
+        (void)plt;
         // ---- five hidden stages: I, A1, B1, A2, B2 ----
 #pragma unroll 1
         for (int st = 0; st < 5 && ok; ++st) {
@@ -459,7 +462,13 @@ __global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const D
 #pragma unroll
                   for (int i = 0; i < 32; i += 4) {
                     const float4 t4 = *reinterpret_cast<const float4*>(bias + c0 + i);
-                    const float4 g4 = __ldg(reinterpret_cast<const float4*>(pl + c0 + i));
+                    float4 g4;
+                    if constexpr (SAVE) {
+                      g4 = make_float4(__ldg(plt + (size_t)(c0 + i) * DN_ROWS), __ldg(plt + (size_t)(c0 + i + 1) * DN_ROWS),
+                                       __ldg(plt + (size_t)(c0 + i + 2) * DN_ROWS), __ldg(plt + (size_t)(c0 + i + 3) * DN_ROWS));
+                    } else {
+                      g4 = __ldg(reinterpret_cast<const float4*>(pl + c0 + i));
+                    }
                     o[i] = fmaf(__uint_as_float(v[i]), ASC, t4.x) + g4.x; o[i + 1] = fmaf(__uint_as_float(v[i + 1]), ASC, t4.y) + g4.y;
                     o[i + 2] = fmaf(__uint_as_float(v[i + 2]), ASC, t4.z) + g4.z; o[i + 3] = fmaf(__uint_as_float(v[i + 3]), ASC, t4.w) + g4.w;
                   }
@@ -482,7 +491,13 @@ __global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const D
 #pragma unroll
                   for (int i = 0; i < 32; i += 4) {
                     const float4 t4 = *reinterpret_cast<const float4*>(bias + c0 + i);
-                    const float4 g4 = __ldg(reinterpret_cast<const float4*>(pl + sec * DN_H + c0 + i));
+                    float4 g4;
+                    if constexpr (SAVE) {
+                      const float* pg = plt + (size_t)(sec * DN_H + c0 + i) * DN_ROWS;
+                      g4 = make_float4(__ldg(pg), __ldg(pg + DN_ROWS), __ldg(pg + 2 * DN_ROWS), __ldg(pg + 3 * DN_ROWS));
+                    } else {
+                      g4 = __ldg(reinterpret_cast<const float4*>(pl + sec * DN_H + c0 + i));
+                    }
                     o[i] = fmaf(g4.x, fmaf(__uint_as_float(v[i]), ASC, t4.x), __uint_as_float(hr[i]));
                     o[i + 1] = fmaf(g4.y, fmaf(__uint_as_float(v[i + 1]), ASC, t4.y), __uint_as_float(hr[i + 1]));
                     o[i + 2] = fmaf(g4.z, fmaf(__uint_as_float(v[i + 2]), ASC, t4.z), __uint_as_float(hr[i + 2]));
@@ -596,12 +611,10 @@ __global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const D
           }
           const float xin = yin[D - 1 - j];
           bad = bad || !(fabsf(xin) <= 3.0e38f);
-          if constexpr (SAVE) {
-            if (valid) {
-              float* pr = a.sv.P + ((size_t)l * a.sv.R + grow) * s.PLD + j * DN_MULT;
+          if constexpr (SAVE) {   // row-minor layout: the 32 rows of a warp store one 128-byte line per parameter
+            float* pr = a.sv.P + (((size_t)l * a.sv.tiles + tile) * s.PLD + j * DN_MULT) * DN_ROWS + r;
 #pragma unroll
-              for (int i = 0; i < DN_MULT; ++i) pr[i] = q[i];
-            }
+            for (int i = 0; i < DN_MULT; ++i) pr[(size_t)i * DN_ROWS] = q[i];
           }
           float lad;
           float y;
@@ -611,7 +624,7 @@ __global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const D
           yout[j] = y;
           if (l + 1 < s.L) {
             put_x(D - 1 - j, y, l + 1, tile);
-            if constexpr (SAVE) if (valid) a.sv.XS[((size_t)(l + 1) * a.sv.R + grow) * D + j] = y;
+            if constexpr (SAVE) a.sv.XS[(((size_t)(l + 1) * a.sv.tiles + tile) * D + j) * DN_ROWS + r] = y;
           }
         }
         if (half == 0) {                                       // keep the group-B barrier phase in step

@@ -35,6 +35,12 @@ constexpr int TG_THREADS = TG_PRODUCERS + 32;   // + warp 8: MMA issuer, owns th
 constexpr int TG_EU = 8;           // epilogue elements per thread whose global reads are in flight together
                                    // (16 for the 32-column tiles -- their whole share in one batch -- measured slower:
                                    //  2.61 vs 2.28 ms per 948-row training step)
+// An epilogue functor may ask for the warp's lanes to run along the output ROW index (kLanesAlongRows = true): it
+// then writes a row-minor ("tile-transposed") layout with coalesced stores.  Default: lanes along the column index.
+template <class E, class = void>
+struct tg_lanes_along_rows : std::false_type {};
+template <class E>
+struct tg_lanes_along_rows<E, std::enable_if_t<E::kLanesAlongRows>> : std::true_type {};
 template <class E, class = void>
 struct tg_has_fetch : std::false_type {};
 template <class E>
@@ -258,6 +264,12 @@ tc_gemm_kernel(const Src src, int MA, int NBc, int K, int k_per_slice, Epi epi, 
           const int idx = base + u * TG_PRODUCERS, r = idx / BN, c = idx % BN;
           if (idx < TG_ROWS * BN && m0 + r < MA && n0 + c < NBc) epi.apply(m0 + r, n0 + c, stage[r * LD + c], t[u]);
         }
+      }
+    } else if constexpr (tg_lanes_along_rows<Epi>::value) {
+#pragma unroll 4
+      for (int idx = tid; idx < TG_ROWS * BN; idx += TG_PRODUCERS) {
+        const int r = idx % TG_ROWS, c = idx / TG_ROWS;      // LD = BN + 1 is odd: conflict-free column reads
+        if (m0 + r < MA && n0 + c < NBc) epi(m0 + r, n0 + c, stage[r * LD + c]);
       }
     } else {
 #pragma unroll 4

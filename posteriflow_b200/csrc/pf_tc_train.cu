@@ -97,12 +97,12 @@ __global__ void tt_pack_kernel(TtShape s, uint8_t* __restrict__ image, const flo
 struct TtArgs {
   TtShape s;
   const uint8_t* wimg;
-  const float* proj; int64_t ldproj;    // [R][L*3*H]
-  const float* P; const float* XS;      // saved by the forward
+  const float* proj; int64_t ldproj;    // [tiles][L*3*H][128]  tile-transposed (pf_train.cuh)
+  const float* P; const float* XS;      // [L][tiles][PLD][128], [L][tiles][D][128]  saved by the forward
   const uint8_t* img;                   // [L][TT_NA][tiles][TT_IMG]
   const float* gz; const float* gl;     // upstream gradients [R, D], [R] (either may be NULL = 0)
   uint8_t* gimg;                        // [L][TT_NG][tiles][TT_IMG]
-  float* gproj;                         // [R][L*3*H]
+  float* gproj;                         // [tiles][L*3*H][128]
   float* gx;                            // [R, D] or NULL
   float* dbf[TT_MAX_L];                 // final_layer.bias gradient of each layer (dim 0's 47 entries) or NULL
   int64_t R; int n_tiles; float tail; int* err;
@@ -221,8 +221,9 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
         for (int j = 0; j < D; ++j) gy_s[r * 12 + j] = (valid && a.gz) ? a.gz[grow * D + j] : 0.f;
       bar_sync(3, 256);
       for (int l = s.L - 1; l >= 0 && ok; --l) {
-        const float* projr = a.proj + growc * a.ldproj + (size_t)l * 3 * TT_H;
-        float* gprojr = a.gproj + growc * a.ldproj + (size_t)l * 3 * TT_H;
+        // row-minor layouts: column c of this thread's row sits at base[c * 128] (one 128-byte line per warp access)
+        const float* projr = a.proj + ((size_t)tile * a.ldproj + (size_t)l * 3 * TT_H) * TT_ROWS + r;
+        float* gprojr = a.gproj + ((size_t)tile * a.ldproj + (size_t)l * 3 * TT_H) * TT_ROWS + r;
         // ---------------- E0: spline VJP -> d params (two operand tiles: dims 1..ga, then ga+1..) ----------------
 #pragma unroll 1
         for (int ps = 0; ps < 2 && ok; ++ps) {
@@ -236,10 +237,10 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
             const bool is0 = (ps == 0 && half == 1 && jj == jcnt - 1);
             const int j = is0 ? 0 : jbeg + jj;
             float q[TT_MULT], gp[TT_MULT];
-            const float* pr = a.P + ((size_t)l * a.R + growc) * s.PLD + j * TT_MULT;
+            const float* pr = a.P + (((size_t)l * a.n_tiles + tile) * s.PLD + j * TT_MULT) * TT_ROWS + r;
 #pragma unroll
-            for (int i = 0; i < TT_MULT; ++i) q[i] = __ldg(pr + i);
-            const float xin = a.XS[((size_t)l * a.R + growc) * D + (D - 1 - j)];
+            for (int i = 0; i < TT_MULT; ++i) q[i] = __ldg(pr + (size_t)i * TT_ROWS);
+            const float xin = a.XS[(((size_t)l * a.n_tiles + tile) * D + (D - 1 - j)) * TT_ROWS + r];
             const float gyj = gy_s[r * 12 + j];
             const float gxd = rqs_forward_backward<TT_NB>(TtRegQ{q}, xin, a.tail, gyj, glr, TtGradOut{gp});
             gxd_s[r * 12 + j] = valid ? gxd : 0.f;
@@ -335,10 +336,7 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
             }
             if (gate || k == 4) {
 #pragma unroll
-              for (int i = 0; i < 32; i += 4) {
-                const float4 t4 = __ldg(reinterpret_cast<const float4*>(projr + sec * TT_H + c0 + i));
-                g[i] = t4.x; g[i + 1] = t4.y; g[i + 2] = t4.z; g[i + 3] = t4.w;
-              }
+              for (int i = 0; i < 32; ++i) g[i] = __ldg(projr + (size_t)(sec * TT_H + c0 + i) * TT_ROWS);
             }
             tmem_wait_ld();
             float o[32];
@@ -370,19 +368,11 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
                 gp4[i] = o[i] * vv * g[i] * (1.f - g[i]);
                 o[i] *= g[i];
               }
-              if (valid) {
 #pragma unroll
-                for (int i = 0; i < 32; i += 4)
-                  *reinterpret_cast<float4*>(gprojr + sec * TT_H + c0 + i) = make_float4(gp4[i], gp4[i + 1], gp4[i + 2], gp4[i + 3]);
-              }
+              for (int i = 0; i < 32; ++i) gprojr[(size_t)(sec * TT_H + c0 + i) * TT_ROWS] = gp4[i];   // (rows past R: exact zeros)
             } else if (k == 4) {             // relu(context_layer) backward: g[] holds the relu'd context term
-              if (valid) {
 #pragma unroll
-                for (int i = 0; i < 32; i += 4)
-                  *reinterpret_cast<float4*>(gprojr + c0 + i) =
-                      make_float4(g[i] > 0.f ? o[i] : 0.f, g[i + 1] > 0.f ? o[i + 1] : 0.f, g[i + 2] > 0.f ? o[i + 2] : 0.f,
-                                  g[i + 3] > 0.f ? o[i + 3] : 0.f);
-              }
+              for (int i = 0; i < 32; ++i) gprojr[(size_t)(c0 + i) * TT_ROWS] = g[i] > 0.f ? o[i] : 0.f;
             }
 #pragma unroll
             for (int i = 0; i < 4; ++i) {

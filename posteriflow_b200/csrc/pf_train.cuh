@@ -30,14 +30,20 @@ enum { TT_G_PA = 0, TT_G_PB = 1, TT_G_V2 = 2, TT_G_U2 = 3, TT_G_V1 = 4, TT_G_U1 
 __host__ __device__ inline size_t tt_img_off(int l, int which, int nwhich, int tile, int tiles) {
   return (((size_t)l * nwhich + which) * (size_t)tiles + tile) * TT_IMG;
 }
+// Per-row fp32 arrays are kept TILE-TRANSPOSED: [tile][column][128 rows].  A chain-kernel thread owns one row of its tile
+// (tcgen05.ld offers no other mapping), so with the row index minor every load / store of a warp is one 128-byte line;
+// row-major [R][columns] would cost one line per LANE (32 LSU wavefronts per instruction, partial-sector writes).
+__host__ __device__ inline size_t tt_t_off(int tile, int ncols, int col, int row_in_tile) {
+  return ((size_t)tile * ncols + col) * TT_ROWS + row_in_tile;
+}
 
 static inline size_t tt_align(size_t b) { return (b + 255) / 256 * 256; }
 
 // carve of the `saved` buffer handed from pf_flow_forward to pf_flow_backward (fused form)
 struct TtSaved {
-  float* proj;    // [R][L*3*H]  relu(c0) | gate 1 | gate 2 per layer (sorted hidden order)
-  float* XS;      // [L][R][D]
-  float* P;       // [L][R][PLD]
+  float* proj;    // [tiles][L*3*H][128]  relu(c0) | gate 1 | gate 2 per layer (sorted hidden order), tile-transposed
+  float* XS;      // [L][tiles][D][128]   input of layer l (before its ReversePermutation), tile-transposed
+  float* P;       // [L][tiles][PLD][128] spline parameters, tile-transposed
   uint8_t* img;   // [L][TT_NA][tiles][TT_IMG]
   uint8_t* xt;    // [L][tiles][TT_XT]
   size_t bytes;
@@ -46,9 +52,9 @@ struct TtSaved {
     char* p = reinterpret_cast<char*>(base);
     size_t o = 0;
     auto take = [&](size_t b) { char* r = p ? p + o : nullptr; o += tt_align(b); return r; };
-    proj = reinterpret_cast<float*>(take((size_t)R * f->L * 3 * f->H * 4));
-    XS = reinterpret_cast<float*>(take((size_t)f->L * R * f->D * 4));
-    P = reinterpret_cast<float*>(take((size_t)f->L * R * f->PLD * 4));
+    proj = reinterpret_cast<float*>(take(tiles * TT_ROWS * (size_t)f->L * 3 * f->H * 4));
+    XS = reinterpret_cast<float*>(take((size_t)f->L * tiles * TT_ROWS * f->D * 4));
+    P = reinterpret_cast<float*>(take((size_t)f->L * tiles * TT_ROWS * f->PLD * 4));
     img = reinterpret_cast<uint8_t*>(take((size_t)f->L * TT_NA * tiles * TT_IMG));
     xt = reinterpret_cast<uint8_t*>(take((size_t)f->L * tiles * TT_XT));
     bytes = o;
@@ -58,7 +64,7 @@ struct TtSaved {
 // carve of the backward workspace (fused form)
 struct TtWork {
   uint8_t* gimg;   // [L][TT_NG][tiles][TT_IMG]  bf16 gradient images
-  float* gproj;    // [R][L*3*H]  d loss / d (pre-activation of the context layers)
+  float* gproj;    // [tiles][L*3*H][128]  d loss / d (pre-activation of the context layers), tile-transposed
   size_t bytes;
   TtWork(const pf_flow* f, void* base, int64_t R) {
     const size_t tiles = (size_t)((R + TT_ROWS - 1) / TT_ROWS);
@@ -66,7 +72,7 @@ struct TtWork {
     size_t o = 0;
     auto take = [&](size_t b) { char* r = p ? p + o : nullptr; o += tt_align(b); return r; };
     gimg = reinterpret_cast<uint8_t*>(take((size_t)f->L * TT_NG * tiles * TT_IMG));
-    gproj = reinterpret_cast<float*>(take((size_t)R * f->L * 3 * f->H * 4));
+    gproj = reinterpret_cast<float*>(take(tiles * TT_ROWS * (size_t)f->L * 3 * f->H * 4));
     bytes = o;
   }
 };
