@@ -12,6 +12,8 @@
 //   flows.py:727-779  compute_psd_aware_nll             -> pf_flow_forward(nll != NULL)
 //   lean_npe.py:318-332 LeanNPE.sample_posterior (post-encoder) -> pf_sample_fused
 //   loss.backward() through nflows (experiments/train_lean_npe.py:365) -> pf_flow_backward
+#include <stdlib.h>
+
 #include "pf_common.cuh"
 #include "pf_gemm.cuh"
 #include "pf_tc_gemm.cuh"
@@ -424,7 +426,13 @@ extern "C" pf_status pf_flow_forward(pf_flow* f, const float* x, const float* ct
     const int64_t ldp = (int64_t)L * 3 * H;
     (void)ldp;
     if (flags & PF_FLAG_CTX_IS_PROJ) return PF_ERR_UNSUPPORTED;   // a pre-projected context is row-major: GEMM-per-launch form only
-    PF_TRY(ctxproj_tiled(f, st, ctx, R, flags, sv.proj));
+    {
+      const char* ct = getenv("PF_CTX_TC");
+      if (f->C <= TT_CIMG_COLS && !(flags & PF_FLAG_SANITIZE_CTX) && !(ct && ct[0] == '0'))
+        PF_TRY(pf_tt_ctxproj(f, st, ctx, R, sv.proj, sv.c16));       // tcgen05 projection kernel (pf_tc_train.cu)
+      else
+        PF_TRY(ctxproj_tiled(f, st, ctx, R, flags, sv.proj));        // generic tensor-core GEMM, fp32 operands split on the fly
+    }
     const size_t need = pad256((size_t)R * D) + pad256((size_t)R);
     if ((!z || !logdet) && (!workspace || workspace_bytes < need)) return PF_ERR_WORKSPACE;
     float* zb = z ? z : reinterpret_cast<float*>(workspace);
@@ -928,31 +936,14 @@ extern "C" pf_status pf_flow_backward(pf_flow* f, const void* saved, const float
     TtWork ws(f, workspace, R);
     if (!workspace || ws.bytes > workspace_bytes) return PF_ERR_WORKSPACE;
     PF_TRY(pf_tt_backward(f, st, sv, ws, R, gz, glogdet, gx, grads));
-    PF_TRY(pf_tt_wgrad(f, st, sv, ws, R, grads));
+    PF_TRY(pf_tt_wgrad(f, st, sv, ws, R, ctx, grads));
     const int NL = L * 3 * H;
-    if (gctx)      // d ctx [R, C] = gproj [R, L*3H] . Wctx [L*3H, C]: contraction over the L*3H columns, read from the
-                   // tile-transposed gproj with the lanes along the flow rows
-      PF_TRY((gemm_tn(f, st, LoadTileT{ws.gproj, NL}, LoadPlain{f->Wctx, C}, NL, R, C, EpiAccum{gctx, C})));
-    if (grads) {
-      EpiWgradCtxAll ew;
-      ColMapAll cmap;
-      memset(&ew, 0, sizeof(ew));
-      memset(&cmap, 0, sizeof(cmap));
-      ew.C = C; ew.H = H; ew.perm = f->d_perm;
-      cmap.H = H; cmap.perm = f->d_perm;
-      bool any_w = false, any_b = false;
-      for (int l = 0; l < L; ++l) {
-        ew.dst[l * 3] = grads[l].ctx_w; ew.dst[l * 3 + 1] = grads[l].blk_ctx_w[0]; ew.dst[l * 3 + 2] = grads[l].blk_ctx_w[1];
-        cmap.dst[l * 3] = grads[l].ctx_b; cmap.dst[l * 3 + 1] = grads[l].blk_ctx_b[0]; cmap.dst[l * 3 + 2] = grads[l].blk_ctx_b[1];
-        for (int k = 0; k < 3; ++k) { any_w = any_w || ew.dst[l * 3 + k]; any_b = any_b || cmap.dst[l * 3 + k]; }
-      }
-      if (any_w)   // d Wctx [L*3H, C] = gproj^T . ctx: contraction over the flow rows
-        PF_TRY((gemm_tn(f, st, LoadTileTk{ws.gproj, NL}, LoadPlain{ctx, C}, R, NL, C, ew)));
-      if (any_b) {
-        const int tiles = (R + TT_ROWS - 1) / TT_ROWS;
-        colsum_tiled_kernel<<<cdiv(NL, 8), 256, 0, st>>>(ws.gproj, NL, tiles, cmap);
-        PF_LAUNCH_CHECK(f);
-      }
+    if (gctx) {    // d ctx [R, C] = gproj [R, L*3H] . Wctx [L*3H, C]
+      const char* ct = getenv("PF_CTX_TC");
+      if (C <= TT_CIMG_COLS && !(ct && ct[0] == '0'))
+        PF_TRY(pf_tt_dctx(f, st, ws, R, gctx));                      // tcgen05 kernel over the gradient images
+      else        // generic GEMM: contraction over the L*3H columns of the tile-transposed fp32 gproj, lanes along the rows
+        PF_TRY((gemm_tn(f, st, LoadTileT{ws.gproj, NL}, LoadPlain{f->Wctx, C}, NL, R, C, EpiAccum{gctx, C})));
     }
     return train_tc_check(f, st, "pf_flow_backward (fused)");
   }

@@ -14,6 +14,7 @@
 //                        as MN-major operands (the contraction index is the tile row), double-buffered bulk loads; bias
 //                        gradients are the column sums of the same G tiles.  Plain read-modify-write stores into nflows'
 //                        own weight layout: every output entry has exactly one owner CTA (no atomics).
+#include <cuda_fp16.h>
 #include <stdlib.h>
 
 #include "pf_common.cuh"
@@ -41,7 +42,11 @@ struct TtShape {
 struct TtState {
   TtShape s;
   uint8_t* wimg;     // [L][layer_bytes] backward weight image
+  uint8_t* cfimg;    // context projection, forward: [L*3 column blocks][C/16 chunks][fp16 hi | lo of 16 W, 16 KB]
+  uint8_t* cbimg;    // context projection, d ctx:   [L*3 blocks][16 chunks][bf16 hi | lo of W^T, (C x 16) x 2 x 2 B]
+  int C, CK;         // context width, K = 16 chunks of it
 };
+constexpr int TT_CB_CHUNK = TT_CIMG_COLS * 16 * 2 * 2;    // 18 432 bytes: [288 x 16] bf16 hi | lo
 
 // ------------------------------------------------------------------------------------------------
 // backward weight image: 16 KB slots, each the bf16 (hi | lo) pair of one K = 16 chunk of a TRANSPOSED matrix in the
@@ -91,6 +96,39 @@ __global__ void tt_pack_kernel(TtShape s, uint8_t* __restrict__ image, const flo
   }
 }
 
+// context-layer weight images.  Wctx is the handle's [L*3*H][C] array (rows = sorted hidden units, sections c0 | gate 1 |
+// gate 2 per layer).  blockIdx.y = column block nb = l * 3 + section (256 rows of Wctx).
+//   forward (blockIdx.x <  CK):      chunk kc of B[n = hidden unit][k = context column]: fp16 hi | lo of 16 W   (16 KB)
+//   d ctx   (blockIdx.x >= CK, 16):  chunk kc of B[n = context column][k = hidden unit]: bf16 hi | lo of W      (18 KB)
+__global__ void tt_pack_ctx_kernel(const float* __restrict__ Wctx, int C, int CK, uint8_t* __restrict__ cfimg,
+                                   uint8_t* __restrict__ cbimg) {
+  const int nb = blockIdx.y;
+  if ((int)blockIdx.x < CK) {
+    const int kc = blockIdx.x;
+    __half* dst = reinterpret_cast<__half*>(cfimg + ((size_t)nb * CK + kc) * TT_SLOT);
+    for (int e = threadIdx.x; e < 256 * 16; e += blockDim.x) {
+      const int n = e / 16, kk = e % 16, c = kc * 16 + kk;
+      const float v = c < C ? Wctx[((size_t)nb * TT_H + n) * C + c] * 16.f : 0.f;
+      const float vs = fminf(fmaxf(v, -60000.f), 60000.f);
+      const int o = (kk / 8) * (256 * 8) + (n / 8) * 64 + (n % 8) * 8 + (kk % 8);
+      const __half hi = __float2half_rn(vs);
+      dst[o] = hi;
+      dst[256 * 16 + o] = __float2half_rn(vs - __half2float(hi));
+    }
+  } else {
+    const int kc = blockIdx.x - CK;
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(cbimg + ((size_t)nb * 16 + kc) * TT_CB_CHUNK);
+    for (int e = threadIdx.x; e < TT_CIMG_COLS * 16; e += blockDim.x) {
+      const int n = e / 16, kk = e % 16;                     // n = context column, k = hidden unit kc * 16 + kk
+      const float v = n < C ? Wctx[((size_t)nb * TT_H + kc * 16 + kk) * C + n] : 0.f;
+      const int o = (kk / 8) * (TT_CIMG_COLS * 8) + (n / 8) * 64 + (n % 8) * 8 + (kk % 8);
+      const __nv_bfloat16 hi = __float2bfloat16(v);
+      dst[o] = hi;
+      dst[TT_CIMG_COLS * 16 + o] = __float2bfloat16(v - __bfloat162float(hi));
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // the backward chain kernel
 // ------------------------------------------------------------------------------------------------
@@ -106,6 +144,7 @@ struct TtArgs {
   float* gx;                            // [R, D] or NULL
   float* dbf[TT_MAX_L];                 // final_layer.bias gradient of each layer (dim 0's 47 entries) or NULL
   int64_t R; int n_tiles; float tail; int* err;
+  long long* prof;                      // NULL, or 8 cycle counters filled by CTA 0 (PF_TC_PROF=1)
 };
 
 constexpr int TT_OFF_ACT = 0;
@@ -193,6 +232,13 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
     const int ch = half * 128;
     uint32_t acc_par = 0;
     bool ok = true;
+    // cycle profile of CTA 0 (PF_TC_PROF=1): 0 spline VJP | 1 wait before the second parameter tile | 2 hidden waits |
+    // 3 hidden epilogues | 4 wait + d x epilogue | 5 publish / reopen | 6 total
+    const bool prof = a.prof && blockIdx.x == 0 && tid == 0;
+    long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long tmark = clock64();
+    const long long t_begin = tmark;
+    auto mark = [&](int k) { if (prof) { const long long n = clock64(); pc[k] += n - tmark; tmark = n; } };
     // operand tile complete: make it visible to the async proxy, start the bulk copy of its hi half to `gdst` (the
     // gradient image the weight-gradient kernel reads), hand it to the MMA warp
     auto publish = [&](uint8_t* gdst) {
@@ -212,10 +258,22 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
       if (rt == 0) bulk_wait_read0();
       bar_sync(3, 256);
     };
+    // 32 columns of this thread's row -> bf16 hi / lo tile images in global memory (the context-layer gradients: operands
+    // of the weight-gradient kernel and of the d ctx product)
+    auto store_image = [&](uint8_t* ghi, uint8_t* glo, int c0, const float* vals) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        uint4 w4, l4;
+        split_bf16(vals[8 * i], vals[8 * i + 1], w4.x, l4.x); split_bf16(vals[8 * i + 2], vals[8 * i + 3], w4.y, l4.y);
+        split_bf16(vals[8 * i + 4], vals[8 * i + 5], w4.z, l4.z); split_bf16(vals[8 * i + 6], vals[8 * i + 7], w4.w, l4.w);
+        const size_t io = (size_t)(c0 / 8 + i) * 2048 + rowoff;
+        *reinterpret_cast<uint4*>(ghi + io) = w4;
+        *reinterpret_cast<uint4*>(glo + io) = l4;
+      }
+    };
     for (int tile = blockIdx.x; tile < a.n_tiles && ok; tile += gridDim.x) {
       const int64_t grow = (int64_t)tile * TT_ROWS + r;
       const bool valid = grow < a.R;
-      const int64_t growc = valid ? grow : a.R - 1;               // clamped row for loads of per-row constants
       const float glr = (valid && a.gl) ? a.gl[grow] : 0.f;
       if (half == 0)
         for (int j = 0; j < D; ++j) gy_s[r * 12 + j] = (valid && a.gz) ? a.gz[grow * D + j] : 0.f;
@@ -262,11 +320,14 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
               continue;
             }
             if (!opened) {
+              mark(0);
               if (ps == 1) {   // the MMAs of group A must be done with the operand tile
                 if (!(ok = wait(acc_bar, acc_par, 50))) break;
                 acc_par ^= 1;
               }
+              mark(1);
               reopen();
+              mark(5);
               opened = true;
             }
             const int cbase = (j - gfirst) * TT_MULT;
@@ -288,7 +349,9 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
             }
             reopen();
           }
+          mark(0);
           publish(a.gimg + tt_img_off(l, ps == 0 ? TT_G_PA : TT_G_PB, TT_NG, tile, a.n_tiles));
+          mark(5);
         }
         if (!ok) break;
         // ---------------- E2 .. E6: the five hidden data-gradient epilogues ----------------
@@ -302,7 +365,9 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
           if (!(ok = wait(acc_bar, acc_par, 52 + k))) break;
           acc_par ^= 1;
           tc_fence_after();
+          mark(2);
           reopen();
+          mark(5);
           const bool res_in = (k == 2 || k == 4), gate = (k == 0 || k == 2), has_mask = k >= 1;
           const int mimg = k == 1 ? TT_A_U2 : (k == 2 ? TT_A_H1 : (k == 3 ? TT_A_U1 : TT_A_H0));
           const uint8_t* mbase = a.img + tt_img_off(l, mimg, TT_NA, tile, a.n_tiles);
@@ -370,9 +435,17 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
               }
 #pragma unroll
               for (int i = 0; i < 32; ++i) gprojr[(size_t)(sec * TT_H + c0 + i) * TT_ROWS] = gp4[i];   // (rows past R: exact zeros)
+              store_image(a.gimg + tt_img_off(l, TT_G_C0 + sec, TT_NG, tile, a.n_tiles),
+                          a.gimg + tt_img_off(l, TT_G_C0L + sec, TT_NG, tile, a.n_tiles), c0, gp4);
             } else if (k == 4) {             // relu(context_layer) backward: g[] holds the relu'd context term
+              float gc[32];
 #pragma unroll
-              for (int i = 0; i < 32; ++i) gprojr[(size_t)(c0 + i) * TT_ROWS] = g[i] > 0.f ? o[i] : 0.f;
+              for (int i = 0; i < 32; ++i) {
+                gc[i] = g[i] > 0.f ? o[i] : 0.f;
+                gprojr[(size_t)(c0 + i) * TT_ROWS] = gc[i];
+              }
+              store_image(a.gimg + tt_img_off(l, TT_G_C0, TT_NG, tile, a.n_tiles),
+                          a.gimg + tt_img_off(l, TT_G_C0L, TT_NG, tile, a.n_tiles), c0, gc);
             }
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
@@ -385,7 +458,9 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
             }
           }
           if (k == 0 || k == 2) tmem_wait_st();
+          mark(3);
           publish(a.gimg + tt_img_off(l, TT_G_V2 + k, TT_NG, tile, a.n_tiles));
+          mark(5);
         }
         if (!ok) break;
         // ---------------- E7: d x of this layer -> d output of the layer below ----------------
@@ -407,9 +482,14 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
         }
         tc_fence_before();
         bar_sync(3, 256);
+        mark(4);
       }
     }
     if (rt == 0) bulk_wait0();      // the last gradient image is in global memory before the CTA exits
+    if (prof) {
+      for (int i = 0; i < 6; ++i) a.prof[i] = pc[i];
+      a.prof[6] = clock64() - t_begin;
+    }
   } else if (warp == 8) {
     // ============================ MMA issuer ============================
     uint32_t op_par = 0, slot = 0, full_par = 0;
@@ -491,6 +571,23 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
 }
 
 // ------------------------------------------------------------------------------------------------
+// context rows [R, C] fp32 -> bf16 tile images [tiles][C/8 column groups][16 row groups][8 rows x 16 B]
+// ------------------------------------------------------------------------------------------------
+__global__ void tt_ctx_image_kernel(const float* __restrict__ ctx, int C, int64_t R, int tiles, uint8_t* __restrict__ cimg) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;      // (tile, column group, row in tile)
+  const int ncg = TT_CIMG_COLS / 8;
+  if (i >= (int64_t)tiles * ncg * TT_ROWS) return;
+  const int rr = (int)(i % TT_ROWS), cg = (int)((i / TT_ROWS) % ncg), tile = (int)(i / ((int64_t)TT_ROWS * ncg));
+  const int64_t row = (int64_t)tile * TT_ROWS + rr;
+  float v[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) v[k] = (row < R && cg * 8 + k < C) ? ctx[row * C + cg * 8 + k] : 0.f;
+  uint4 w;
+  w.x = pack_bf16(v[0], v[1]); w.y = pack_bf16(v[2], v[3]); w.z = pack_bf16(v[4], v[5]); w.w = pack_bf16(v[6], v[7]);
+  *reinterpret_cast<uint4*>(cimg + (size_t)tile * TT_CIMG + (size_t)cg * 2048 + (rr / 8) * 128 + (rr % 8) * 16) = w;
+}
+
+// ------------------------------------------------------------------------------------------------
 // the weight-gradient kernel
 // ------------------------------------------------------------------------------------------------
 struct TtWgArgs {
@@ -498,6 +595,8 @@ struct TtWgArgs {
   const uint8_t* img;      // forward images
   const uint8_t* xt;       // x-tile images
   const uint8_t* gimg;     // gradient images
+  const uint8_t* cimg;     // context images
+  int C;
   int tiles;
   int64_t R;
   const int* perm;         // [H] sorted slot -> nflows unit
@@ -510,10 +609,10 @@ constexpr int WG_THREADS = 192;       // 4 epilogue / column-sum warps, MMA issu
 constexpr int WG_STAGES = 2;
 constexpr int WG_GBYTES = 32768;      // [128 rows x 128 columns] of a gradient image
 constexpr int WG_ABYTES = 65536;      // [128 rows x 256 columns] activation image
-constexpr int WG_STAGE = WG_GBYTES + WG_ABYTES;
+constexpr int WG_STAGE = WG_GBYTES + TT_CIMG;     // sized for the widest second operand (the context image)
 constexpr int WG_OFF_BAR = WG_STAGES * WG_STAGE;
 constexpr int WG_SMEM = WG_OFF_BAR + 128;
-constexpr int WG_JOBS = 14;           // per layer
+constexpr int WG_JOBS = 20;           // per layer: final 4 | 4 hidden matrices x 2 | initial 2 | 3 context layers x 2
 
 // instruction descriptor, kind::f16: bf16 x bf16 -> fp32, BOTH operands MN-major (bits 15 / 16), dense
 __host__ __device__ constexpr uint32_t umma_idesc_bf16_mn(int M, int N) {
@@ -533,15 +632,17 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   // ---- decode the job ----
   const int l = blockIdx.x / WG_JOBS, jk = blockIdx.x % WG_JOBS;
-  const int mat = jk < 4 ? 0 : 1 + (jk - 4) / 2;       // 0 final | 1 Wb2 | 2 Wa2 | 3 Wb1 | 4 Wa1 | 5 W0
+  // 0 final | 1 Wb2 | 2 Wa2 | 3 Wb1 | 4 Wa1 | 5 W0 | 6 context_layer | 7 blocks.0.context_layer | 8 blocks.1.context_layer
+  const int mat = jk < 4 ? 0 : 1 + (jk - 4) / 2;
   const int mt = jk < 4 ? (jk & 1) : ((jk - 4) & 1);   // 128-column block of the gradient image
-  const int gwhich = jk < 2 ? TT_G_PA : (jk < 4 ? TT_G_PB : TT_G_V2 + (mat - 1));
+  const int gwhich = jk < 2 ? TT_G_PA : (jk < 4 ? TT_G_PB : (mat <= 5 ? TT_G_V2 + (mat - 1) : TT_G_C0 + (mat - 6)));
   const int awhich = mat == 0 ? TT_A_H2 : (mat == 1 ? TT_A_U2 : (mat == 2 ? TT_A_H1 : (mat == 3 ? TT_A_U1 : TT_A_H0)));
-  const int N = mat == 5 ? 16 : 256;
-  const uint32_t abytes = mat == 5 ? TT_XT : WG_ABYTES;
+  const int N = mat == 5 ? 16 : (mat >= 6 ? TT_CIMG_COLS : 256);
+  const uint32_t abytes = mat == 5 ? TT_XT : (mat >= 6 ? TT_CIMG : WG_ABYTES);
   const uint8_t* gsrc = a.gimg + tt_img_off(l, gwhich, TT_NG, 0, a.tiles) + (size_t)mt * WG_GBYTES;
-  const uint8_t* asrc = mat == 5 ? a.xt + (size_t)l * a.tiles * TT_XT : a.img + tt_img_off(l, awhich, TT_NA, 0, a.tiles);
-  const size_t astride = mat == 5 ? TT_XT : TT_IMG;
+  const uint8_t* asrc = mat == 5 ? a.xt + (size_t)l * a.tiles * TT_XT
+                                 : (mat >= 6 ? a.cimg : a.img + tt_img_off(l, awhich, TT_NA, 0, a.tiles));
+  const size_t astride = mat == 5 ? TT_XT : (mat >= 6 ? TT_CIMG : TT_IMG);
 
   if (tid == 0) {
     for (int i = 0; i < WG_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 5); }
@@ -549,7 +650,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
     *abort_s = 0;
     fence_mbar_init();
   }
-  if (warp == 4) tmem_alloc(tmem_slot, 256);
+  if (warp == 4) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -611,11 +712,18 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
         if (g.blk_lin_w[blk][j]) wrow = g.blk_lin_w[blk][j] + (size_t)wr * TT_H;
         if (g.blk_lin_b[blk][j]) bdst = g.blk_lin_b[blk][j] + wr;
         ld = TT_H;
-      } else {
+      } else if (mat == 5) {
         wr = a.perm[gm];
         if (g.initial_w) wrow = g.initial_w + (size_t)wr * s.D;
         if (g.initial_b) bdst = g.initial_b + wr;
         ld = s.D;
+      } else {
+        wr = a.perm[gm];
+        float* w = mat == 6 ? g.ctx_w : g.blk_ctx_w[mat - 7];
+        float* b = mat == 6 ? g.ctx_b : g.blk_ctx_b[mat - 7];
+        if (w) wrow = w + (size_t)wr * a.C;
+        if (b) bdst = b + wr;
+        ld = a.C;
       }
       (void)ld;
       if (bdst) *bdst += bsum;
@@ -629,7 +737,9 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
             const int n = c0 + i;
-            if (mat == 5) {
+            if (mat >= 6) {
+              if (n < a.C) wrow[n] += __uint_as_float(v[i]);          // context Linear layers are unmasked, columns unsorted
+            } else if (mat == 5) {
               if (n < s.D && rule_mask(rule, wr, n, s.D, TT_MULT) != 0.f) wrow[n] += __uint_as_float(v[i]);
             } else {
               const int wc = a.perm[n];
@@ -641,7 +751,8 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
     }
   } else if (warp == 4) {
     // ---- MMA issuer ----
-    const uint32_t idesc = umma_idesc_bf16_mn(128, N);
+    const int NH = mat >= 6 ? N / 2 : N;              // the context image is 288 columns wide: two N = 144 instructions
+    const uint32_t idesc = umma_idesc_bf16_mn(128, NH);
     const uint32_t lbo = a.mn_swap ? 2048u : 128u, sbo = a.mn_swap ? 128u : 2048u;
     uint32_t st = 0, par = 0;
     bool ok = true;
@@ -655,6 +766,10 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
           const uint64_t ad = umma_smem_desc(gb + (uint32_t)ks * 256u, lbo, sbo);
           const uint64_t bd = umma_smem_desc(ab + (uint32_t)ks * 256u, lbo, sbo);
           umma_ss(tmem, ad, bd, idesc, (t > 0 || ks > 0) ? 1u : 0u);
+          if (mat >= 6) {     // columns NH .. 2 NH - 1: NH / 8 column groups further into the image
+            const uint64_t bd2 = umma_smem_desc(ab + (uint32_t)(NH / 8) * 2048u + (uint32_t)ks * 256u, lbo, sbo);
+            umma_ss(tmem + (uint32_t)NH, ad, bd2, idesc, (t > 0 || ks > 0) ? 1u : 0u);
+          }
         }
         umma_commit(&empty[st]);
         if (t + 1 == a.tiles) umma_commit(acc_bar);
@@ -679,7 +794,301 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) tmem_dealloc(tmem, 256);
+  if (warp == 4) tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------------------------------------
+// context projection of the training rows on tcgen05 (replaces a [R, C] x [C, L*3*H] GEMM whose fp32 operands were
+// converted on the fly): out[tile][n][row] = relu | sigmoid (ctx . Wctx^T + b), split fp16 operands as in the forward.
+// One CTA per (tile, group of column blocks): the tile's context image stays in shared memory, the weight chunks stream
+// through a ring, two accumulators alternate so that the epilogue of block j runs under the MMAs of block j + 1.
+// ------------------------------------------------------------------------------------------------
+struct TtCpArgs {
+  const uint8_t* cimg16;   // [tiles][2][TT_CIMG] fp16 hi | lo context images (K-major operand layout)
+  const uint8_t* cfimg;
+  const float* bias;       // [L*3*H] sorted order
+  float* out;              // [tiles][NB*256][128]
+  int CK, NB, nb_per_cta, tiles;
+  int* err;
+};
+constexpr int CP_THREADS = 192;
+constexpr int CP_OFF_RING = 2 * TT_CIMG;
+constexpr int CP_NSLOT = 3;
+constexpr int CP_OFF_BAR = CP_OFF_RING + CP_NSLOT * TT_SLOT;
+constexpr int CP_SMEM = CP_OFF_BAR + 128;
+
+__global__ void tt_ctx_image16_kernel(const float* __restrict__ ctx, int C, int64_t R, int tiles, uint8_t* __restrict__ cimg16) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int ncg = TT_CIMG_COLS / 8;
+  if (i >= (int64_t)tiles * ncg * TT_ROWS) return;
+  const int rr = (int)(i % TT_ROWS), cg = (int)((i / TT_ROWS) % ncg), tile = (int)(i / ((int64_t)TT_ROWS * ncg));
+  const int64_t row = (int64_t)tile * TT_ROWS + rr;
+  uint32_t h[4], l[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    float a = (row < R && cg * 8 + 2 * k < C) ? ctx[row * C + cg * 8 + 2 * k] : 0.f;
+    float b = (row < R && cg * 8 + 2 * k + 1 < C) ? ctx[row * C + cg * 8 + 2 * k + 1] : 0.f;
+    a = fminf(fmaxf(a, -60000.f), 60000.f);
+    b = fminf(fmaxf(b, -60000.f), 60000.f);
+    const __half2 hh = __floats2half2_rn(a, b);
+    const float2 hf = __half22float2(hh);
+    const __half2 ll = __floats2half2_rn(a - hf.x, b - hf.y);
+    h[k] = *reinterpret_cast<const uint32_t*>(&hh);
+    l[k] = *reinterpret_cast<const uint32_t*>(&ll);
+  }
+  const size_t o = (size_t)cg * 2048 + (rr / 8) * 128 + (rr % 8) * 16;
+  *reinterpret_cast<uint4*>(cimg16 + ((size_t)tile * 2) * TT_CIMG + o) = make_uint4(h[0], h[1], h[2], h[3]);
+  *reinterpret_cast<uint4*>(cimg16 + ((size_t)tile * 2 + 1) * TT_CIMG + o) = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
+__global__ void __launch_bounds__(CP_THREADS, 1) tt_ctxproj_kernel(const TtCpArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* sA = smem;                       // hi image | lo image
+  uint8_t* ring = smem + CP_OFF_RING;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + CP_OFF_BAR);
+  uint64_t* full = bars;                    // [NSLOT]
+  uint64_t* empty = bars + CP_NSLOT;        // [NSLOT]
+  uint64_t* a_bar = bars + 2 * CP_NSLOT;    // context images landed
+  uint64_t* acc_full = a_bar + 1;           // [2] accumulator complete
+  uint64_t* acc_free = a_bar + 3;           // [2] accumulator drained by the epilogue (4 warp arrivals)
+  volatile int* abort_s = reinterpret_cast<volatile int*>(a_bar + 5);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(a_bar + 6);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int tile = blockIdx.x;
+  const int nb0 = blockIdx.y * a.nb_per_cta;
+  const int nb1 = min(a.NB, nb0 + a.nb_per_cta);
+  if (tid == 0) {
+    for (int i = 0; i < CP_NSLOT; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(a_bar, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_free[i], 4); }
+    *abort_s = 0;
+    fence_mbar_init();
+  }
+  if (warp == 4) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  auto wait = [&](uint64_t* bar, uint32_t parity, int code) -> bool {
+    for (uint32_t i = 0; i < (1u << 22); ++i) {
+      if (mbar_try_wait(bar, parity)) return true;
+      if ((i & 255) == 255 && *abort_s) return false;
+    }
+    *abort_s = 1;
+    raise_flag(a.err, code);
+    return false;
+  };
+  if (warp < 4) {
+    // ---- epilogue: thread = row of the tile ----
+    const int r = warp * 32 + lane;
+    const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16);
+    uint32_t par[2] = {0, 0};
+    bool ok = true;
+    for (int nb = nb0; nb < nb1 && ok; ++nb) {
+      const int ab = (nb - nb0) & 1;
+      if (!(ok = wait(&acc_full[ab], par[ab], 80))) break;
+      par[ab] ^= 1;
+      tc_fence_after();
+      const int sec = nb % 3;
+      float* dst = a.out + ((size_t)tile * a.NB * 256 + (size_t)nb * 256) * TT_ROWS + r;
+      const float* bias = a.bias + (size_t)nb * 256;
+#pragma unroll 1
+      for (int c0 = 0; c0 < 256; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tl + ab * 256 + c0, v);
+        tmem_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const float x = fmaf(__uint_as_float(v[i]), 1.f / 16.f, __ldg(bias + c0 + i));
+          dst[(size_t)(c0 + i) * TT_ROWS] = sec == 0 ? fmaxf(x, 0.f) : 1.f / (1.f + expf(-x));
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_free[ab]);
+    }
+  } else if (warp == 4) {
+    // ---- MMA issuer ----
+    const uint32_t idesc = umma_idesc_bf16(TT_ROWS, 256) & ~((1u << 7) | (1u << 10));     // fp16 operands
+    const uint32_t aHi = smem_u32(sA), aLo = aHi + TT_CIMG, aRing = smem_u32(ring);
+    uint32_t slot = 0, full_par = 0, free_par[2] = {1, 1};
+    bool ok = wait(a_bar, 0, 81);
+    tc_fence_after();
+    for (int nb = nb0; nb < nb1 && ok; ++nb) {
+      const int ab = (nb - nb0) & 1;
+      if (!(ok = wait(&acc_free[ab], free_par[ab], 82))) break;
+      free_par[ab] ^= 1;
+      tc_fence_after();
+      for (int kc = 0; kc < a.CK && ok; ++kc) {
+        if (!(ok = wait(&full[slot], full_par, 83))) break;
+        tc_fence_after();
+        const uint32_t bbase = aRing + slot * TT_SLOT;
+        if (elect_one_sync()) {
+          const uint64_t bh = umma_smem_desc(bbase, 256 * 16, 128), bl = umma_smem_desc(bbase + 8192u, 256 * 16, 128);
+          const uint64_t ah = umma_smem_desc(aHi + (uint32_t)kc * 4096u, 2048, 128);
+          const uint64_t al = umma_smem_desc(aLo + (uint32_t)kc * 4096u, 2048, 128);
+          const uint32_t acc = tmem + (uint32_t)ab * 256u;
+          umma_ss(acc, ah, bh, idesc, kc > 0 ? 1u : 0u);
+          umma_ss(acc, al, bh, idesc, 1u);
+          umma_ss(acc, ah, bl, idesc, 1u);
+          umma_commit(&empty[slot]);
+          if (kc + 1 == a.CK) umma_commit(&acc_full[ab]);
+        }
+        __syncwarp();
+        if (++slot == CP_NSLOT) { slot = 0; full_par ^= 1; }
+      }
+    }
+  } else {
+    // ---- loader ----
+    if (elect_one_sync()) {
+      mbar_arrive_expect_tx(a_bar, 2 * TT_CIMG);
+      bulk_g2s(sA, a.cimg16 + (size_t)tile * 2 * TT_CIMG, 2 * TT_CIMG, a_bar);
+    }
+    __syncwarp();
+    uint32_t slot = 0, empty_par = 1;
+    bool ok = true;
+    for (int nb = nb0; nb < nb1 && ok; ++nb) {
+      const uint8_t* src = a.cfimg + (size_t)nb * a.CK * TT_SLOT;
+      for (int kc = 0; kc < a.CK; ++kc) {
+        if (!(ok = wait(&empty[slot], empty_par, 84))) break;
+        if (elect_one_sync()) {
+          mbar_arrive_expect_tx(&full[slot], TT_SLOT);
+          bulk_g2s(ring + (size_t)slot * TT_SLOT, src + (size_t)kc * TT_SLOT, TT_SLOT, &full[slot]);
+        }
+        __syncwarp();
+        if (++slot == CP_NSLOT) { slot = 0; empty_par ^= 1; }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------------------------------------
+// d ctx [R, C] = sum over (layer, context Linear) of G [R, 256] . W [256, C] on tcgen05: the gradient images (bf16
+// hi / lo, written by the backward chain kernel) are the A operand, chunk by chunk; the transposed weight chunks stream
+// beside them through one ring.  One CTA per (tile, slice of the L*3 images); slices accumulate atomically.
+// ------------------------------------------------------------------------------------------------
+struct TtDcArgs {
+  const uint8_t* gimg;     // gradient images
+  const uint8_t* cbimg;
+  float* gctx;             // [R, C], zero-filled by the caller
+  int L, C, tiles, imgs_per_cta;
+  int64_t R;
+  int* err;
+};
+constexpr int DC_THREADS = 192;
+constexpr int DC_STAGE = 8192 + TT_CB_CHUNK;        // A hi 4 KB | A lo 4 KB | B 18 KB
+constexpr int DC_NSTAGE = 8;
+constexpr int DC_OFF_BAR = DC_NSTAGE * DC_STAGE;
+constexpr int DC_SMEM = DC_OFF_BAR + 256;
+
+__global__ void __launch_bounds__(DC_THREADS, 1) tt_dctx_kernel(const TtDcArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + DC_OFF_BAR);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + DC_NSTAGE;
+  uint64_t* acc_bar = bars + 2 * DC_NSTAGE;
+  volatile int* abort_s = reinterpret_cast<volatile int*>(acc_bar + 1);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 2);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int tile = blockIdx.x;
+  const int i0 = blockIdx.y * a.imgs_per_cta, i1 = min(a.L * 3, i0 + a.imgs_per_cta);
+  if (tid == 0) {
+    for (int i = 0; i < DC_NSTAGE; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(acc_bar, 1);
+    *abort_s = 0;
+    fence_mbar_init();
+  }
+  if (warp == 4) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  auto wait = [&](uint64_t* bar, uint32_t parity, int code) -> bool {
+    for (uint32_t i = 0; i < (1u << 22); ++i) {
+      if (mbar_try_wait(bar, parity)) return true;
+      if ((i & 255) == 255 && *abort_s) return false;
+    }
+    *abort_s = 1;
+    raise_flag(a.err, code);
+    return false;
+  };
+  constexpr int NH = TT_CIMG_COLS / 2;      // two N = 144 instructions per chunk
+  if (warp < 4) {
+    if (i0 < i1 && wait(acc_bar, 0, 90)) {
+      tc_fence_after();
+      const int r = warp * 32 + lane;
+      const int64_t row = (int64_t)tile * TT_ROWS + r;
+      const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16);
+      for (int c0 = 0; c0 < TT_CIMG_COLS; c0 += 16) {
+        uint32_t v[16];
+        tmem_ld16(tl + c0, v);
+        tmem_wait_ld();
+        if (row < a.R) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (c0 + i < a.C) atomicAdd(a.gctx + row * a.C + c0 + i, __uint_as_float(v[i]));
+        }
+      }
+    }
+  } else if (warp == 4) {
+    const uint32_t idesc = umma_idesc_bf16(TT_ROWS, NH);
+    uint32_t st = 0, par = 0;
+    bool ok = true;
+    for (int im = i0; im < i1 && ok; ++im) {
+      for (int kc = 0; kc < 16 && ok; ++kc) {
+        if (!(ok = wait(&full[st], par, 91))) break;
+        tc_fence_after();
+        const uint32_t base = smem_u32(smem + st * DC_STAGE);
+        if (elect_one_sync()) {
+          const uint64_t ah = umma_smem_desc(base, 2048, 128), al = umma_smem_desc(base + 4096u, 2048, 128);
+          const uint32_t bb = base + 8192u;
+          const uint32_t first = (im == i0 && kc == 0) ? 0u : 1u;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const uint64_t bh = umma_smem_desc(bb + (uint32_t)h * (NH / 8) * 128u, TT_CIMG_COLS * 16, 128);
+            const uint64_t bl = umma_smem_desc(bb + (uint32_t)TT_CIMG_COLS * 32u + (uint32_t)h * (NH / 8) * 128u, TT_CIMG_COLS * 16, 128);
+            const uint32_t acc = tmem + (uint32_t)h * NH;
+            umma_ss(acc, ah, bh, idesc, first);
+            umma_ss(acc, al, bh, idesc, 1u);
+            umma_ss(acc, ah, bl, idesc, 1u);
+          }
+          umma_commit(&empty[st]);
+          if (im + 1 == i1 && kc == 15) umma_commit(acc_bar);
+        }
+        __syncwarp();
+        if (++st == DC_NSTAGE) { st = 0; par ^= 1; }
+      }
+    }
+  } else {
+    uint32_t st = 0, par = 1;
+    bool ok = true;
+    for (int im = i0; im < i1 && ok; ++im) {
+      const int l = im / 3, sec = im % 3;
+      const uint8_t* ghi = a.gimg + tt_img_off(l, TT_G_C0 + sec, TT_NG, tile, a.tiles);
+      const uint8_t* glo = a.gimg + tt_img_off(l, TT_G_C0L + sec, TT_NG, tile, a.tiles);
+      const uint8_t* wsrc = a.cbimg + (size_t)im * 16 * TT_CB_CHUNK;
+      for (int kc = 0; kc < 16; ++kc) {
+        if (!(ok = wait(&empty[st], par, 92))) break;
+        if (elect_one_sync()) {
+          uint8_t* d = smem + st * DC_STAGE;
+          mbar_arrive_expect_tx(&full[st], DC_STAGE);
+          bulk_g2s(d, ghi + (size_t)kc * 4096, 4096, &full[st]);
+          bulk_g2s(d + 4096, glo + (size_t)kc * 4096, 4096, &full[st]);
+          bulk_g2s(d + 8192, wsrc + (size_t)kc * TT_CB_CHUNK, TT_CB_CHUNK, &full[st]);
+        }
+        __syncwarp();
+        if (++st == DC_NSTAGE) { st = 0; par ^= 1; }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) tmem_dealloc(tmem, 512);
 }
 
 }  // namespace pf
@@ -710,10 +1119,16 @@ pf_status pf_tt_pack(pf_flow* f, cudaStream_t st) {
   TtState* t = reinterpret_cast<TtState*>(f->train);
   if (!t) {
     t = new TtState();
+    memset(t, 0, sizeof(*t));
     t->s = s;
-    t->wimg = nullptr;
+    t->C = f->C;
+    t->CK = (f->C + 15) / 16;
     cudaError_t e = cudaMalloc(&t->wimg, (size_t)s.L * s.layer_bytes);
+    if (e == cudaSuccess) e = cudaMalloc(&t->cfimg, (size_t)s.L * 3 * t->CK * TT_SLOT);
+    if (e == cudaSuccess) e = cudaMalloc(&t->cbimg, (size_t)s.L * 3 * 16 * TT_CB_CHUNK);
     if (e != cudaSuccess) {
+      if (t->wimg) cudaFree(t->wimg);
+      if (t->cfimg) cudaFree(t->cfimg);
       delete t;
       return cuda_fail(e, "backward weight image allocation", __FILE__, __LINE__);
     }
@@ -722,6 +1137,72 @@ pf_status pf_tt_pack(pf_flow* f, cudaStream_t st) {
   dim3 grid(s.NA / 16 + s.NBn / 16 + 65, s.L);
   tt_pack_kernel<<<grid, 256, 0, st>>>(s, t->wimg, f->WfT, f->WaT, f->WbT, f->W0T);
   PF_LAUNCH_CHECK(f);
+  if (f->C <= TT_CIMG_COLS) {
+    dim3 g2(t->CK + 16, s.L * 3);
+    tt_pack_ctx_kernel<<<g2, 256, 0, st>>>(f->Wctx, f->C, t->CK, t->cfimg, t->cbimg);
+    PF_LAUNCH_CHECK(f);
+  }
+  return PF_OK;
+}
+
+// context projection of R training rows into the tile-transposed layout; `scratch` holds the fp16 context images
+pf_status pf_tt_ctxproj(pf_flow* f, cudaStream_t st, const float* ctx, int64_t R, float* out, uint8_t* scratch) {
+  TtState* t = reinterpret_cast<TtState*>(f->train);
+  if (!t || f->C > TT_CIMG_COLS) return PF_ERR_UNSUPPORTED;
+  static bool attr_done[64] = {};
+  const int dev = f->desc.device;
+  if (dev < 64 && !attr_done[dev]) {
+    PF_CUDA(cudaFuncSetAttribute(tt_ctxproj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CP_SMEM));
+    PF_CUDA(cudaFuncSetAttribute(tt_dctx_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DC_SMEM));
+    attr_done[dev] = true;
+  }
+  const int tiles = (int)((R + TT_ROWS - 1) / TT_ROWS);
+  {
+    const int64_t n = (int64_t)tiles * (TT_CIMG_COLS / 8) * TT_ROWS;
+    tt_ctx_image16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(ctx, f->C, R, tiles, scratch);
+    PF_LAUNCH_CHECK(f);
+  }
+  TtCpArgs a;
+  memset(&a, 0, sizeof(a));
+  a.cimg16 = scratch;
+  a.cfimg = t->cfimg;
+  a.bias = f->bctx;
+  a.out = out;
+  a.CK = t->CK;
+  a.NB = f->L * 3;
+  a.tiles = tiles;
+  // column-block groups per tile: enough CTAs for ~2 waves of the SMs, never more groups than blocks
+  int groups = (2 * f->sm_count + tiles - 1) / tiles;
+  if (groups < 1) groups = 1;
+  if (groups > a.NB) groups = a.NB;
+  a.nb_per_cta = (a.NB + groups - 1) / groups;
+  groups = (a.NB + a.nb_per_cta - 1) / a.nb_per_cta;
+  a.err = f->tg_err;
+  tt_ctxproj_kernel<<<dim3(tiles, groups), CP_THREADS, CP_SMEM, st>>>(a);
+  PF_LAUNCH_CHECK(f);
+  return PF_OK;
+}
+size_t pf_tt_ctxproj_scratch(int64_t R) { return (size_t)((R + TT_ROWS - 1) / TT_ROWS) * 2 * TT_CIMG; }
+
+pf_status pf_tt_dctx(pf_flow* f, cudaStream_t st, const TtWork& ws, int64_t R, float* gctx) {
+  TtState* t = reinterpret_cast<TtState*>(f->train);
+  if (!t || f->C > TT_CIMG_COLS) return PF_ERR_UNSUPPORTED;
+  TtDcArgs a;
+  memset(&a, 0, sizeof(a));
+  a.gimg = ws.gimg;
+  a.cbimg = t->cbimg;
+  a.gctx = gctx;
+  a.L = f->L; a.C = f->C;
+  a.tiles = (int)((R + TT_ROWS - 1) / TT_ROWS);
+  a.R = R;
+  int slices = (f->sm_count + a.tiles - 1) / a.tiles;      // about one CTA per SM
+  if (slices < 1) slices = 1;
+  if (slices > f->L * 3) slices = f->L * 3;
+  a.imgs_per_cta = (f->L * 3 + slices - 1) / slices;
+  slices = (f->L * 3 + a.imgs_per_cta - 1) / a.imgs_per_cta;
+  a.err = f->tg_err;
+  tt_dctx_kernel<<<dim3(a.tiles, slices), DC_THREADS, DC_SMEM, st>>>(a);
+  PF_LAUNCH_CHECK(f);
   return PF_OK;
 }
 
@@ -729,6 +1210,8 @@ void pf_tt_destroy(pf_flow* f) {
   TtState* t = reinterpret_cast<TtState*>(f->train);
   if (!t) return;
   cudaFree(t->wimg);
+  cudaFree(t->cfimg);
+  cudaFree(t->cbimg);
   delete t;
   f->train = nullptr;
 }
@@ -759,22 +1242,42 @@ pf_status pf_tt_backward(pf_flow* f, cudaStream_t st, const TtSaved& sv, const T
   a.n_tiles = (int)((R + TT_ROWS - 1) / TT_ROWS);
   a.tail = f->desc.tail_bound;
   a.err = f->tg_err;
+  static long long* d_prof = nullptr;
+  {
+    const char* pr = getenv("PF_TC_PROF");
+    if (pr && pr[0] == '1' && !d_prof && cudaMalloc(&d_prof, 8 * sizeof(long long)) != cudaSuccess) d_prof = nullptr;
+  }
+  a.prof = d_prof;
   const int grid = a.n_tiles < f->sm_count ? a.n_tiles : f->sm_count;
   tt_backward_kernel<<<grid, TT_THREADS, TT_SMEM, st>>>(a);
   PF_LAUNCH_CHECK(f);
+  if (d_prof) {
+    long long h[8];
+    PF_CUDA(cudaStreamSynchronize(st));
+    PF_CUDA(cudaMemcpy(h, d_prof, sizeof(h), cudaMemcpyDeviceToHost));
+    fprintf(stderr, "[pf_tt prof] backward CTA0: total %lld cycles: spline VJP %lld | wait group A %lld | hidden wait %lld "
+            "compute %lld | d x %lld | publish/reopen %lld\n", h[6], h[0], h[1], h[2], h[3], h[4], h[5]);
+  }
   return PF_OK;
 }
 
-pf_status pf_tt_wgrad(pf_flow* f, cudaStream_t st, const TtSaved& sv, const TtWork& ws, int64_t R,
+pf_status pf_tt_wgrad(pf_flow* f, cudaStream_t st, const TtSaved& sv, const TtWork& ws, int64_t R, const float* ctx,
                       const pf_layer_grads* grads) {
   TtState* t = reinterpret_cast<TtState*>(f->train);
   if (!t) return PF_ERR_NOT_PACKED;
   if (!grads) return PF_OK;
+  if (f->C > TT_CIMG_COLS || !ctx) return PF_ERR_UNSUPPORTED;
   TtWgArgs a;
   memset(&a, 0, sizeof(a));
   a.s = t->s;
-  a.img = sv.img; a.xt = sv.xt; a.gimg = ws.gimg;
+  a.img = sv.img; a.xt = sv.xt; a.gimg = ws.gimg; a.cimg = ws.cimg;
+  a.C = f->C;
   a.tiles = (int)((R + TT_ROWS - 1) / TT_ROWS);
+  {
+    const int64_t n = (int64_t)a.tiles * (TT_CIMG_COLS / 8) * TT_ROWS;
+    tt_ctx_image_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(ctx, f->C, R, a.tiles, ws.cimg);
+    PF_LAUNCH_CHECK(f);
+  }
   a.R = R;
   a.perm = f->d_perm;
   const char* sw = getenv("PF_MN_SWAP");

@@ -25,7 +25,11 @@ constexpr int TT_MAX_L = 32;
 enum { TT_A_H0 = 0, TT_A_U1 = 1, TT_A_H1 = 2, TT_A_U2 = 3, TT_A_H2 = 4, TT_A_V1 = 5, TT_A_V1L = 6, TT_A_V2 = 7, TT_A_V2L = 8,
        TT_NA = 9 };
 // gradient images (written by tt_backward_kernel): d params of dims 1..ga | ga+1.. , then the five hidden gradients
-enum { TT_G_PA = 0, TT_G_PB = 1, TT_G_V2 = 2, TT_G_U2 = 3, TT_G_V1 = 4, TT_G_U1 = 5, TT_G_H0 = 6, TT_NG = 7 };
+// ... and the three context-layer gradients (pre-activation of relu(context_layer), gate 1, gate 2), hi and lo halves
+enum { TT_G_PA = 0, TT_G_PB = 1, TT_G_V2 = 2, TT_G_U2 = 3, TT_G_V1 = 4, TT_G_U1 = 5, TT_G_H0 = 6,
+       TT_G_C0 = 7, TT_G_G1 = 8, TT_G_G2 = 9, TT_G_C0L = 10, TT_G_G1L = 11, TT_G_G2L = 12, TT_NG = 13 };
+constexpr int TT_CIMG_COLS = 288;                 // context image: [128 x C] bf16 in the tile-image layout (C <= 288)
+constexpr int TT_CIMG = TT_CIMG_COLS / 8 * 2048;  // 73 728 bytes
 
 __host__ __device__ inline size_t tt_img_off(int l, int which, int nwhich, int tile, int tiles) {
   return (((size_t)l * nwhich + which) * (size_t)tiles + tile) * TT_IMG;
@@ -46,6 +50,7 @@ struct TtSaved {
   float* P;       // [L][tiles][PLD][128] spline parameters, tile-transposed
   uint8_t* img;   // [L][TT_NA][tiles][TT_IMG]
   uint8_t* xt;    // [L][tiles][TT_XT]
+  uint8_t* c16;   // [tiles][2][TT_CIMG]  fp16 hi | lo images of the context rows (operand of the projection kernel)
   size_t bytes;
   TtSaved(const pf_flow* f, void* base, int64_t R) {
     const size_t tiles = (size_t)((R + TT_ROWS - 1) / TT_ROWS);
@@ -57,6 +62,7 @@ struct TtSaved {
     P = reinterpret_cast<float*>(take((size_t)f->L * tiles * TT_ROWS * f->PLD * 4));
     img = reinterpret_cast<uint8_t*>(take((size_t)f->L * TT_NA * tiles * TT_IMG));
     xt = reinterpret_cast<uint8_t*>(take((size_t)f->L * tiles * TT_XT));
+    c16 = reinterpret_cast<uint8_t*>(take(tiles * 2 * (size_t)TT_CIMG));
     bytes = o;
   }
 };
@@ -65,6 +71,7 @@ struct TtSaved {
 struct TtWork {
   uint8_t* gimg;   // [L][TT_NG][tiles][TT_IMG]  bf16 gradient images
   float* gproj;    // [tiles][L*3*H][128]  d loss / d (pre-activation of the context layers), tile-transposed
+  uint8_t* cimg;   // [tiles][TT_CIMG]  bf16 image of the context rows (weight-gradient operand of the context layers)
   size_t bytes;
   TtWork(const pf_flow* f, void* base, int64_t R) {
     const size_t tiles = (size_t)((R + TT_ROWS - 1) / TT_ROWS);
@@ -73,6 +80,7 @@ struct TtWork {
     auto take = [&](size_t b) { char* r = p ? p + o : nullptr; o += tt_align(b); return r; };
     gimg = reinterpret_cast<uint8_t*>(take((size_t)f->L * TT_NG * tiles * TT_IMG));
     gproj = reinterpret_cast<float*>(take(tiles * TT_ROWS * (size_t)f->L * 3 * f->H * 4));
+    cimg = reinterpret_cast<uint8_t*>(take(tiles * (size_t)TT_CIMG));
     bytes = o;
   }
 };
@@ -84,4 +92,7 @@ bool pf_tt_supported(const pf_flow* f);
 pf_status pf_tt_backward(pf_flow* f, cudaStream_t st, const pf::TtSaved& sv, const pf::TtWork& ws, int64_t R, const float* gz,
                          const float* glogdet, float* gx, const pf_layer_grads* grads);
 pf_status pf_tt_wgrad(pf_flow* f, cudaStream_t st, const pf::TtSaved& sv, const pf::TtWork& ws, int64_t R,
-                      const pf_layer_grads* grads);
+                      const float* ctx, const pf_layer_grads* grads);
+pf_status pf_tt_ctxproj(pf_flow* f, cudaStream_t st, const float* ctx, int64_t R, float* out, uint8_t* scratch);
+size_t pf_tt_ctxproj_scratch(int64_t R);
+pf_status pf_tt_dctx(pf_flow* f, cudaStream_t st, const pf::TtWork& ws, int64_t R, float* gctx);

@@ -270,8 +270,9 @@ def test_three_adamw_steps_then_every_direction_matches_the_oracle(tier, monkeyp
             zg, fg = ma.flow.forward(xo.cuda(), probe_c.cuda())
         if tier == "fp32":
             for a, b, nm in ((xg, xo, "x"), (lg, lo, "inverse logdet"), (zg, zo, "z"), (fg, fo, "forward logdet")):
-                e = float(((a.cpu() - b).abs() / b.abs().clamp_min(1.0)).max())
-                assert e <= 5e-4, (it, nm, e)     # single float32 entries differ by more than 1e-4 (knots); not arbitrated here
+                err = (a.cpu() - b).abs() / b.abs().clamp_min(1.0)
+                # single float32 entries differ by more than 1e-4 (rows next to a knot); not float64-arbitrated here
+                assert float(err.median()) <= 1e-5 and float(err.max()) <= 2e-3, (it, nm, float(err.median()), float(err.max()))
         else:
             e = float(((xg.cpu() - xo).abs() / xo.abs().clamp_min(1.0)).median())
             assert e <= 2e-2, (it, e)
@@ -283,7 +284,7 @@ def test_three_adamw_steps_then_every_direction_matches_the_oracle(tier, monkeyp
     with torch.no_grad():
         ma.flow.layer_weights()[0].add_(0.0)
     ma.flow.handle()
-    assert 1 <= fh.launches - l0 <= 4, fh.launches - l0
+    assert 1 <= fh.launches - l0 <= 6, fh.launches - l0    # job-table kernel + sampler / dense / backward / context images
 
 
 # ------------------------------------------------------------------------------------------------
