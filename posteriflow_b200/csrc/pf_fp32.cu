@@ -339,7 +339,7 @@ struct SavedLayout {
 // The fused training step (pf_train.cuh) serves the dense-context form (one context row per flow row: what batch_nll /
 // LeanNPE.nll pass) of handles whose shape the dense tensor-core kernels cover.
 static inline bool fused_train(const pf_flow* f, const int64_t* row2ctx, int64_t n_per_ctx) {
-  return f->train_fused && f->train && f->dense && !row2ctx && n_per_ctx == 1;
+  return f->train_fused && f->train && f->dense && !row2ctx && n_per_ctx == 1 && f->C <= TT_CIMG_COLS;
 }
 
 extern "C" size_t pf_flow_saved_bytes(const pf_flow* f, int64_t R, int64_t E) {
@@ -816,55 +816,6 @@ struct EpiWgradCtx {  // rows = [3][H] sections of the three context Linear laye
     if (d) atomicAdd(d + (int64_t)perm[n1 % H] * C + n2, acc);
   }
 };
-// all layers at once: row n1 of gproj^T . ctx belongs to layer n1 / 3H, context Linear (n1 / H) % 3
-struct EpiWgradCtxAll {
-  float* dst[TT_MAX_L * 3]; int C; int H; const int* perm;
-  __device__ __forceinline__ void operator()(int n1, int n2, float acc) const {
-    float* d = dst[n1 / H];
-    if (d) atomicAdd(d + (int64_t)perm[n1 % H] * C + n2, acc);
-  }
-};
-struct ColMapAll {
-  const int* perm; int H;
-  float* dst[TT_MAX_L * 3];
-  __device__ __forceinline__ float* operator()(int c) const {
-    float* d = dst[c / H];
-    return d ? d + perm[c % H] : nullptr;
-  }
-};
-// column sums of a tile-transposed [tiles][ncols][128] array: one warp per column, float4 per lane and tile
-__global__ void __launch_bounds__(256) colsum_tiled_kernel(const float* __restrict__ src, int ncols, int tiles, ColMapAll map) {
-  const int c = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-  if (c >= ncols) return;
-  float s = 0.f;
-  for (int t = 0; t < tiles; ++t) {
-    const float4 v = __ldg(reinterpret_cast<const float4*>(src + ((size_t)t * ncols + c) * TT_ROWS) + lane);
-    s += (v.x + v.y) + (v.z + v.w);
-  }
-#pragma unroll
-  for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-  if (lane == 0) {
-    float* d = map(c);
-    if (d) atomicAdd(d, s);
-  }
-}
-// element (flow row m, column n) of a tile-transposed array; as the TN source's (contraction m, output n) loader ...
-struct LoadTileTk {   // ... with the flow rows as the contraction index: la(m = row, n = column)
-  const float* p; int ncols;
-  __device__ __forceinline__ float operator()(int m, int n) const {
-    return p[((int64_t)(m / TT_ROWS) * ncols + n) * TT_ROWS + (m % TT_ROWS)];
-  }
-};
-struct LoadTileT {    // ... with the columns as the contraction index: la(m = column, n = row) -- lanes along the rows
-  const float* p; int ncols;
-  __device__ __forceinline__ float operator()(int m, int n) const {
-    return p[((int64_t)(n / TT_ROWS) * ncols + m) * TT_ROWS + (n % TT_ROWS)];
-  }
-};
-struct EpiAccum {     // out[m, n] += acc   (the tensor-core TN kernel splits the contraction over CTAs: atomic)
-  float* out; int ld;
-  __device__ __forceinline__ void operator()(int m, int n, float acc) const { atomicAdd(out + (int64_t)m * ld + n, acc); }
-};
 struct LoadRev {  // X[m, D-1-n]
   const float* p; int D;
   __device__ __forceinline__ float operator()(int m, int n) const { return p[(int64_t)m * D + (D - 1 - n)]; }
@@ -937,14 +888,7 @@ extern "C" pf_status pf_flow_backward(pf_flow* f, const void* saved, const float
     if (!workspace || ws.bytes > workspace_bytes) return PF_ERR_WORKSPACE;
     PF_TRY(pf_tt_backward(f, st, sv, ws, R, gz, glogdet, gx, grads));
     PF_TRY(pf_tt_wgrad(f, st, sv, ws, R, ctx, grads));
-    const int NL = L * 3 * H;
-    if (gctx) {    // d ctx [R, C] = gproj [R, L*3H] . Wctx [L*3H, C]
-      const char* ct = getenv("PF_CTX_TC");
-      if (C <= TT_CIMG_COLS && !(ct && ct[0] == '0'))
-        PF_TRY(pf_tt_dctx(f, st, ws, R, gctx));                      // tcgen05 kernel over the gradient images
-      else        // generic GEMM: contraction over the L*3H columns of the tile-transposed fp32 gproj, lanes along the rows
-        PF_TRY((gemm_tn(f, st, LoadTileT{ws.gproj, NL}, LoadPlain{f->Wctx, C}, NL, R, C, EpiAccum{gctx, C})));
-    }
+    if (gctx) PF_TRY(pf_tt_dctx(f, st, ws, R, gctx));   // d ctx [R, C] = (gate / context gradients) . Wctx, all layers
     return train_tc_check(f, st, "pf_flow_backward (fused)");
   }
   SavedLayout sv(f, const_cast<void*>(saved), R, E);

@@ -76,6 +76,12 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, u
                : "memory");
 }
 
+// asynchronous prefetch of a contiguous global range into L2 (no shared-memory destination, no completion tracking):
+// turns the HBM latency of data a kernel will read a stage later into an L2 hit (bytes % 16 == 0)
+__device__ __forceinline__ void bulk_prefetch_l2(const void* gmem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem_src), "r"(bytes) : "memory");
+}
+
 // ---- tensor memory ------------------------------------------------------------------------------
 // one full warp; writes the base TMEM address to *smem_dst
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t ncols) {

@@ -345,6 +345,131 @@ __device__ __forceinline__ float rqs_inverse_fast(const float* q, float y, float
   lad = -fx_log(dnum * fx_rcp(den * den));
   return fmaf(root, wk, xk);
 }
+
+// Reverse mode of the forward map with the hardware ex2 / lg2 / rcp approximations (~2^-22 relative): the variant the
+// fused backward kernel of the tensor-core tiers runs (its operands are split-bf16, ~1e-5; gradient tolerance 2e-3).
+// Same formulas, same argument meaning as rqs_forward_backward above.
+template <int NB, class P, class GOut>
+__device__ __forceinline__ float rqs_forward_backward_fast(const P& prm, float x, float B, float gy, float gl, const GOut& G) {
+  if (!(x >= -B && x <= B)) {
+#pragma unroll
+    for (int i = 0; i < 3 * NB - 1; ++i) G(i, 0.f);
+    return gy;
+  }
+  float pw[NB], ph[NB];
+  float mw = -INFINITY, mh = -INFINITY;
+#pragma unroll
+  for (int i = 0; i < NB; ++i) {
+    pw[i] = prm(i);
+    ph[i] = prm(NB + i);
+    mw = fmaxf(mw, pw[i]);
+    mh = fmaxf(mh, ph[i]);
+  }
+  float sw = 0.f, sh = 0.f;
+#pragma unroll
+  for (int i = 0; i < NB; ++i) {
+    pw[i] = fx_exp(pw[i] - mw);
+    ph[i] = fx_exp(ph[i] - mh);
+    sw += pw[i];
+    sh += ph[i];
+  }
+  const float scale = 1.f - kMinBin * NB;
+  const float rw = fx_rcp(sw), rh = fx_rcp(sh);
+  // knots along x (search axis) and the bin
+  int k = 0;
+  float xk = -B, wk = 0.f, yk = -B, hk = 0.f;
+  {
+    float cum = 0.f, prev = -B;
+#pragma unroll
+    for (int i = 0; i < NB; ++i) {
+      pw[i] *= rw;  // softmax probabilities from here on
+      cum += kMinBin + scale * pw[i];
+      float next = (i == NB - 1) ? B : (2.f * B) * cum + (-B);
+      if (i == 0 || x >= prev) { k = i; xk = prev; wk = next - prev; }
+      prev = next;
+    }
+    cum = 0.f; prev = -B;
+#pragma unroll
+    for (int i = 0; i < NB; ++i) {
+      ph[i] *= rh;
+      cum += kMinBin + scale * ph[i];
+      float next = (i == NB - 1) ? B : (2.f * B) * cum + (-B);
+      if (i == k) { yk = prev; hk = next - prev; }
+      prev = next;
+    }
+  }
+  float u0 = kEdgeLogit, u1 = kEdgeLogit;
+#pragma unroll
+  for (int i = 0; i < NB - 1; ++i) {
+    float u = prm(2 * NB + i);
+    if (i + 1 == k) u0 = u;
+    if (i == k) u1 = u;
+  }
+  const float dk = kMinDeriv + (u0 > 20.f ? u0 : fx_log(1.f + fx_exp(u0))), dk1 = kMinDeriv + (u1 > 20.f ? u1 : fx_log(1.f + fx_exp(u1)));
+
+  // forward intermediates
+  const float rwk = fx_rcp(wk);
+  const float s = hk * rwk;
+  const float th = (x - xk) * rwk;
+  const float omt = 1.f - th;
+  const float tt = th * omt;
+  const float inner = s * th * th + dk * tt;
+  const float num = hk * inner;
+  const float cf = dk + dk1 - 2.f * s;
+  const float den = s + cf * tt;
+  const float Q = dk1 * th * th + 2.f * s * tt + dk * omt * omt;
+  const float dnum = s * s * Q;
+  // reverse
+  const float rden = fx_rcp(den);
+  const float g_num = gy * rden;
+  const float g_den = -gy * num * rden * rden - 2.f * gl * rden;
+  const float g_dnum = gl * fx_rcp(dnum);
+  const float g_Q = g_dnum * s * s;
+  float g_s = g_dnum * 2.f * s * Q + g_Q * 2.f * tt + g_den * (1.f - 2.f * tt) + g_num * hk * th * th;
+  float g_dk = g_Q * omt * omt + g_den * tt + g_num * hk * tt;
+  float g_dk1 = g_Q * th * th + g_den * tt;
+  float g_tt = g_Q * 2.f * s + g_den * cf + g_num * hk * dk;
+  float g_th = g_Q * (2.f * dk1 * th - 2.f * dk * omt) + g_num * hk * s * 2.f * th + g_tt * (1.f - 2.f * th);
+  float g_h = g_num * inner + g_s * rwk;
+  float g_w = -g_th * th * rwk - g_s * s * rwk;
+  const float gx = g_th * rwk;
+  const float g_xk = -g_th * rwk;
+  const float g_yk = gy;
+  // knots -> cumulative sums.  cw_j = 2B * sum_{i<j} w_i - B for 0 < j < NB (ends pinned).
+  // bin k uses knots k (left) and k+1 (right): grad wrt knot k: g_xk - g_w ; knot k+1: g_w.
+  const float Gk = (k > 0) ? (g_xk - g_w) : 0.f;
+  const float Gk1 = (k + 1 < NB) ? g_w : 0.f;
+  const float Hk = (k > 0) ? (g_yk - g_h) : 0.f;
+  const float Hk1 = (k + 1 < NB) ? g_h : 0.f;
+  // g wrt normalised width i: 2B * (Gk [i < k] + Gk1 [i < k+1]); softmax backward
+  float dotw = 0.f, doth = 0.f;
+#pragma unroll
+  for (int i = 0; i < NB; ++i) {
+    float gw_i = (2.f * B) * ((i < k ? Gk : 0.f) + (i < k + 1 ? Gk1 : 0.f));
+    float gh_i = (2.f * B) * ((i < k ? Hk : 0.f) + (i < k + 1 ? Hk1 : 0.f));
+    dotw += gw_i * pw[i];
+    doth += gh_i * ph[i];
+  }
+#pragma unroll
+  for (int i = 0; i < NB; ++i) {
+    float gw_i = (2.f * B) * ((i < k ? Gk : 0.f) + (i < k + 1 ? Gk1 : 0.f));
+    float gh_i = (2.f * B) * ((i < k ? Hk : 0.f) + (i < k + 1 ? Hk1 : 0.f));
+    G(i, scale * pw[i] * (gw_i - dotw));
+    G(NB + i, scale * ph[i] * (gh_i - doth));
+  }
+  // softplus'(u) = sigmoid(u) (torch: 1 above the threshold of 20)
+  const float sg0 = u0 > 20.f ? 1.f : fx_rcp(1.f + fx_exp(-u0));
+  const float sg1 = u1 > 20.f ? 1.f : fx_rcp(1.f + fx_exp(-u1));
+#pragma unroll
+  for (int i = 0; i < NB - 1; ++i) {
+    float g = 0.f;
+    if (i + 1 == k) g += g_dk * sg0;
+    if (i == k) g += g_dk1 * sg1;
+    G(2 * NB + i, g);
+  }
+  return gx;
+}
+
 #endif
 
 }  // namespace pf

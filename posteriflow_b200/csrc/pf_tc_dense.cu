@@ -379,6 +379,12 @@ __global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const D
       }
       arrive_ops();                                             // x tile of layer 0
       for (int l = 0; l < s.L && ok; ++l) {
+        if constexpr (SAVE) {   // training: per-row gates come from global memory -- ask the L2 for the NEXT layer's block
+          if (rt == 0 && l + 1 < s.L) {
+            const char* pj = reinterpret_cast<const char*>(a.proj + ((size_t)tile * a.ldproj + (size_t)(l + 1) * 3 * DN_H) * DN_ROWS);
+            for (int o = 0; o < 3 * DN_H * DN_ROWS * 4; o += 65536) bulk_prefetch_l2(pj + o, 65536);
+          }
+        }
         // ---- this layer's constants -> shared memory (all 256 row threads) ----
         bar_sync(1, 256);                                       // previous layer's readers are done
         {

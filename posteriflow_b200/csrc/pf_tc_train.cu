@@ -26,11 +26,13 @@ namespace pf {
 using namespace pf::sm100;
 
 constexpr int TT_THREADS = 320;
-constexpr int TT_NSLOT = 3;
+constexpr int TT_NSLOT = 5;      // weight ring depth (16 KB slots): what shared memory leaves beside the two operand tiles
 constexpr int TT_SLOT = 16384;
 constexpr int TT_H = 256;
 constexpr int TT_NB = 16;
 constexpr int TT_MULT = 3 * TT_NB - 1;
+constexpr int TT_PCOL = 48;      // columns a dimension's 47 parameter gradients take in an operand tile: 8-aligned, so a
+                                 // thread writes them as six conflict-free 16-byte stores (the 48th is a zero pad)
 
 struct TtShape {
   int D, L, PLD, DP;
@@ -72,7 +74,8 @@ __global__ void tt_pack_kernel(TtShape s, uint8_t* __restrict__ image, const flo
       float v = 0.f;
       if (kind <= 1) {
         const int first = kind == 0 ? 1 : 1 + s.ga, cnt = kind == 0 ? s.ga : s.gb;
-        if (k < cnt * TT_MULT) v = WfT[((size_t)l * H + n) * s.PLD + (size_t)first * TT_MULT + k];
+        const int dim = k / TT_PCOL, i = k % TT_PCOL;
+        if (dim < cnt && i < TT_MULT) v = WfT[((size_t)l * H + n) * s.PLD + (size_t)(first + dim) * TT_MULT + i];
       } else {
         const int hs = kind - 2;                    // 0 Wb2, 1 Wa2, 2 Wb1, 3 Wa1
         const int blk = hs < 2 ? 1 : 0;
@@ -140,7 +143,6 @@ struct TtArgs {
   const uint8_t* img;                   // [L][TT_NA][tiles][TT_IMG]
   const float* gz; const float* gl;     // upstream gradients [R, D], [R] (either may be NULL = 0)
   uint8_t* gimg;                        // [L][TT_NG][tiles][TT_IMG]
-  float* gproj;                         // [tiles][L*3*H][128]
   float* gx;                            // [R, D] or NULL
   float* dbf[TT_MAX_L];                 // final_layer.bias gradient of each layer (dim 0's 47 entries) or NULL
   int64_t R; int n_tiles; float tail; int* err;
@@ -281,7 +283,24 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
       for (int l = s.L - 1; l >= 0 && ok; --l) {
         // row-minor layouts: column c of this thread's row sits at base[c * 128] (one 128-byte line per warp access)
         const float* projr = a.proj + ((size_t)tile * a.ldproj + (size_t)l * 3 * TT_H) * TT_ROWS + r;
-        float* gprojr = a.gproj + ((size_t)tile * a.ldproj + (size_t)l * 3 * TT_H) * TT_ROWS + r;
+        // one thread asks the L2 for what this tile reads next (contiguous blocks of the saved arrays): the spline
+        // parameters of the layer below, and this layer's gates / pre-gate values / relu-mask images
+        if (rt == 0) {
+          if (l > 0) {
+            const float* pn = a.P + ((size_t)(l - 1) * a.n_tiles + tile) * s.PLD * TT_ROWS;
+            for (uint32_t o = 0; o < (uint32_t)s.PLD * TT_ROWS * 4u; o += 65536u) {
+              const uint32_t n = (uint32_t)s.PLD * TT_ROWS * 4u - o;
+              bulk_prefetch_l2(reinterpret_cast<const char*>(pn) + o, n < 65536u ? n : 65536u);
+            }
+            bulk_prefetch_l2(a.XS + ((size_t)(l - 1) * a.n_tiles + tile) * D * TT_ROWS, (uint32_t)D * TT_ROWS * 4u);
+          }
+          const char* pj = reinterpret_cast<const char*>(a.proj + ((size_t)tile * a.ldproj + (size_t)l * 3 * TT_H) * TT_ROWS);
+          for (int o = 0; o < 3 * TT_H * TT_ROWS * 4; o += 65536) bulk_prefetch_l2(pj + o, 65536);
+          for (int w = 0; w < TT_NA; ++w) {
+            if (w == TT_A_H2) continue;
+            bulk_prefetch_l2(a.img + tt_img_off(l, w, TT_NA, tile, a.n_tiles), TT_IMG);
+          }
+        }
         // ---------------- E0: spline VJP -> d params (two operand tiles: dims 1..ga, then ga+1..) ----------------
 #pragma unroll 1
         for (int ps = 0; ps < 2 && ok; ++ps) {
@@ -300,7 +319,7 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
             for (int i = 0; i < TT_MULT; ++i) q[i] = __ldg(pr + (size_t)i * TT_ROWS);
             const float xin = a.XS[(((size_t)l * a.n_tiles + tile) * D + (D - 1 - j)) * TT_ROWS + r];
             const float gyj = gy_s[r * 12 + j];
-            const float gxd = rqs_forward_backward<TT_NB>(TtRegQ{q}, xin, a.tail, gyj, glr, TtGradOut{gp});
+            const float gxd = rqs_forward_backward_fast<TT_NB>(TtRegQ{q}, xin, a.tail, gyj, glr, TtGradOut{gp});
             gxd_s[r * 12 + j] = valid ? gxd : 0.f;
             if (is0) {
               // dim 0's parameters are bias only: their gradient goes straight to final_layer.bias[0:47]
@@ -330,15 +349,18 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
               mark(5);
               opened = true;
             }
-            const int cbase = (j - gfirst) * TT_MULT;
+            const int cg0 = (j - gfirst) * (TT_PCOL / 8);       // first 8-column group of this dimension
 #pragma unroll
-            for (int i = 0; i < TT_MULT; ++i) {
-              const int c = cbase + i;
-              const float v = valid ? gp[i] : 0.f;
-              const __nv_bfloat16 hi = __float2bfloat16(v);
-              const uint32_t o = (uint32_t)(c / 8) * 2048 + rowoff + (uint32_t)(c % 8) * 2;
-              *reinterpret_cast<__nv_bfloat16*>(sACT + o) = hi;
-              *reinterpret_cast<__nv_bfloat16*>(sACTLO + o) = __float2bfloat16(v - __bfloat162float(hi));
+            for (int c8 = 0; c8 < TT_PCOL / 8; ++c8) {
+              float e[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) e[i] = (valid && 8 * c8 + i < TT_MULT) ? gp[8 * c8 + i < TT_MULT ? 8 * c8 + i : 0] : 0.f;
+              uint4 w4, l4;
+              split_bf16(e[0], e[1], w4.x, l4.x); split_bf16(e[2], e[3], w4.y, l4.y);
+              split_bf16(e[4], e[5], w4.z, l4.z); split_bf16(e[6], e[7], w4.w, l4.w);
+              const size_t io = (size_t)(cg0 + c8) * 2048 + rowoff;
+              *reinterpret_cast<uint4*>(sACT + io) = w4;
+              *reinterpret_cast<uint4*>(sACTLO + io) = l4;
             }
           }
           if (!ok) break;
@@ -433,17 +455,12 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
                 gp4[i] = o[i] * vv * g[i] * (1.f - g[i]);
                 o[i] *= g[i];
               }
-#pragma unroll
-              for (int i = 0; i < 32; ++i) gprojr[(size_t)(sec * TT_H + c0 + i) * TT_ROWS] = gp4[i];   // (rows past R: exact zeros)
               store_image(a.gimg + tt_img_off(l, TT_G_C0 + sec, TT_NG, tile, a.n_tiles),
                           a.gimg + tt_img_off(l, TT_G_C0L + sec, TT_NG, tile, a.n_tiles), c0, gp4);
             } else if (k == 4) {             // relu(context_layer) backward: g[] holds the relu'd context term
               float gc[32];
 #pragma unroll
-              for (int i = 0; i < 32; ++i) {
-                gc[i] = g[i] > 0.f ? o[i] : 0.f;
-                gprojr[(size_t)(c0 + i) * TT_ROWS] = gc[i];
-              }
+              for (int i = 0; i < 32; ++i) gc[i] = g[i] > 0.f ? o[i] : 0.f;
               store_image(a.gimg + tt_img_off(l, TT_G_C0, TT_NG, tile, a.n_tiles),
                           a.gimg + tt_img_off(l, TT_G_C0L, TT_NG, tile, a.n_tiles), c0, gc);
             }
@@ -700,8 +717,8 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
       int wr = -1;                                  // row index in nflows' space (mask rule)
       if (mat == 0) {
         const int first = jk < 2 ? 1 : 1 + s.ga, cnt = jk < 2 ? s.ga : s.gb;
-        if (gm < cnt * TT_MULT) {
-          wr = first * TT_MULT + gm;
+        if (gm / TT_PCOL < cnt && gm % TT_PCOL < TT_MULT) {
+          wr = (first + gm / TT_PCOL) * TT_MULT + gm % TT_PCOL;
           if (g.final_w) wrow = g.final_w + (size_t)wr * TT_H;
           if (g.final_b) bdst = g.final_b + wr;
           ld = TT_H;
@@ -811,7 +828,7 @@ struct TtCpArgs {
   int CK, NB, nb_per_cta, tiles;
   int* err;
 };
-constexpr int CP_THREADS = 192;
+constexpr int CP_THREADS = 320;      // 8 epilogue warps (two per TMEM lane quarter: column halves), MMA issuer, loader
 constexpr int CP_OFF_RING = 2 * TT_CIMG;
 constexpr int CP_NSLOT = 3;
 constexpr int CP_OFF_BAR = CP_OFF_RING + CP_NSLOT * TT_SLOT;
@@ -861,11 +878,11 @@ __global__ void __launch_bounds__(CP_THREADS, 1) tt_ctxproj_kernel(const TtCpArg
   if (tid == 0) {
     for (int i = 0; i < CP_NSLOT; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     mbar_init(a_bar, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_free[i], 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_free[i], 8); }
     *abort_s = 0;
     fence_mbar_init();
   }
-  if (warp == 4) tmem_alloc(tmem_slot, 512);
+  if (warp == 8) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -879,10 +896,11 @@ __global__ void __launch_bounds__(CP_THREADS, 1) tt_ctxproj_kernel(const TtCpArg
     raise_flag(a.err, code);
     return false;
   };
-  if (warp < 4) {
-    // ---- epilogue: thread = row of the tile ----
-    const int r = warp * 32 + lane;
-    const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16);
+  if (warp < 8) {
+    // ---- epilogue: two threads per row of the tile (column halves) ----
+    const int q4 = warp & 3, half = warp >> 2;
+    const int r = q4 * 32 + lane;
+    const uint32_t tl = tmem + ((uint32_t)(q4 * 32) << 16);
     uint32_t par[2] = {0, 0};
     bool ok = true;
     for (int nb = nb0; nb < nb1 && ok; ++nb) {
@@ -894,21 +912,22 @@ __global__ void __launch_bounds__(CP_THREADS, 1) tt_ctxproj_kernel(const TtCpArg
       float* dst = a.out + ((size_t)tile * a.NB * 256 + (size_t)nb * 256) * TT_ROWS + r;
       const float* bias = a.bias + (size_t)nb * 256;
 #pragma unroll 1
-      for (int c0 = 0; c0 < 256; c0 += 32) {
+      for (int c0 = half * 128; c0 < half * 128 + 128; c0 += 32) {
         uint32_t v[32];
         tmem_ld32(tl + ab * 256 + c0, v);
         tmem_wait_ld();
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           const float x = fmaf(__uint_as_float(v[i]), 1.f / 16.f, __ldg(bias + c0 + i));
-          dst[(size_t)(c0 + i) * TT_ROWS] = sec == 0 ? fmaxf(x, 0.f) : 1.f / (1.f + expf(-x));
+          // sigmoid through the hardware ex2 / rcp (~2^-22 relative: far below the tier's tolerance)
+          dst[(size_t)(c0 + i) * TT_ROWS] = sec == 0 ? fmaxf(x, 0.f) : fx_rcp(1.f + fx_ex2(-1.4426950408889634f * x));
         }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_free[ab]);
     }
-  } else if (warp == 4) {
+  } else if (warp == 8) {
     // ---- MMA issuer ----
     const uint32_t idesc = umma_idesc_bf16(TT_ROWS, 256) & ~((1u << 7) | (1u << 10));     // fp16 operands
     const uint32_t aHi = smem_u32(sA), aLo = aHi + TT_CIMG, aRing = smem_u32(ring);
@@ -963,7 +982,7 @@ __global__ void __launch_bounds__(CP_THREADS, 1) tt_ctxproj_kernel(const TtCpArg
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) tmem_dealloc(tmem, 512);
+  if (warp == 8) tmem_dealloc(tmem, 512);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1104,8 +1123,8 @@ static bool tt_plan(const pf_flow* f, TtShape& s) {
   s.D = f->D; s.L = f->L; s.PLD = f->PLD; s.DP = f->DP;
   s.ga = (f->D - 1 + 1) / 2;
   s.gb = f->D - 1 - s.ga;
-  s.NA = round_up(s.ga * TT_MULT, 16);
-  s.NBn = s.gb > 0 ? round_up(s.gb * TT_MULT, 16) : 16;
+  s.NA = round_up(s.ga * TT_PCOL, 16);
+  s.NBn = s.gb > 0 ? round_up(s.gb * TT_PCOL, 16) : 16;
   if (s.NA > 256 || s.NBn > 256) return false;
   s.layer_bytes = (uint32_t)(s.NA / 16 + s.NBn / 16 + 65) * TT_SLOT;
   return true;
@@ -1235,7 +1254,7 @@ pf_status pf_tt_backward(pf_flow* f, cudaStream_t st, const TtSaved& sv, const T
   a.ldproj = (int64_t)f->L * 3 * TT_H;
   a.P = sv.P; a.XS = sv.XS; a.img = sv.img;
   a.gz = gz; a.gl = glogdet;
-  a.gimg = ws.gimg; a.gproj = ws.gproj;
+  a.gimg = ws.gimg;
   a.gx = gx;
   for (int l = 0; l < f->L; ++l) a.dbf[l] = grads ? grads[l].final_b : nullptr;
   a.R = R;

@@ -4,13 +4,15 @@
 //
 // Replaces, for one NLL training step of the flow head (experiments/train_lean_npe.py:357-369, flows.py:727-779):
 // 70 forward + 200 backward kernel launches of the GEMM-per-launch form by
-//   1  context projection GEMM            [R,288] x [288, L*3*256]                       (pf_tc_gemm.cuh)
+//   2  context projection                  fp16 hi / lo images of the context rows, then ctx . Wctx^T on tcgen05 for all L*3
+//                                          context Linear layers (two accumulators: epilogue under the next block's MMAs)
 //   1  forward kernel                      all L layers per 128-row tile on chip, activations saved as bf16 images
 //   1  backward chain kernel               all L layers per tile: spline VJP -> 7 data-gradient MMA stages per layer
-//   1  weight-gradient kernel              one CTA per (layer, matrix, 128-row block of the output): contraction over
-//                                          ALL flow rows by MN-major tcgen05.mma on the saved images, bias gradients
-//                                          as column sums of the same tiles, plain stores (no atomics, no zero fill)
-//   3  context-path kernels                d ctx (GEMM), d Wctx (GEMM), d bctx (column sums) over the fp32 gate gradients
+//   2  weight-gradient kernel              bf16 context images, then one CTA per (layer, matrix, 128-row block of the
+//                                          output) -- the 3 context Linear layers included: contraction over ALL flow rows
+//                                          by MN-major tcgen05.mma on the saved images, bias gradients as column sums of
+//                                          the same tiles, plain read-modify-write stores (no atomics)
+//   1  d ctx kernel                        gate / context gradients (bf16 hi / lo images) . Wctx over all L*3 layers
 #pragma once
 #include "pf_common.cuh"
 
@@ -70,7 +72,6 @@ struct TtSaved {
 // carve of the backward workspace (fused form)
 struct TtWork {
   uint8_t* gimg;   // [L][TT_NG][tiles][TT_IMG]  bf16 gradient images
-  float* gproj;    // [tiles][L*3*H][128]  d loss / d (pre-activation of the context layers), tile-transposed
   uint8_t* cimg;   // [tiles][TT_CIMG]  bf16 image of the context rows (weight-gradient operand of the context layers)
   size_t bytes;
   TtWork(const pf_flow* f, void* base, int64_t R) {
@@ -79,7 +80,6 @@ struct TtWork {
     size_t o = 0;
     auto take = [&](size_t b) { char* r = p ? p + o : nullptr; o += tt_align(b); return r; };
     gimg = reinterpret_cast<uint8_t*>(take((size_t)f->L * TT_NG * tiles * TT_IMG));
-    gproj = reinterpret_cast<float*>(take(tiles * TT_ROWS * (size_t)f->L * 3 * f->H * 4));
     cimg = reinterpret_cast<uint8_t*>(take(tiles * (size_t)TT_CIMG));
     bytes = o;
   }
