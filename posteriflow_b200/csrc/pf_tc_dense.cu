@@ -624,7 +624,9 @@ __global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const D
           }
           float lad;
           float y;
-          if constexpr (SPLIT == 3) y = rqs_apply<DN_NB, false>(DnRegQ{q}, xin, a.tail, lad);   // exact expf / logf / division
+          // split tier, inference (log q at the FP32 tolerance): exact expf / logf / division.  bf16 tier and the training
+          // forward (whose parameters are saved before this point and differentiated by the backward): hardware ex2 / lg2 / rcp
+          if constexpr (SPLIT == 3 && !SAVE) y = rqs_apply<DN_NB, false>(DnRegQ{q}, xin, a.tail, lad);
           else y = dn_rqs_forward(q, xin, a.tail, lad);
           ld_acc += lad;
           yout[j] = y;

@@ -104,13 +104,19 @@ class GraphedNLLStep:
         from .ops import no_row2ctx
         no_r2c = no_row2ctx(st["x"])
 
+        self._ensure_flat()
+
         def body():
             z, ld, saved = torch.ops.posteriflow.nsf_forward(st["x"], st["ctx"], weights, fh.id, 1, True, no_r2c)
             nll = 0.5 * ((z * z).sum(dim=1) + const) - ld
             loss = (nll * st["w"]).sum()
             outs = torch.ops.posteriflow.nsf_backward(saved, st["ctx"], z * st["w"].unsqueeze(1), -st["w"], weights,
                                                       fh.id, 1)
-            return loss, outs[1], list(outs[2:])
+            gw = list(outs[2:])
+            # inside the graph: the step's flow-weight gradients go straight into the views of the flat buffer that the
+            # data-parallel all-reduce exchanges (one multi-tensor copy per replay instead of one per step on the host)
+            torch._foreach_copy_(self._step_views, gw)
+            return loss, outs[1], gw
 
         s = torch.cuda.Stream(device=dev)
         s.wait_stream(torch.cuda.current_stream(dev))
@@ -127,13 +133,18 @@ class GraphedNLLStep:
         return st
 
     def _ensure_flat(self):
-        """Views of ONE flat buffer, one per flow parameter: the data-parallel all-reduce is a single collective."""
+        """Views of ONE flat buffer, one per flow parameter: the data-parallel all-reduce is a single collective.
+        `flat_step` (same layout) receives each replay's gradients inside the graph; `flat_grad` holds what `.grad` points
+        at (equal to `flat_step` after a fresh step, the running sum under gradient accumulation)."""
         if self._gbuf is None:
             dev = self.flow_params[0].device
-            self.flat_grad = torch.zeros(sum(p.numel() for p in self.flow_params), dtype=torch.float32, device=dev)
-            self._gbuf, o = [], 0
+            n = sum(p.numel() for p in self.flow_params)
+            self.flat_grad = torch.zeros(n, dtype=torch.float32, device=dev)
+            self.flat_step = torch.zeros(n, dtype=torch.float32, device=dev)
+            self._gbuf, self._step_views, o = [], [], 0
             for p in self.flow_params:
                 self._gbuf.append(self.flat_grad[o:o + p.numel()].view(p.shape))
+                self._step_views.append(self.flat_step[o:o + p.numel()].view(p.shape))
                 o += p.numel()
 
     def __call__(self, params: Tensor, nsig: Tensor, context: Tensor) -> Tensor:
@@ -185,15 +196,20 @@ class GraphedNLLStep:
         st["graph"].replay()
         self.last_launches = st["launches"]
         # the graph's gradient tensors are overwritten by the next replay: hand out copies (two multi-tensor kernels)
-        self._ensure_flat()
         fresh = [i for i, p in enumerate(self.flow_params) if p.requires_grad and p.grad is None]
-        accum = [i for i, p in enumerate(self.flow_params) if p.requires_grad and p.grad is not None]
-        if fresh:
-            torch._foreach_copy_([self._gbuf[i] for i in fresh], [st["gw"][i] for i in fresh])
-            for i in fresh:
-                self.flow_params[i].grad = self._gbuf[i]
-        if accum:
-            torch._foreach_add_([self.flow_params[i].grad for i in accum], [st["gw"][i] for i in accum])
+        if len(fresh) == len(self.flow_params):
+            # the usual step (zero_grad(set_to_none=True) before it): ONE flat copy, then .grad = the views
+            self.flat_grad.copy_(self.flat_step)
+            for p, v in zip(self.flow_params, self._gbuf):
+                p.grad = v
+        else:
+            accum = [i for i, p in enumerate(self.flow_params) if p.requires_grad and p.grad is not None]
+            if fresh:
+                torch._foreach_copy_([self._gbuf[i] for i in fresh], [self._step_views[i] for i in fresh])
+                for i in fresh:
+                    self.flow_params[i].grad = self._gbuf[i]
+            if accum:
+                torch._foreach_add_([self.flow_params[i].grad for i in accum], [self._step_views[i] for i in accum])
         if ctx_full.requires_grad:
             ctx_full.backward(st["gctx"][:R])
         return st["loss"].detach()
