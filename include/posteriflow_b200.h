@@ -238,6 +238,9 @@ pf_status pf_posterior_summary(const float* theta, int64_t E, int64_t n, int32_t
 
 size_t pf_flow_workspace_bytes(const pf_flow* flow, int32_t op, int64_t R, int64_t E);
 size_t pf_flow_saved_bytes(const pf_flow* flow, int64_t R, int64_t E);
+/* 1 if pf_flow_forward(saved) / pf_flow_backward of this (packed) handle run as the fused persistent kernels (tensor-core
+ * tier, LeanNPE-class shape, dense context form), 0 if they run GEMM per launch: callers size their batches by it */
+int32_t pf_flow_fused_training(const pf_flow* flow);
 /* number of kernels the last call on this handle launched (bench.py's gpu_launches counter) */
 int64_t pf_flow_last_launch_count(const pf_flow* flow);
 /* hidden-unit permutation of the packed layout: perm[s] = nflows unit index at sorted slot s */

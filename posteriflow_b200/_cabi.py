@@ -24,7 +24,7 @@ EXPORTS = [
     "pf_flow_create", "pf_flow_destroy", "pf_flow_pack", "pf_flow_ctxproj", "pf_flow_inverse",
     "pf_sample_fused", "pf_flow_forward", "pf_flow_backward", "pf_flow_workspace_bytes",
     "pf_flow_saved_bytes", "pf_flow_last_launch_count", "pf_flow_hidden_perm", "pf_status_str",
-    "pf_last_cuda_error", "pf_abi_version", "pf_physical_logq", "pf_posterior_summary", "pf_flow_check",
+    "pf_last_cuda_error", "pf_abi_version", "pf_physical_logq", "pf_posterior_summary", "pf_flow_check", "pf_flow_fused_training",
 ]
 
 _fp = C.c_void_p  # every device pointer is passed as an integer address
@@ -74,6 +74,8 @@ def load_library() -> C.CDLL:
     lib.pf_flow_destroy.restype = None
     lib.pf_flow_pack.argtypes = [C.c_void_p, C.POINTER(LayerPtrs), _fp]
     lib.pf_flow_pack.restype = i32
+    lib.pf_flow_fused_training.argtypes = [C.c_void_p]
+    lib.pf_flow_fused_training.restype = i32
     lib.pf_flow_check.argtypes = [C.c_void_p, _fp]
     lib.pf_flow_check.restype = i32
     lib.pf_flow_ctxproj.argtypes = [C.c_void_p, _fp, i64, u32, _fp, _fp]

@@ -342,6 +342,10 @@ static inline bool fused_train(const pf_flow* f, const int64_t* row2ctx, int64_t
   return f->train_fused && f->train && f->dense && !row2ctx && n_per_ctx == 1 && f->C <= TT_CIMG_COLS;
 }
 
+extern "C" int32_t pf_flow_fused_training(const pf_flow* f) {
+  return (f && f->train_fused && f->train && f->dense && f->C <= TT_CIMG_COLS) ? 1 : 0;
+}
+
 extern "C" size_t pf_flow_saved_bytes(const pf_flow* f, int64_t R, int64_t E) {
   if (!f || R < 0 || E < 0) return 0;
   size_t b = SavedLayout(f, nullptr, R, E).bytes;

@@ -1214,7 +1214,7 @@ pf_status pf_tt_dctx(pf_flow* f, cudaStream_t st, const TtWork& ws, int64_t R, f
   a.L = f->L; a.C = f->C;
   a.tiles = (int)((R + TT_ROWS - 1) / TT_ROWS);
   a.R = R;
-  int slices = (f->sm_count + a.tiles - 1) / a.tiles;      // about one CTA per SM
+  int slices = f->sm_count / a.tiles;                      // one wave: at most one CTA per SM
   if (slices < 1) slices = 1;
   if (slices > f->L * 3) slices = f->L * 3;
   a.imgs_per_cta = (f->L * 3 + slices - 1) / slices;

@@ -139,6 +139,11 @@ class FlowHandle:
     def _note_launches(self) -> None:
         self.launches += int(self.lib.pf_flow_last_launch_count(self.h))
 
+    @property
+    def fused_training(self) -> bool:
+        """forward(save) / backward run as the fused persistent kernels rather than GEMM per launch"""
+        return bool(self.lib.pf_flow_fused_training(self.h))
+
     def hidden_perm(self) -> List[int]:
         buf = (C.c_int32 * self.shape[2])()
         A.check(self.lib.pf_flow_hidden_perm(self.h, buf), "pf_flow_hidden_perm")

@@ -81,10 +81,21 @@ class GraphedNLLStep:
     gradient), so a handful of graphs covers the step-to-step variation of the number of signals.  The part of
     the graph of `context` that lies outside the flow (row gather, rank embedding, the caller's encoder) stays
     with autograd: the graph hands back d loss / d full-context and `Tensor.backward` carries it on.
-    Same value and gradients as `batch_nll(...).backward()` (tests/test_gpu_glue.py)."""
+    Same value and gradients as `batch_nll(...).backward()` (tests/test_gpu_glue.py).
 
-    def __init__(self, model, bucket: int = 128, distributed: bool = False):
+    **Slot mode** (`slots=True`; the default whenever all B * max_signals (event, rank) slots of a batch fit one wave of
+    128-row tiles, i.e. B * max_signals <= 128 * #SMs): the fused training kernels keep one tile per SM from the first
+    layer to the last, so a step costs one tile's latency whether 8 or 148 SMs are busy.  The step then runs over EVERY
+    slot of the batch with weight [rank < nsig] / count instead of gathering the present signals first: all shapes are
+    static, so the row gather, the scaler, the rank embedding, their backward and the signal count move INTO the
+    captured graph -- no `nonzero` (a host sync), no ATen glue around the replay, one graph for every batch of that
+    size.  Absent slots carry weight zero (their parameters are replaced by a fixed in-range value first): they add
+    exactly nothing to the loss and to every gradient."""
+
+    def __init__(self, model, bucket: int = 128, distributed: bool = False, slots: Optional[bool] = None):
         self.model, self.bucket, self.distributed = model, int(bucket), distributed
+        self.slots = slots
+        self.slot_graphs = {}
         self.graphs = {}
         self.flow_params = model.flow.layer_weights()
         self._gbuf = None
@@ -132,6 +143,123 @@ class GraphedNLLStep:
         st["launches"] = fh.launches - l0      # library kernels inside one replay
         return st
 
+    # -- slot mode ---------------------------------------------------------------------------------------------------
+    def _use_slots(self, B: int, dev) -> bool:
+        if self.slots is not None:
+            return bool(self.slots)
+        if not self.model.flow.handle().fused_training:      # GEMM-per-launch kernels: more rows = more time
+            return False
+        n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
+        return B * int(self.model.max_signals) <= 128 * n_sm
+
+    def _capture_slots(self, B: int, ctx_requires_grad: bool):
+        import math
+        m = self.model
+        dev = self.flow_params[0].device
+        D, C, S = m.flow.features, m.flow.context_features, int(m.max_signals)
+        R = B * S
+        cap = (R + 127) // 128 * 128
+        st = {"params": torch.zeros(B, S, D, device=dev), "nsig": torch.zeros(B, dtype=torch.long, device=dev),
+              "context": torch.zeros(B, m.context_dim, device=dev), "inv_count": torch.zeros((), device=dev),
+              "use_inv": torch.zeros((), device=dev)}
+        fh = m.flow.handle()
+        weights = [p.detach() for p in self.flow_params]
+        const = D * math.log(2 * math.pi)
+        from .ops import no_row2ctx
+        no_r2c = no_row2ctx(st["params"])
+        self._ensure_flat()
+        sc = m.scaler
+        fill = sc.denormalize(torch.zeros(D, device=dev))                  # an in-range physical value for absent slots
+        xbuf = torch.zeros(cap, D, device=dev)
+        cbuf = torch.zeros(cap, C, device=dev)
+        wbuf = torch.zeros(cap, device=dev)
+        emb = m.rank_embed.weight
+
+        def body():
+            present = (torch.arange(S, device=dev).unsqueeze(0) < st["nsig"].unsqueeze(1))          # [B, S]
+            count = present.sum().to(torch.float32).clamp_min(1.0)
+            inv = torch.where(st["use_inv"] > 0, st["inv_count"], 1.0 / count)     # global count under data parallelism
+            p = torch.where(present.unsqueeze(2), st["params"], fill)
+            xbuf[:R].copy_(sc.normalize(p).reshape(R, D))
+            # slot (b, r) = row b * S + r: broadcast copies, no gather kernels
+            c3 = cbuf[:R].view(B, S, C)
+            c3[:, :, :m.context_dim].copy_(st["context"].unsqueeze(1).expand(B, S, m.context_dim))
+            c3[:, :, m.context_dim:].copy_(emb.detach()[:S].unsqueeze(0).expand(B, S, C - m.context_dim))
+            wbuf[:R].copy_(present.reshape(R).to(torch.float32) * inv)
+            z, ld, saved = torch.ops.posteriflow.nsf_forward(xbuf, cbuf, weights, fh.id, 1, True, no_r2c)
+            nll = 0.5 * ((z * z).sum(dim=1) + const) - ld
+            loss = (nll * wbuf).sum()
+            outs = torch.ops.posteriflow.nsf_backward(saved, cbuf, z * wbuf.unsqueeze(1), -wbuf, weights, fh.id, 1)
+            gw = list(outs[2:])
+            torch._foreach_copy_(self._step_views, gw)
+            g3 = outs[1][:R].reshape(B, S, C)
+            gcontext = g3[..., :m.context_dim].sum(dim=1)                  # backward of the row gather ...
+            gemb = g3[..., m.context_dim:].sum(dim=0)                      # ... and of the rank embedding
+            return loss, gcontext, gemb
+
+        s = torch.cuda.Stream(device=dev)
+        s.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(s):
+            for _ in range(2):
+                body()
+        torch.cuda.current_stream(dev).wait_stream(s)
+        g = torch.cuda.CUDAGraph()
+        l0 = fh.launches
+        with torch.cuda.graph(g):
+            st["loss"], st["gcontext"], st["gemb"] = body()
+        # everything the captured kernels read or write must outlive this frame: the graph holds raw addresses
+        st["keep"] = (xbuf, cbuf, wbuf, fill, no_r2c, weights, emb)
+        st["graph"] = g
+        st["launches"] = fh.launches - l0
+        return st
+
+    def _call_slots(self, params: Tensor, nsig: Tensor, context: Tensor) -> Tensor:
+        m = self.model
+        B = int(context.shape[0])
+        st = self.slot_graphs.get(B)
+        if st is None:
+            st = self.slot_graphs[B] = self._capture_slots(B, context.requires_grad)
+        with torch.no_grad():
+            st["params"].copy_(params[:, :int(m.max_signals), :])
+            st["nsig"].copy_(nsig)
+            st["context"].copy_(context)
+            if self.distributed:
+                from .dist import _world
+                import torch.distributed as dist
+                if _world()[1] > 1:
+                    count = nsig.clamp(max=int(m.max_signals)).sum().to(torch.float32)
+                    dist.all_reduce(count)
+                    st["inv_count"].copy_(1.0 / count.clamp_min(1.0))
+                    st["use_inv"].fill_(1.0)
+        st["graph"].replay()
+        self.last_launches = st["launches"]
+        self._assign_flow_grads()
+        w = m.rank_embed.weight
+        if w.requires_grad:
+            if w.grad is None:
+                w.grad = st["gemb"].clone()
+            else:
+                w.grad.add_(st["gemb"])
+        if context.requires_grad:
+            context.backward(st["gcontext"])
+        return st["loss"].detach()
+
+    def _assign_flow_grads(self):
+        fresh = [i for i, p in enumerate(self.flow_params) if p.requires_grad and p.grad is None]
+        if len(fresh) == len(self.flow_params):
+            # the usual step (zero_grad(set_to_none=True) before it): ONE flat copy, then .grad = the views
+            self.flat_grad.copy_(self.flat_step)
+            for p, v in zip(self.flow_params, self._gbuf):
+                p.grad = v
+        else:
+            accum = [i for i, p in enumerate(self.flow_params) if p.requires_grad and p.grad is not None]
+            if fresh:
+                torch._foreach_copy_([self._gbuf[i] for i in fresh], [self._step_views[i] for i in fresh])
+                for i in fresh:
+                    self.flow_params[i].grad = self._gbuf[i]
+            if accum:
+                torch._foreach_add_([self.flow_params[i].grad for i in accum], [self._step_views[i] for i in accum])
+
     def _ensure_flat(self):
         """Views of ONE flat buffer, one per flow parameter: the data-parallel all-reduce is a single collective.
         `flat_step` (same layout) receives each replay's gradients inside the graph; `flat_grad` holds what `.grad` points
@@ -149,6 +277,13 @@ class GraphedNLLStep:
 
     def __call__(self, params: Tensor, nsig: Tensor, context: Tensor) -> Tensor:
         m = self.model
+        fh0 = m.flow._handle
+        if fh0 is None or fh0.device != self.flow_params[0].device:
+            m.flow.handle()
+        else:
+            fh0.ensure_packed(self.flow_params)
+        if self._use_slots(int(context.shape[0]), context.device):
+            return self._call_slots(params, nsig.to(context.device), context)
         event, rank = signal_rows(nsig.to(context.device), int(m.max_signals))
         R = int(event.numel())
         if R == 0:
@@ -196,20 +331,7 @@ class GraphedNLLStep:
         st["graph"].replay()
         self.last_launches = st["launches"]
         # the graph's gradient tensors are overwritten by the next replay: hand out copies (two multi-tensor kernels)
-        fresh = [i for i, p in enumerate(self.flow_params) if p.requires_grad and p.grad is None]
-        if len(fresh) == len(self.flow_params):
-            # the usual step (zero_grad(set_to_none=True) before it): ONE flat copy, then .grad = the views
-            self.flat_grad.copy_(self.flat_step)
-            for p, v in zip(self.flow_params, self._gbuf):
-                p.grad = v
-        else:
-            accum = [i for i, p in enumerate(self.flow_params) if p.requires_grad and p.grad is not None]
-            if fresh:
-                torch._foreach_copy_([self._gbuf[i] for i in fresh], [self._step_views[i] for i in fresh])
-                for i in fresh:
-                    self.flow_params[i].grad = self._gbuf[i]
-            if accum:
-                torch._foreach_add_([self.flow_params[i].grad for i in accum], [self._step_views[i] for i in accum])
+        self._assign_flow_grads()
         if ctx_full.requires_grad:
             ctx_full.backward(st["gctx"][:R])
         return st["loss"].detach()

@@ -235,19 +235,24 @@ def test_batch_nll_fused_matches_loop_and_oracle():
     assert float((c1.grad - c2.grad).abs().max()) <= 1e-4 * scale
 
 
-@pytest.mark.parametrize("tier", ["fp32", "bf16"])
+@pytest.mark.parametrize("tier", ["fp32", "bf16", "bf16-rows"])
 def test_graphed_nll_step_matches_batch_nll(tier, monkeypatch):
     """GraphedNLLStep (one CUDA-graph replay per step, rows padded to a bucket with zero weight) == batch_nll +
     backward through autograd: same loss, same gradient of the context, the rank embedding and every flow weight;
     replaying the cached graph on a second batch with a different number of rows in the same bucket stays exact,
     and a second call without clearing .grad accumulates."""
     import posteriflow_b200 as P
+    # "bf16": the fused training kernels in SLOT mode (every (event, rank) slot with weight [rank < nsig] / count, gather /
+    # scaler / embedding and their backward inside the graph); "bf16-rows": the same kernels over the gathered rows
+    slots = None if tier != "bf16-rows" else False
+    tier = "bf16" if tier == "bf16-rows" else tier
     if tier == "bf16":       # capture the split-bf16 tcgen05 GEMMs too (by default they serve calls of >= 512 rows)
         monkeypatch.setenv("PF_TRAIN_TC_MIN_ROWS", "0")
     spec, w, g = load_golden("lean_glue")
     m = lean_model(w, g, tier=tier)
     sc = O.Scaler()
-    step = P.GraphedNLLStep(m, bucket=64)
+    step = P.GraphedNLLStep(m, bucket=64, slots=slots)
+    assert step._use_slots(40, torch.device("cuda")) == (tier == "bf16" and slots is None)
     gen = torch.Generator().manual_seed(12)
     tol = 1e-4 if tier == "fp32" else 5e-4
     for trial in range(3):
