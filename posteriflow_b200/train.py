@@ -277,13 +277,14 @@ class GraphedNLLStep:
 
     def __call__(self, params: Tensor, nsig: Tensor, context: Tensor) -> Tensor:
         m = self.model
-        fh0 = m.flow._handle
-        if fh0 is None or fh0.device != self.flow_params[0].device:
-            m.flow.handle()
-        else:
-            fh0.ensure_packed(self.flow_params)
-        if self._use_slots(int(context.shape[0]), context.device):
-            return self._call_slots(params, nsig.to(context.device), context)
+        if context.is_cuda:
+            fh0 = m.flow._handle
+            if fh0 is None or fh0.device != self.flow_params[0].device:
+                m.flow.handle()
+            else:
+                fh0.ensure_packed(self.flow_params)
+            if self._use_slots(int(context.shape[0]), context.device):
+                return self._call_slots(params, nsig.to(context.device), context)
         event, rank = signal_rows(nsig.to(context.device), int(m.max_signals))
         R = int(event.numel())
         if R == 0:
