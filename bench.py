@@ -138,7 +138,7 @@ def run_reference(args):
     print(json.dumps({
         "impl": "reference", "metric": "posterior_samples_per_sec", "value": v, "unit": "samples/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": dict(workload_config(args.gpus), sample="SUB-SAMPLE, EXTRAPOLATED: the CPU arm runs " + sample +
                        "; its samples/s is quoted for the config above assuming linear scaling in the row count"),
         "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
@@ -269,6 +269,44 @@ def run_ours(args):
     ms_lp, launches_lp = timed(step_logprob, args.steps, args.warmup)
     ms_inf, launches_inf = timed(step_infer, args.steps, args.warmup)
     ms_sum, _ = timed(step_summary, args.steps, args.warmup)
+
+    # ---- the tier that meets the FP32 tolerance (north_star: |d theta|, |d log q| <= 1e-4 relative) ----
+    # tier="bf16x3": log-prob on the split-operand dense tcgen05 kernel; its sampling direction runs on the FP32-FMA
+    # kernels, timed on a bounded sub-sample
+    fp32acc = None
+    if args.tier == "bf16":
+        m3 = P.LeanNPE(tier="bf16x3").to(dev)
+        m3.load_state_dict(model.state_dict())
+        E3 = min(E, 512)
+        R3 = E3 * n
+        y3, c3 = y_norm[:R3], ctx_full[:E3]
+        Es = min(E, 16)
+
+        def step_lp3(i):
+            with torch.no_grad():
+                return m3.flow.compute_psd_aware_nll(y3, c3, None, n_per_ctx=n)
+
+        def step_s3(i):
+            return P.sample_fused(m3.flow, scaler, ctx_full[:Es], n, z=None, seed=5000 + i)
+
+        fh3 = m3.flow.handle()
+        ms_lp3, _ = timed(step_lp3, args.steps, args.warmup)
+        ms_s3, _ = timed(step_s3, max(2, args.steps // 2), 3)
+        lp3_rows = R3 * args.steps / (ms_lp3 * 1e-3)
+        fp32acc = {"tier": "bf16x3 (split fp16 operands: 3 MMAs per product, exact fp32 spline); parity at 1e-4 in "
+                           "tests/test_gpu_round2.py::test_split_tier_density_direction_meets_the_fp32_tolerance",
+                   "log_prob": {"value": lp3_rows * world, "unit": "rows/s", "rows_per_gpu": R3,
+                                "ms_per_step": ms_lp3 / args.steps,
+                                "roofline": {"bound": "tensor", "achieved": lp3_rows * (F_X + F_CTX / n) / 1e12,
+                                             "peak": float(peaks()[0]["bf16_tflops_sustained"]) / 3.0, "unit": "TFLOP/s",
+                                             "frac": lp3_rows * (F_X + F_CTX / n) / 1e12 / (float(peaks()[0]["bf16_tflops_sustained"]) / 3.0),
+                                             "frac_burst": lp3_rows * (F_X + F_CTX / n) / 1e12 / (float(peaks()[0]["bf16_tflops"]) / 3.0),
+                                             "note": "peak = one third of the bf16 peak: three tensor instructions per product"}},
+                   "sampler": {"value": Es * n * world * max(2, args.steps // 2) / (ms_s3 * 1e-3), "unit": "samples/s",
+                               "sample": f"{Es} events x {n} samples per GPU (sub-sample)",
+                               "kernels": "FP32-FMA tier kernels (launch-bound): the stepwise tensor-core sampler has no "
+                                          "split-operand variant -- ten activation arrays of a 128-row tile do not fit on chip"}}
+        del m3, fh3
 
     # ---- BASELINE config #2: ONE event x 50 000 samples, sample blocks over the ranks (dist.shard_sampling), per-rank
     # disjoint Philox keys; at 8 GPUs a 49-tile launch per GPU -- the latency regime of single-event serving ----
@@ -430,6 +468,7 @@ def run_ours(args):
                      "api": "NSFPosteriorFlow.compute_psd_aware_nll(y [R,11], context [E,288], n_per_ctx=n), no gradient",
                      "roofline": {"bound": "tensor", "achieved": lp_tf, "peak": peak, "unit": "TFLOP/s",
                                   "frac": lp_tf / peak, "frac_burst": lp_tf / peak_burst, "flop_per_row": flop_row}},
+        "fp32_accuracy": fp32acc,
         "infer_loop": {"metric": "samples_with_log_prob_per_sec", "value": R * world * args.steps / (ms_inf * 1e-3),
                        "unit": "samples/s", "ms_per_step": ms_inf / args.steps, "gpu_launches": int(launches_inf),
                        "api": "posteriflow_b200.posterior_chunk (pipeline.py:168-186 on the device: sampler -> wrap -> rail "

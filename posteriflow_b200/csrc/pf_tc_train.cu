@@ -685,25 +685,47 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
   if (warp < 4) {
     // ---- column sums of the gradient tiles (bias gradients), then the epilogue ----
     const int m = warp * 32 + lane;                 // column of this CTA's 128-column block = row of the weight block
-    float bsum = 0.f;
+    // column sums: thread (cg = m / 8, r8 = m % 8) reads row r8 of every 8-row core matrix of column group cg as one
+    // 16-byte load (a quarter warp covers one 128-byte core matrix: conflict-free), keeps 8 partial column sums, and the
+    // 8 threads of a column group are reduced by shuffles once per tile
+    const int cg = m >> 3, r8 = m & 7;
+    float bs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     uint32_t st = 0, par = 0;
     bool ok = true;
     for (int t = 0; t < a.tiles && ok; ++t) {
       if (!(ok = wait(&full[st], par, 70))) break;
-      const uint8_t* gb = smem + st * WG_STAGE + (size_t)(m / 8) * 2048 + (m % 8) * 2;
-      float acc0 = 0.f, acc1 = 0.f;
+      const uint8_t* gb = smem + st * WG_STAGE + (size_t)cg * 2048 + r8 * 16;
+      float ps[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll 4
       for (int rg = 0; rg < 16; ++rg) {
-#pragma unroll
-        for (int rr = 0; rr < 8; rr += 2) {
-          acc0 += __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(gb + rg * 128 + rr * 16));
-          acc1 += __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(gb + rg * 128 + rr * 16 + 16));
-        }
+        const uint4 w = *reinterpret_cast<const uint4*>(gb + rg * 128);
+        ps[0] += __uint_as_float(w.x << 16); ps[1] += __uint_as_float(w.x & 0xffff0000u);
+        ps[2] += __uint_as_float(w.y << 16); ps[3] += __uint_as_float(w.y & 0xffff0000u);
+        ps[4] += __uint_as_float(w.z << 16); ps[5] += __uint_as_float(w.z & 0xffff0000u);
+        ps[6] += __uint_as_float(w.w << 16); ps[7] += __uint_as_float(w.w & 0xffff0000u);
       }
-      bsum += acc0 + acc1;
       __syncwarp();
-      if (lane == 0) mbar_arrive(&empty[st]);
+      if (lane == 0) mbar_arrive(&empty[st]);         // shared memory is no longer read: the stage may be refilled
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float v = ps[i];
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        bs[i] += v;
+      }
       if (++st == WG_STAGES) { st = 0; par ^= 1; }
+    }
+    // thread m needs the sum of column m: column group m / 8, element m % 8 -- held (identically) by the 8 threads of
+    // that group: pick it with a shuffle from lane (m / 8 % 4) * 8 of this warp ... the group lives in this very warp
+    float bsum = 0.f;
+    {
+      const int src_lane = ((m >> 3) & 3) * 8;      // any lane of column group m / 8 (all eight hold the same sums)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float v = __shfl_sync(0xffffffffu, bs[i], src_lane);
+        if ((m & 7) == i) bsum = v;
+      }
     }
     if (ok) ok = wait(acc_bar, 0, 71);
     tc_fence_after();

@@ -487,3 +487,21 @@ def test_split_tier_addressing_modes_and_edge_rows():
         za, _ = x3.forward(x, ctx, row2ctx=r2c)
         zb, _ = x3.forward(x, ctx.index_select(0, r2c).contiguous())
     assert torch.equal(za[ok], zb[ok])
+
+
+def test_split_tier_trains_on_the_fused_kernels():
+    """tier="bf16x3": forward (inference) at the FP32 tolerance AND the same fused training step as tier="bf16" -- identical
+    kernels, so the same gradients for identical weights and inputs (up to atomic accumulation order)."""
+    spec, w, g = load_golden("lean_default")
+    grads = {}
+    for tier in ("bf16", "bf16x3"):
+        flow = make_flow(spec, w, "cuda", tier=tier)
+        assert flow.handle().fused_training
+        x = t(g["fwd_x"], "cuda").requires_grad_(True)
+        ctx = t(g["ctx"], "cuda").requires_grad_(True)
+        flow.compute_psd_aware_nll(x, ctx, None).sum().backward()
+        grads[tier] = (x.grad.clone(), ctx.grad.clone(), flow.layer_weights()[16].grad.clone())
+    # same kernels, same operands; d ctx and the dim-0 bias gradient accumulate by atomicAdd across CTAs, so the summation
+    # ORDER (and with it the last fp32 bits) differs from launch to launch
+    for a, b in zip(grads["bf16"], grads["bf16x3"]):
+        assert float((a - b).abs().max()) <= 1e-5 * float(a.abs().max())
