@@ -187,6 +187,20 @@ pf_status pf_sample_fused(pf_flow* flow, const float* ctx, const pf_scaler* scal
                           uint8_t* railed, uint32_t flags, void* workspace, size_t workspace_bytes,
                           void* stream);
 
+/* pf_sample_fused for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO counterpart in the reference.
+ * Same arguments and results as pf_sample_fused minus the workspace: the sampler's scratch (the per-event context
+ * projection) lives in a file-scope __device__ array of 32 MiB inside the library (csrc/pf_static.cu), held by every
+ * GPU that loads the library until the process exits.  The call itself allocates nothing (no cudaMalloc / cudaFree /
+ * allocating library routine).  Limit: pf_flow_workspace_bytes-equivalent scratch <= 32 MiB, i.e. E <= 1075 events per
+ * call at the LeanNPE shape on the tensor-core tier (any n); beyond it PF_ERR_WORKSPACE, text in pf_last_cuda_error().
+ * All calls on a device share the array (it keeps the last call's contents; nothing in it needs to start at zero):
+ * calls that overlap on the GPU race -- serialise them.  The first call on a device resolves the array's device
+ * address (cudaGetSymbolAddress): make it outside graph capture. */
+pf_status pf_sample_fused_static(pf_flow* flow, const float* ctx, const pf_scaler* scaler, const float* z,
+                                 uint64_t seed, int64_t E, int64_t n, float* theta, float* logdet,
+                                 uint8_t* railed, uint32_t flags, void* stream);
+
 /* ---- density direction (theta -> z) and its backward ---------------------------------------- */
 
 /* Replaces NSFPosteriorFlow.forward (flows.py:610-618): z [R, D], logdet [R].
