@@ -628,6 +628,8 @@ constexpr int WG_GBYTES = 32768;      // [128 rows x 128 columns] of a gradient 
 constexpr int WG_ABYTES = 65536;      // [128 rows x 256 columns] activation image
 constexpr int WG_STAGE = WG_GBYTES + TT_CIMG;     // sized for the widest second operand (the context image)
 constexpr int WG_OFF_BAR = WG_STAGES * WG_STAGE;
+constexpr int WG_OFF_EPI = 128 * (TT_CIMG_COLS + 1) * 4;   // epilogue: row pointers behind the staged [128][N + 1] block
+static_assert(WG_OFF_EPI + 128 * 12 <= WG_OFF_BAR, "epilogue staging must fit in the operand stages");
 constexpr int WG_SMEM = WG_OFF_BAR + 128;
 constexpr int WG_JOBS = 20;           // per layer: final 4 | 4 hidden matrices x 2 | initial 2 | 3 context layers x 2
 
@@ -729,13 +731,24 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
     }
     if (ok) ok = wait(acc_bar, 0, 71);
     tc_fence_after();
-    if (ok) {
+    // ---- epilogue: accumulator -> shared memory (transposed to nflows' column order) -> coalesced read-modify-write ----
+    // A thread owns one ROW of the weight block (its TMEM lane); written straight from there, every store of a warp hit 32
+    // different rows of the gradient (32 sectors per instruction, and a permuted column on top).  The block is staged in
+    // the (now idle) operand stages as S[row][column in nflows' order], row pitch N + 1 floats (conflict-free both ways),
+    // then each warp walks whole rows with consecutive lanes on consecutive columns.
+    bar_sync(1, 128);                               // every epilogue warp is done reading the last operand stage
+    const bool go = ok && !*abort_s;
+    float* S = reinterpret_cast<float*>(smem);
+    const int ldS = N + 1;
+    float** rowptr = reinterpret_cast<float**>(smem + WG_OFF_EPI);
+    int* roww = reinterpret_cast<int*>(smem + WG_OFF_EPI + 128 * sizeof(float*));
+    const int rule = mat == 0 ? RULE_FINAL : (mat == 5 ? RULE_INITIAL : RULE_HIDDEN);
+    if (go) {
       const pf_layer_grads& g = a.g[l];
       const int gm = mt * 128 + m;                  // column within the gradient image
       // destination row / bias slot of this thread
       float* wrow = nullptr;
       float* bdst = nullptr;
-      int ld = 0;
       int wr = -1;                                  // row index in nflows' space (mask rule)
       if (mat == 0) {
         const int first = jk < 2 ? 1 : 1 + s.ga, cnt = jk < 2 ? s.ga : s.gb;
@@ -743,48 +756,69 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
           wr = (first + gm / TT_PCOL) * TT_MULT + gm % TT_PCOL;
           if (g.final_w) wrow = g.final_w + (size_t)wr * TT_H;
           if (g.final_b) bdst = g.final_b + wr;
-          ld = TT_H;
         }
       } else if (mat <= 4) {
         const int blk = mat <= 2 ? 1 : 0, j = (mat & 1) ? 1 : 0;      // Wb = linear_layers.1, Wa = linear_layers.0
         wr = a.perm[gm];
         if (g.blk_lin_w[blk][j]) wrow = g.blk_lin_w[blk][j] + (size_t)wr * TT_H;
         if (g.blk_lin_b[blk][j]) bdst = g.blk_lin_b[blk][j] + wr;
-        ld = TT_H;
       } else if (mat == 5) {
         wr = a.perm[gm];
         if (g.initial_w) wrow = g.initial_w + (size_t)wr * s.D;
         if (g.initial_b) bdst = g.initial_b + wr;
-        ld = s.D;
       } else {
         wr = a.perm[gm];
         float* w = mat == 6 ? g.ctx_w : g.blk_ctx_w[mat - 7];
         float* b = mat == 6 ? g.ctx_b : g.blk_ctx_b[mat - 7];
         if (w) wrow = w + (size_t)wr * a.C;
         if (b) bdst = b + wr;
-        ld = a.C;
       }
-      (void)ld;
       if (bdst) *bdst += bsum;
+      rowptr[m] = wrow;
+      roww[m] = wr;
       const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16);
-      const int rule = mat == 0 ? RULE_FINAL : (mat == 5 ? RULE_INITIAL : RULE_HIDDEN);
+      float* srow = S + (size_t)m * ldS;
       for (int c0 = 0; c0 < N; c0 += 16) {
         uint32_t v[16];
         tmem_ld16(tl + c0, v);
         tmem_wait_ld();
-        if (wrow) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const int n = c0 + i;
-            if (mat >= 6) {
-              if (n < a.C) wrow[n] += __uint_as_float(v[i]);          // context Linear layers are unmasked, columns unsorted
-            } else if (mat == 5) {
-              if (n < s.D && rule_mask(rule, wr, n, s.D, TT_MULT) != 0.f) wrow[n] += __uint_as_float(v[i]);
-            } else {
-              const int wc = a.perm[n];
-              if (rule_mask(rule, wr, wc, s.D, TT_MULT) != 0.f) wrow[wc] += __uint_as_float(v[i]);
-            }
+        for (int i = 0; i < 16; ++i) {
+          const int n = c0 + i;
+          const int dc = (mat <= 4) ? a.perm[n] : n;   // hidden input units: sorted slot -> nflows column
+          srow[dc] = __uint_as_float(v[i]);
+        }
+      }
+    }
+    bar_sync(1, 128);
+    if (go) {
+      const int ncols = mat >= 6 ? a.C : (mat == 5 ? s.D : TT_H);
+      // four rows per pass, every load of the pass issued before the first add: the read-modify-write is latency-bound
+      // (one L2 / HBM round trip per pass instead of one per 32 columns)
+      constexpr int RB = 4, KC = TT_CIMG_COLS / 32;       // 9 column steps cover the widest block (288)
+      for (int r0 = warp * 32; r0 < warp * 32 + 32; r0 += RB) {
+        float old[RB][KC];
+        float* wrow[RB];
+        unsigned keep[RB];
+#pragma unroll
+        for (int q = 0; q < RB; ++q) {
+          wrow[q] = rowptr[r0 + q];
+          const int wr = roww[r0 + q];
+          keep[q] = 0u;
+#pragma unroll
+          for (int k = 0; k < KC; ++k) {
+            const int c = lane + 32 * k;
+            // context Linear layers are unmasked; masked entries of the MADE matrices are never touched (gradient exactly 0)
+            const bool on = wrow[q] && c < ncols && (mat >= 6 || rule_mask(rule, wr, c, s.D, TT_MULT) != 0.f);
+            if (on) { keep[q] |= 1u << k; old[q][k] = __ldcg(wrow[q] + c); }
           }
+        }
+#pragma unroll
+        for (int q = 0; q < RB; ++q) {
+          const float* srow = S + (size_t)(r0 + q) * ldS;
+#pragma unroll
+          for (int k = 0; k < KC; ++k)
+            if (keep[q] >> k & 1u) wrow[q][lane + 32 * k] = old[q][k] + srow[lane + 32 * k];
         }
       }
     }
@@ -1060,20 +1094,36 @@ __global__ void __launch_bounds__(DC_THREADS, 1) tt_dctx_kernel(const TtDcArgs a
   };
   constexpr int NH = TT_CIMG_COLS / 2;      // two N = 144 instructions per chunk
   if (warp < 4) {
-    if (i0 < i1 && wait(acc_bar, 0, 90)) {
-      tc_fence_after();
+    // A thread owns one row of the tile (its TMEM lane): adding from there would touch 32 different rows of d ctx per
+    // instruction.  The [128 x C] block is staged in the idle operand stages (row pitch C_pad + 1 floats) and added row by
+    // row with consecutive lanes on consecutive columns.
+    const bool ok = i0 < i1 && wait(acc_bar, 0, 90);
+    tc_fence_after();
+    bar_sync(1, 128);
+    const bool go = ok && !*abort_s;
+    float* S = reinterpret_cast<float*>(smem);
+    constexpr int ldS = TT_CIMG_COLS + 1;
+    static_assert(128 * ldS * 4 <= DC_OFF_BAR, "epilogue staging must fit in the operand stages");
+    if (go) {
       const int r = warp * 32 + lane;
-      const int64_t row = (int64_t)tile * TT_ROWS + r;
       const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16);
+      float* srow = S + (size_t)r * ldS;
       for (int c0 = 0; c0 < TT_CIMG_COLS; c0 += 16) {
         uint32_t v[16];
         tmem_ld16(tl + c0, v);
         tmem_wait_ld();
-        if (row < a.R) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i)
-            if (c0 + i < a.C) atomicAdd(a.gctx + row * a.C + c0 + i, __uint_as_float(v[i]));
-        }
+        for (int i = 0; i < 16; ++i) srow[c0 + i] = __uint_as_float(v[i]);
+      }
+    }
+    bar_sync(1, 128);
+    if (go) {
+      for (int r = warp; r < TT_ROWS; r += 4) {
+        const int64_t row = (int64_t)tile * TT_ROWS + r;
+        if (row >= a.R) break;
+        const float* srow = S + (size_t)r * ldS;
+        float* dst = a.gctx + row * a.C;
+        for (int c = lane; c < a.C; c += 32) atomicAdd(dst + c, srow[c]);
       }
     }
   } else if (warp == 4) {
