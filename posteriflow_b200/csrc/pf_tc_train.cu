@@ -742,7 +742,6 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
     const int ldS = N + 1;
     float** rowptr = reinterpret_cast<float**>(smem + WG_OFF_EPI);
     int* roww = reinterpret_cast<int*>(smem + WG_OFF_EPI + 128 * sizeof(float*));
-    const int rule = mat == 0 ? RULE_FINAL : (mat == 5 ? RULE_INITIAL : RULE_HIDDEN);
     if (go) {
       const pf_layer_grads& g = a.g[l];
       const int gm = mt * 128 + m;                  // column within the gradient image
@@ -775,7 +774,8 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
       }
       if (bdst) *bdst += bsum;
       rowptr[m] = wrow;
-      roww[m] = wr;
+      // threshold of the mask comparison (see the write-back below); rows without a destination never pass it
+      roww[m] = mat >= 6 ? 0 : (mat == 0 ? (wr >= 0 ? wr / TT_MULT : -1) : hidden_degree(wr, s.D));
       const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16);
       float* srow = S + (size_t)m * ldS;
       for (int c0 = 0; c0 < N; c0 += 16) {
@@ -796,29 +796,35 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
       // four rows per pass, every load of the pass issued before the first add: the read-modify-write is latency-bound
       // (one L2 / HBM round trip per pass instead of one per 32 columns)
       constexpr int RB = 4, KC = TT_CIMG_COLS / 32;       // 9 column steps cover the widest block (288)
+      // mask rule as one comparison thr[row] >= cv[column] (nflows' MADE masks, pf_common.cuh rule_mask):
+      //   hidden  deg(row) >= deg(col) | final  row / MULT >= deg(col) | initial  deg(row) >= col + 1 | context: no mask
+      // cv depends on (lane, k) only: computed once, so no division and no branch sits between the loads of a pass
+      int cv[KC];
+#pragma unroll
+      for (int k = 0; k < KC; ++k) {
+        const int c = lane + 32 * k;
+        cv[k] = c >= ncols ? 0x7fffffff : (mat >= 6 ? -1 : (mat == 5 ? c + 1 : hidden_degree(c, s.D)));
+      }
       for (int r0 = warp * 32; r0 < warp * 32 + 32; r0 += RB) {
         float old[RB][KC];
         float* wrow[RB];
-        unsigned keep[RB];
 #pragma unroll
         for (int q = 0; q < RB; ++q) {
           wrow[q] = rowptr[r0 + q];
-          const int wr = roww[r0 + q];
-          keep[q] = 0u;
+          const int thr = wrow[q] ? roww[r0 + q] : (int)0x80000000;
 #pragma unroll
           for (int k = 0; k < KC; ++k) {
-            const int c = lane + 32 * k;
-            // context Linear layers are unmasked; masked entries of the MADE matrices are never touched (gradient exactly 0)
-            const bool on = wrow[q] && c < ncols && (mat >= 6 || rule_mask(rule, wr, c, s.D, TT_MULT) != 0.f);
-            if (on) { keep[q] |= 1u << k; old[q][k] = __ldcg(wrow[q] + c); }
+            const bool on = thr >= cv[k];
+            old[q][k] = on ? __ldcg(wrow[q] + lane + 32 * k) : __int_as_float(0x7fc00000);
           }
         }
 #pragma unroll
         for (int q = 0; q < RB; ++q) {
           const float* srow = S + (size_t)(r0 + q) * ldS;
+          const int thr = wrow[q] ? roww[r0 + q] : (int)0x80000000;
 #pragma unroll
           for (int k = 0; k < KC; ++k)
-            if (keep[q] >> k & 1u) wrow[q][lane + 32 * k] = old[q][k] + srow[lane + 32 * k];
+            if (thr >= cv[k]) wrow[q][lane + 32 * k] = old[q][k] + srow[lane + 32 * k];
         }
       }
     }
