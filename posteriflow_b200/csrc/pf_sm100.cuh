@@ -212,6 +212,88 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
                : "memory");
 }
 
+// ---- CTA pairs (cluster of two CTAs, tcgen05 cta_group::2) ---------------------------------------
+// Measured on the B200 (tests/umma_2cta_probe.cu): tcgen05.mma.cta_group::2 with M = 128 gives each CTA 64 rows of A and
+// N / 2 rows of B; in EACH CTA the accumulator takes all 128 TMEM lanes x N / 2 columns: lanes 0..63 = its rows x
+// B rows [0, N/2) (the leader's half of B), lanes 64..127 = the same rows x B rows [N/2, N).  One instruction per pair
+// costs 71 cycles at N = 256 against 133 for the one-CTA M = 128 form: a 128-row tile split over two SMs halves both
+// the tensor time and the rows per epilogue thread, with no operand exchange.
+__device__ __forceinline__ uint32_t cluster_cta_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// all threads of both CTAs (aligned: every thread of a warp executes it)
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t* smem_dst, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t addr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(ncols) : "memory");
+}
+// issued by ONE thread of the leader CTA (rank 0); the descriptors address the same offsets in both CTAs' shared memory
+__device__ __forceinline__ void umma_ss2(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+// completion of the pair's MMAs issued so far -> one arrival on the barrier at this offset in every CTA of `mask`
+__device__ __forceinline__ void umma_commit2(uint64_t* bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                   smem_u32(bar)),
+               "h"(mask)
+               : "memory");
+}
+// Arrive on the barrier at the same offset in CTA `rank` of the cluster, RELAXED: the .release.cluster form compiles to
+// MEMBAR.ALL.GPU + ERRBAR + CGAERRBAR in front of the arrive (~1 000 cycles, measured as the pacer of the pair kernel's
+// weight hand-off).  Used where what the arrival announces is shared memory of THIS SM that the tensor core of THIS SM
+// will read through the async proxy: bytes a bulk copy has completed (observed through its mbarrier), or generic-proxy
+// stores the arriving threads have already pushed to the async proxy with fence.proxy.async -- nothing another SM's
+// threads read through the generic proxy rides on it.
+__device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t rank) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
+      "r"(rank)
+      : "memory");
+}
+// try_wait that acquires at cluster scope (barriers that receive remote arrivals)
+__device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Non-blocking probe, cluster-scope acquire.  For barriers whose arrivals come from the OTHER CTA of a pair (remote
+// arrive, multicast tcgen05.commit): a suspended try_wait was measured to sleep through them until its time limit
+// (~1 100 cycles per hand-off in the pair kernel); test_wait returns at once and the caller spins.
+__device__ __forceinline__ bool mbar_test_wait_cluster(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// generic-proxy writes (any state space) -> visible to the async proxy
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);  // .x = lo (bits 0..15), .y = hi
   return *reinterpret_cast<uint32_t*>(&v);

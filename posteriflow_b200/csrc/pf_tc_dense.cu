@@ -45,6 +45,7 @@ struct DnState {
   DnShape s;
   uint8_t* image;    // [L][layer_bytes]   bf16(W)
   uint8_t* image3;   // [L][layer_bytes3]  bf16 hi | lo of W, chunk by chunk (split tier and training forward)
+  uint8_t* imagep;   // [L][2][DP_LAYER_BYTES]  pair form of image3 (pf_tc_pair.cuh), NULL when the pair kernel is off
   long long* prof;
 };
 
@@ -770,6 +771,8 @@ __global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const D
   if (warp == 8) tmem_dealloc(tmem, 512);
 }
 
+#include "pf_tc_pair.cuh"
+
 }  // namespace pf
 using namespace pf;
 
@@ -821,18 +824,27 @@ pf_status pf_dn_pack(pf_flow* f, cudaStream_t st) {
     t->s = s;
     cudaError_t e = cudaMalloc(&t->image, (size_t)s.L * s.layer_bytes);
     if (e == cudaSuccess) e = cudaMalloc(&t->image3, (size_t)s.L * s.layer_bytes3);
+    // CTA-pair form of the training forward (LeanNPE's D = 11; PF_TRAIN_PAIR=0 keeps the one-CTA kernel)
+    const char* pp = getenv("PF_TRAIN_PAIR");
+    const bool pair_on = s.D == 11 && f->sm_count >= 2 && !(pp && pp[0] == '0');
+    if (e == cudaSuccess && pair_on) e = cudaMalloc(&t->imagep, (size_t)s.L * 2 * DP_LAYER_BYTES);
     if (e != cudaSuccess) {
       if (t->image) cudaFree(t->image);
+      if (t->image3) cudaFree(t->image3);
       delete t;
       return cuda_fail(e, "dense density image allocation", __FILE__, __LINE__);
     }
     const char* pr = getenv("PF_TC_PROF");
-    if (pr && pr[0] == '1' && cudaMalloc(&t->prof, 8 * sizeof(long long)) != cudaSuccess) t->prof = nullptr;
+    if (pr && pr[0] == '1' && cudaMalloc(&t->prof, 16 * sizeof(long long)) != cudaSuccess) t->prof = nullptr;
     f->dense = t;
   }
   dim3 grid(98 + 97, s.L);
   dn_pack_kernel<<<grid, 256, 0, st>>>(s, t->image, t->image3, f->W0, f->Wa, f->Wb, f->Wf);
   PF_LAUNCH_CHECK(f);
+  if (t->imagep) {
+    dp_pack_kernel<<<dim3(DP_PACK_SLOTS, s.L, 2), 256, 0, st>>>(s, t->imagep, f->W0, f->Wa, f->Wb, f->Wf);
+    PF_LAUNCH_CHECK(f);
+  }
   PF_TRY(pf_tt_pack(f, st));   // backward images of the fused training step (pf_tc_train.cu)
   return PF_OK;
 }
@@ -843,6 +855,7 @@ void pf_dn_destroy(pf_flow* f) {
   pf_tt_destroy(f);
   cudaFree(t->image);
   cudaFree(t->image3);
+  if (t->imagep) cudaFree(t->imagep);
   if (t->prof) cudaFree(t->prof);
   delete t;
   f->dense = nullptr;
@@ -865,11 +878,12 @@ static pf_status dn_launch(pf_flow* f, cudaStream_t st, const DnArgs& a) {
 
 static void dn_prof_report(pf_flow* f, DnState* t, cudaStream_t st) {
   if (!t->prof) return;
-  long long h[8];
+  long long h[16];
   if (cudaStreamSynchronize(st) != cudaSuccess) return;
   if (cudaMemcpy(h, t->prof, sizeof(h), cudaMemcpyDeviceToHost) != cudaSuccess) return;
   fprintf(stderr, "[pf_dn prof] CTA0: total %lld cycles: constants %lld | hidden wait %lld compute %lld | final wait %lld "
-          "spline %lld\n", h[5], h[0], h[1], h[2], h[3], h[4]);
+          "spline %lld | MMA warp (pair form): operands %lld own weights %lld peer weights %lld issue %lld\n", h[5], h[0], h[1],
+          h[2], h[3], h[4], h[8], h[9], h[10], h[11]);
 }
 
 // x [R, D] -> z [R, D], logdet [R].  `err` = the handle's error flag.  split = 1 (bf16 operands) | 3 (split operands,
@@ -955,6 +969,20 @@ pf_status pf_dn_forward_save(pf_flow* f, cudaStream_t st, const float* x, const 
   a.err = f->tg_err;
   a.prof = t->prof;
   a.sv = DnSave{img, xt, P, XS, R, a.n_tiles};
+  if (t->imagep) {     // CTA pairs: two SMs per 128-row tile
+    static bool attr_done[64] = {};
+    const int dev = f->desc.device;
+    if (dev < 64 && !attr_done[dev]) {
+      PF_CUDA(cudaFuncSetAttribute(tc_dense_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DP_SMEM));
+      attr_done[dev] = true;
+    }
+    a.image = t->imagep;
+    const int pairs = a.n_tiles < f->sm_count / 2 ? a.n_tiles : f->sm_count / 2;
+    tc_dense_pair_kernel<<<2 * pairs, DP_THREADS, DP_SMEM, st>>>(a);
+    PF_LAUNCH_CHECK(f);
+    dn_prof_report(f, t, st);
+    return PF_OK;
+  }
   PF_TRY((dn_launch<3, true>(f, st, a)));
   dn_prof_report(f, t, st);
   return PF_OK;
