@@ -44,6 +44,7 @@ struct TtShape {
 struct TtState {
   TtShape s;
   uint8_t* wimg;     // [L][layer_bytes] backward weight image
+  uint8_t* wimgp;    // [L][2][slots][8 KB] pair form (pf_tc_train_pair.cuh), NULL when the pair kernels are off
   uint8_t* cfimg;    // context projection, forward: [L*3 column blocks][C/16 chunks][fp16 hi | lo of 16 W, 16 KB]
   uint8_t* cbimg;    // context projection, d ctx:   [L*3 blocks][16 chunks][bf16 hi | lo of W^T, (C x 16) x 2 x 2 B]
   int C, CK;         // context width, K = 16 chunks of it
@@ -586,6 +587,8 @@ __global__ void __launch_bounds__(TT_THREADS, 1) tt_backward_kernel(const TtArgs
   __syncthreads();
   if (warp == 8) tmem_dealloc(tmem, 512);
 }
+
+#include "pf_tc_train_pair.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // context rows [R, C] fp32 -> bf16 tile images [tiles][C/8 column groups][16 row groups][8 rows x 16 B]
@@ -1223,9 +1226,13 @@ pf_status pf_tt_pack(pf_flow* f, cudaStream_t st) {
     cudaError_t e = cudaMalloc(&t->wimg, (size_t)s.L * s.layer_bytes);
     if (e == cudaSuccess) e = cudaMalloc(&t->cfimg, (size_t)s.L * 3 * t->CK * TT_SLOT);
     if (e == cudaSuccess) e = cudaMalloc(&t->cbimg, (size_t)s.L * 3 * 16 * TT_CB_CHUNK);
+    const char* pp = getenv("PF_TRAIN_PAIR");
+    const bool pair_on = f->sm_count >= 2 && !(pp && pp[0] == '0');
+    if (e == cudaSuccess && pair_on) e = cudaMalloc(&t->wimgp, (size_t)s.L * 2 * bp_layer_slots(s) * BP_SLOT);
     if (e != cudaSuccess) {
       if (t->wimg) cudaFree(t->wimg);
       if (t->cfimg) cudaFree(t->cfimg);
+      if (t->cbimg) cudaFree(t->cbimg);
       delete t;
       return cuda_fail(e, "backward weight image allocation", __FILE__, __LINE__);
     }
@@ -1234,6 +1241,10 @@ pf_status pf_tt_pack(pf_flow* f, cudaStream_t st) {
   dim3 grid(s.NA / 16 + s.NBn / 16 + 65, s.L);
   tt_pack_kernel<<<grid, 256, 0, st>>>(s, t->wimg, f->WfT, f->WaT, f->WbT, f->W0T);
   PF_LAUNCH_CHECK(f);
+  if (t->wimgp) {
+    tt_pack_pair_kernel<<<dim3(bp_layer_slots(s), s.L, 2), 256, 0, st>>>(s, t->wimgp, f->WfT, f->WaT, f->WbT, f->W0T);
+    PF_LAUNCH_CHECK(f);
+  }
   if (f->C <= TT_CIMG_COLS) {
     dim3 g2(t->CK + 16, s.L * 3);
     tt_pack_ctx_kernel<<<g2, 256, 0, st>>>(f->Wctx, f->C, t->CK, t->cfimg, t->cbimg);
@@ -1307,6 +1318,7 @@ void pf_tt_destroy(pf_flow* f) {
   TtState* t = reinterpret_cast<TtState*>(f->train);
   if (!t) return;
   cudaFree(t->wimg);
+  if (t->wimgp) cudaFree(t->wimgp);
   cudaFree(t->cfimg);
   cudaFree(t->cbimg);
   delete t;
@@ -1345,8 +1357,19 @@ pf_status pf_tt_backward(pf_flow* f, cudaStream_t st, const TtSaved& sv, const T
     if (pr && pr[0] == '1' && !d_prof && cudaMalloc(&d_prof, 8 * sizeof(long long)) != cudaSuccess) d_prof = nullptr;
   }
   a.prof = d_prof;
-  const int grid = a.n_tiles < f->sm_count ? a.n_tiles : f->sm_count;
-  tt_backward_kernel<<<grid, TT_THREADS, TT_SMEM, st>>>(a);
+  if (t->wimgp) {      // CTA pairs: two SMs per 128-row tile
+    static bool pattr_done[64] = {};
+    if (dev < 64 && !pattr_done[dev]) {
+      PF_CUDA(cudaFuncSetAttribute(tt_backward_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BP_SMEM));
+      pattr_done[dev] = true;
+    }
+    a.wimg = t->wimgp;
+    const int pairs = a.n_tiles < f->sm_count / 2 ? a.n_tiles : f->sm_count / 2;
+    tt_backward_pair_kernel<<<2 * pairs, BP_THREADS, BP_SMEM, st>>>(a);
+  } else {
+    const int grid = a.n_tiles < f->sm_count ? a.n_tiles : f->sm_count;
+    tt_backward_kernel<<<grid, TT_THREADS, TT_SMEM, st>>>(a);
+  }
   PF_LAUNCH_CHECK(f);
   if (d_prof) {
     long long h[8];
