@@ -277,14 +277,14 @@ __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t pa
       : "memory");
   return ok != 0;
 }
-// Non-blocking probe, cluster-scope acquire.  For barriers whose arrivals come from the OTHER CTA of a pair (remote
-// arrive, multicast tcgen05.commit): a suspended try_wait was measured to sleep through them until its time limit
-// (~1 100 cycles per hand-off in the pair kernel); test_wait returns at once and the caller spins.
-__device__ __forceinline__ bool mbar_test_wait_cluster(uint64_t* bar, uint32_t parity) {
+// Non-blocking probe (CTA-scope acquire).  The pair kernels wait with this, not with an .acquire.cluster form: the latter
+// compiles to SYNCS.PHASECHK + CCTL.IVALL -- every successful wait invalidates the SM's L1 -- and nothing the two CTAs
+// exchange is read through the generic proxy (barrier arrivals, tensor-core reads of shared memory, TMEM results).
+__device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
-      "mbarrier.test_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
       "selp.u32 %0, 1, 0, p;\n\t}"
       : "=r"(ok)
       : "r"(smem_u32(bar)), "r"(parity)

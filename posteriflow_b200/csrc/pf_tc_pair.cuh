@@ -14,7 +14,7 @@
 
 constexpr int DP_ROWS = 64;            // rows of the tile owned by one CTA
 constexpr int DP_THREADS = 320;        // 8 row warps (4 threads per row), MMA issuer / relay, weight loader
-constexpr int DP_NSLOT = 8;            // weight ring depth
+constexpr int DP_NSLOT = 16;           // weight ring depth
 constexpr int DP_SLOT = 8192;          // one K = 16 chunk of 128 outputs: fp16 hi (2 x 2 KB) | lo (2 x 2 KB)
 constexpr int DP_NHF = 96, DP_NHC = 48;   // outputs per CTA of the final stages FA / FB (2 dims x 47 -> 96) and FC (1 dim -> 48)
 constexpr uint32_t DP_LAYER_BYTES = 65u * 8192u + 16u * (2u * 64u * DP_NHF + 64u * DP_NHC);   // per layer and CTA rank
@@ -130,7 +130,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(DP_THREADS, 1) tc_de
 
   auto wait = [&](uint64_t* bar, uint32_t parity, int code) -> bool {
     for (uint32_t i = 0; i < (1u << 26); ++i) {            // ~2 s of probes: a protocol bug must not hang the GPU
-      if (mbar_test_wait_cluster(bar, parity)) return true;
+      if (mbar_test_wait(bar, parity)) return true;
       if ((i & 1023) == 1023 && *abort_s) return false;
     }
     *abort_s = 1;
@@ -386,61 +386,92 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(DP_THREADS, 1) tc_de
     }
   } else if (warp == 8) {
     // ============================ MMA issuer (leader) / weight relay (peer) ============================
-    uint32_t op_par = 0, slot = 0, full_par = 0;
-    constexpr uint32_t FMT = (1u << 7) | (1u << 10);            // fp16 x fp16 -> fp32
-    const uint32_t idesc_h = umma_idesc_bf16(128, 256) & ~FMT;
-    const uint32_t idesc_f = umma_idesc_bf16(128, 2 * DP_NHF) & ~FMT, idesc_c = umma_idesc_bf16(128, 2 * DP_NHC) & ~FMT;
-    const uint32_t aX = smem_u32(sXT), aACT = smem_u32(sACT), aACTLO = smem_u32(sACTLO), aRing = smem_u32(ring);
     bool ok = true;
-    const bool mprof = a.prof && blockIdx.x == 0;
-    long long m_op = 0, m_full = 0, m_pfull = 0, m_issue = 0;
-    for (int tile = pair; tile < a.n_tiles && ok; tile += n_pairs) {
-      for (int l = 0; l < s.L && ok; ++l) {
-        for (int st = 0; st < 8 && ok; ++st) {               // I, A1, B1, A2, B2, FA, FB, FC
-          const int NH = st < 5 ? 128 : (st < 7 ? DP_NHF : DP_NHC);
-          const int nk = st == 0 ? 1 : 16;
-          const uint32_t idesc = st < 5 ? idesc_h : (st < 7 ? idesc_f : idesc_c);
-          const uint32_t acc = tmem + (st < 6 ? 0u : (st == 6 ? (uint32_t)DP_NHF : (uint32_t)(2 * DP_NHF)));
-          uint64_t* done = st < 5 ? acc_bar : &accf_bar[st - 5];
-          if (st <= 5 && rank == 0) {                           // FB, FC read the same operand tile as FA
-            const long long t0 = mprof ? clock64() : 0;
-            if (!(ok = wait(op_bar, op_par, 20 + st))) break;
-            if (mprof) m_op += clock64() - t0;
-            op_par ^= 1;
-            tc_fence_after();
-          }
-          for (int c0 = 0; c0 < nk && ok; ++c0) {
-            const long long t1 = mprof ? clock64() : 0;
-            if (!(ok = wait(&full[slot], full_par, 31))) break;
-            const long long t2 = mprof ? clock64() : 0;
-            if (rank == 0) {
-              if (!(ok = wait(&pfull[slot], full_par, 32))) break;
-              const long long t3 = mprof ? clock64() : 0;
-              if (mprof) { m_full += t2 - t1; m_pfull += t3 - t2; }
+    if (rank != 0) {
+      // peer: tell the leader when this CTA's half of a chunk has landed (the leader's tensor instruction reads both halves)
+      uint32_t slot = 0, full_par = 0;
+      for (int tile = pair; tile < a.n_tiles && ok; tile += n_pairs)
+        for (int i = 0; i < s.L * DP_PACK_SLOTS && ok; ++i) {
+          if (!(ok = wait(&full[slot], full_par, 31))) break;
+          if (elect_one_sync()) mbar_arrive_remote(&pfull[slot], 0);
+          __syncwarp();
+          if (++slot == DP_NSLOT) { slot = 0; full_par ^= 1; }
+        }
+    } else {
+      uint32_t op_par = 0, slot = 0;
+      constexpr uint32_t FMT = (1u << 7) | (1u << 10);            // fp16 x fp16 -> fp32
+      const uint32_t idesc_h = umma_idesc_bf16(128, 256) & ~FMT;
+      const uint32_t idesc_f = umma_idesc_bf16(128, 2 * DP_NHF) & ~FMT, idesc_c = umma_idesc_bf16(128, 2 * DP_NHC) & ~FMT;
+      // descriptors advance by adding to their start-address field (16-byte units; shared addresses stay below 2^18)
+      const uint64_t adX = umma_smem_desc(smem_u32(sXT), 1024, 128), adA = umma_smem_desc(smem_u32(sACT), 1024, 128);
+      const uint64_t bd128 = umma_smem_desc(smem_u32(ring), 128 * 16, 128), bdF = umma_smem_desc(smem_u32(ring), DP_NHF * 16, 128),
+                     bdC = umma_smem_desc(smem_u32(ring), DP_NHC * 16, 128);
+      // chunks whose two halves are known to have landed, ahead of the issue pointer: confirmed while the warp would
+      // otherwise idle on the operand barrier, so that the issue loop itself polls nothing (a poll costs ~70 cycles, the
+      // three MMAs of a chunk 195: polling inline made the issuing thread, not the tensor pipe, the pacer)
+      uint32_t cslot = 0, cpar = 0;
+      int ready = 0;
+      auto confirm = [&]() {
+        while (ready < DP_NSLOT) {
+          if (!mbar_test_wait(&full[cslot], cpar) || !mbar_test_wait(&pfull[cslot], cpar)) break;
+          ++ready;
+          if (++cslot == DP_NSLOT) { cslot = 0; cpar ^= 1; }
+        }
+      };
+      const bool mprof = a.prof && blockIdx.x == 0;
+      long long m_op = 0, m_w = 0, m_issue = 0;
+      for (int tile = pair; tile < a.n_tiles && ok; tile += n_pairs) {
+        for (int l = 0; l < s.L && ok; ++l) {
+          for (int st = 0; st < 8 && ok; ++st) {               // I, A1, B1, A2, B2, FA, FB, FC
+            const int NH = st < 5 ? 128 : (st < 7 ? DP_NHF : DP_NHC);
+            const int nk = st == 0 ? 1 : 16;
+            const uint32_t idesc = st < 5 ? idesc_h : (st < 7 ? idesc_f : idesc_c);
+            const uint64_t bd0 = st < 5 ? bd128 : (st < 7 ? bdF : bdC);
+            const uint32_t acc = tmem + (st < 6 ? 0u : (st == 6 ? (uint32_t)DP_NHF : (uint32_t)(2 * DP_NHF)));
+            uint64_t* done = st < 5 ? acc_bar : &accf_bar[st - 5];
+            if (st <= 5) {                                        // FB, FC read the same operand tile as FA
+              const long long t0 = mprof ? clock64() : 0;
+              bool got = false;
+              for (uint32_t i = 0; i < (1u << 26); ++i) {
+                if (mbar_test_wait(op_bar, op_par)) { got = true; break; }
+                confirm();
+                if ((i & 1023) == 1023 && *abort_s) break;
+              }
+              if (!got) { if (!*abort_s) { *abort_s = 1; raise_flag(a.err, 20 + st); } ok = false; break; }
+              if (mprof) m_op += clock64() - t0;
+              op_par ^= 1;
+            }
+            for (int c0 = 0; c0 < nk && ok; ++c0) {
+              const long long t1 = mprof ? clock64() : 0;
+              if (ready == 0) {
+                if (!(ok = wait(&full[cslot], cpar, 31))) break;
+                if (!(ok = wait(&pfull[cslot], cpar, 32))) break;
+                ++ready;
+                if (++cslot == DP_NSLOT) { cslot = 0; cpar ^= 1; }
+              }
+              --ready;
+              const long long t2 = mprof ? clock64() : 0;
               tc_fence_after();
-              const uint32_t bbase = aRing + slot * DP_SLOT;
               if (elect_one_sync()) {
-                const uint64_t bh = umma_smem_desc(bbase, (uint32_t)NH * 16u, 128);
-                const uint64_t bl = umma_smem_desc(bbase + (uint32_t)NH * 32u, (uint32_t)NH * 16u, 128);
-                const uint64_t ah = umma_smem_desc(st == 0 ? aX : aACT + (uint32_t)c0 * 2048u, 1024, 128);
-                const uint64_t al = umma_smem_desc(st == 0 ? aX + 2048u : aACTLO + (uint32_t)c0 * 2048u, 1024, 128);
+                const uint64_t bh = bd0 + (uint64_t)((slot * DP_SLOT) >> 4);
+                const uint64_t bl = bh + (uint64_t)((NH * 32) >> 4);
+                const uint64_t ah = st == 0 ? adX : adA + (uint64_t)(c0 * (2048 >> 4));
+                const uint64_t al = ah + (uint64_t)((st == 0 ? 2048 : 32768) >> 4);
                 umma_ss2(acc, ah, bh, idesc, c0 > 0 ? 1u : 0u);
                 umma_ss2(acc, al, bh, idesc, 1u);
                 umma_ss2(acc, ah, bl, idesc, 1u);
                 umma_commit2(&empty[slot], 3);
                 if (c0 + 1 >= nk) umma_commit2(done, 3);
               }
-              if (mprof) m_issue += clock64() - t3;
-            } else {
-              if (elect_one_sync()) mbar_arrive_remote(&pfull[slot], 0);   // this CTA's half of the chunk has landed
+              __syncwarp();
+              if (mprof) { const long long t3 = clock64(); m_w += t2 - t1; m_issue += t3 - t2; }
+              if (++slot == DP_NSLOT) slot = 0;
             }
-            __syncwarp();
-            if (++slot == DP_NSLOT) { slot = 0; full_par ^= 1; }
           }
         }
       }
+      if (mprof && elect_one_sync()) { a.prof[8] = m_op; a.prof[9] = m_w; a.prof[10] = 0; a.prof[11] = m_issue; }
     }
-    if (mprof && elect_one_sync()) { a.prof[8] = m_op; a.prof[9] = m_full; a.prof[10] = m_pfull; a.prof[11] = m_issue; }
   } else if (warp == 9) {
     // ============================ weight loader (each CTA: its half of every chunk) ============================
     uint32_t slot = 0, empty_par = 1;

@@ -10,7 +10,7 @@
 
 constexpr int BP_ROWS = 64;
 constexpr int BP_THREADS = 320;
-constexpr int BP_NSLOT = 8;
+constexpr int BP_NSLOT = 11;
 constexpr int BP_SLOT = 8192;           // one K = 16 chunk of 128 outputs: bf16 hi (4 KB) | lo (4 KB)
 constexpr int BP_OFF_T0 = 0;            // [64 x 256] bf16 hi (32 KB) | lo (32 KB): parameter gradients A, then every hidden operand
 constexpr int BP_OFF_T1 = 65536;        // parameter gradients B
@@ -105,7 +105,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BP_THREADS, 1) tt_ba
 
   auto wait = [&](uint64_t* bar, uint32_t parity, int code) -> bool {
     for (uint32_t i = 0; i < (1u << 26); ++i) {
-      if (mbar_test_wait_cluster(bar, parity)) return true;
+      if (mbar_test_wait(bar, parity)) return true;
       if ((i & 1023) == 1023 && *abort_s) return false;
     }
     *abort_s = 1;
@@ -367,43 +367,71 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BP_THREADS, 1) tt_ba
     }
   } else if (warp == 8) {
     // ============================ MMA issuer (leader) / weight relay (peer) ============================
-    uint32_t op_par = 0, slot = 0, full_par = 0;
-    const uint32_t idesc256 = umma_idesc_bf16(TT_ROWS, 256), idesc16 = umma_idesc_bf16(TT_ROWS, 16);
-    const uint32_t aT0 = smem_u32(sT0), aT1 = smem_u32(sT1), aRing = smem_u32(ring);
     bool ok = true;
-    for (int tile = pair; tile < a.n_tiles && ok; tile += n_pairs) {
-      for (int l = s.L - 1; l >= 0 && ok; --l) {
-        for (int m = 0; m < 7 && ok; ++m) {          // FA^T, FB^T, Wb2^T, Wa2^T, Wb1^T, Wa1^T, W0^T
-          const int nk = m == 0 ? s.NA / 16 : (m == 1 ? s.NBn / 16 : (m == 6 ? 1 : 16));
-          const uint32_t abase = m == 1 ? aT1 : aT0;
-          if (m != 1 && rank == 0) {                 // FB^T follows FA^T at once: both tiles were written by the same stage
-            if (!(ok = wait(op_bar, op_par, 20 + m))) break;
-            op_par ^= 1;
-            tc_fence_after();
-          }
-          for (int c = 0; c < nk && ok; ++c) {
-            if (!(ok = wait(&full[slot], full_par, 31))) break;
-            if (rank == 0) {
-              if (!(ok = wait(&pfull[slot], full_par, 32))) break;
+    if (rank != 0) {
+      uint32_t slot = 0, full_par = 0;
+      const int per_tile = s.L * bp_layer_slots(s);
+      for (int tile = pair; tile < a.n_tiles && ok; tile += n_pairs)
+        for (int i = 0; i < per_tile && ok; ++i) {
+          if (!(ok = wait(&full[slot], full_par, 31))) break;
+          if (elect_one_sync()) mbar_arrive_remote(&pfull[slot], 0);   // this CTA's half of the chunk has landed
+          __syncwarp();
+          if (++slot == BP_NSLOT) { slot = 0; full_par ^= 1; }
+        }
+    } else {
+      uint32_t op_par = 0, slot = 0;
+      const uint32_t idesc256 = umma_idesc_bf16(TT_ROWS, 256), idesc16 = umma_idesc_bf16(TT_ROWS, 16);
+      const uint64_t ad0 = umma_smem_desc(smem_u32(sT0), 1024, 128), ad1 = umma_smem_desc(smem_u32(sT1), 1024, 128);
+      const uint64_t bd128 = umma_smem_desc(smem_u32(ring), 128 * 16, 128), bd8 = umma_smem_desc(smem_u32(ring), 128, 128);
+      // weights confirmed ahead of the issue pointer while the warp waits for operands (see pf_tc_pair.cuh)
+      uint32_t cslot = 0, cpar = 0;
+      int ready = 0;
+      auto confirm = [&]() {
+        while (ready < BP_NSLOT) {
+          if (!mbar_test_wait(&full[cslot], cpar) || !mbar_test_wait(&pfull[cslot], cpar)) break;
+          ++ready;
+          if (++cslot == BP_NSLOT) { cslot = 0; cpar ^= 1; }
+        }
+      };
+      for (int tile = pair; tile < a.n_tiles && ok; tile += n_pairs) {
+        for (int l = s.L - 1; l >= 0 && ok; --l) {
+          for (int m = 0; m < 7 && ok; ++m) {          // FA^T, FB^T, Wb2^T, Wa2^T, Wb1^T, Wa1^T, W0^T
+            const int nk = m == 0 ? s.NA / 16 : (m == 1 ? s.NBn / 16 : (m == 6 ? 1 : 16));
+            const uint64_t ad = m == 1 ? ad1 : ad0;
+            if (m != 1) {                               // FB^T follows FA^T at once: both tiles were written by the same stage
+              bool got = false;
+              for (uint32_t i = 0; i < (1u << 26); ++i) {
+                if (mbar_test_wait(op_bar, op_par)) { got = true; break; }
+                confirm();
+                if ((i & 1023) == 1023 && *abort_s) break;
+              }
+              if (!got) { if (!*abort_s) { *abort_s = 1; raise_flag(a.err, 20 + m); } ok = false; break; }
+              op_par ^= 1;
+            }
+            for (int c = 0; c < nk && ok; ++c) {
+              if (ready == 0) {
+                if (!(ok = wait(&full[cslot], cpar, 31))) break;
+                if (!(ok = wait(&pfull[cslot], cpar, 32))) break;
+                ++ready;
+                if (++cslot == BP_NSLOT) { cslot = 0; cpar ^= 1; }
+              }
+              --ready;
               tc_fence_after();
-              const uint32_t bbase = aRing + slot * BP_SLOT;
               if (elect_one_sync()) {
+                const uint64_t soff = (uint64_t)((slot * BP_SLOT) >> 4);
                 if (m < 6) {
-                  const uint64_t bh = umma_smem_desc(bbase, 128 * 16, 128);
-                  const uint64_t bl = umma_smem_desc(bbase + 4096u, 128 * 16, 128);
-                  const uint64_t ah = umma_smem_desc(abase + (uint32_t)c * 2048u, 1024, 128);
-                  const uint64_t al = umma_smem_desc(abase + 32768u + (uint32_t)c * 2048u, 1024, 128);
+                  const uint64_t bh = bd128 + soff, bl = bh + (4096 >> 4);
+                  const uint64_t ah = ad + (uint64_t)(c * (2048 >> 4)), al = ah + (32768 >> 4);
                   umma_ss2(tmem, ah, bh, idesc256, (m == 1 || c > 0) ? 1u : 0u);
                   umma_ss2(tmem, al, bh, idesc256, 1u);
                   umma_ss2(tmem, ah, bl, idesc256, 1u);
                   umma_commit2(&empty[slot], 3);
                   if (m != 0 && c + 1 >= nk) umma_commit2(acc_bar, 3);
                 } else {
+#pragma unroll 4
                   for (int cc = 0; cc < 16; ++cc) {
-                    const uint64_t bh = umma_smem_desc(bbase + (uint32_t)cc * 512u, 128, 128);
-                    const uint64_t bl = umma_smem_desc(bbase + (uint32_t)cc * 512u + 256u, 128, 128);
-                    const uint64_t ah = umma_smem_desc(aT0 + (uint32_t)cc * 2048u, 1024, 128);
-                    const uint64_t al = umma_smem_desc(aT0 + 32768u + (uint32_t)cc * 2048u, 1024, 128);
+                    const uint64_t bh = bd8 + soff + (uint64_t)(cc * (512 >> 4)), bl = bh + (256 >> 4);
+                    const uint64_t ah = ad0 + (uint64_t)(cc * (2048 >> 4)), al = ah + (32768 >> 4);
                     umma_ss2(tmem, ah, bh, idesc16, cc > 0 ? 1u : 0u);
                     umma_ss2(tmem, al, bh, idesc16, 1u);
                     umma_ss2(tmem, ah, bl, idesc16, 1u);
@@ -412,11 +440,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BP_THREADS, 1) tt_ba
                   umma_commit2(acc_bar, 3);
                 }
               }
-            } else {
-              if (elect_one_sync()) mbar_arrive_remote(&pfull[slot], 0);
+              __syncwarp();
+              if (++slot == BP_NSLOT) slot = 0;
             }
-            __syncwarp();
-            if (++slot == BP_NSLOT) { slot = 0; full_par ^= 1; }
           }
         }
       }
