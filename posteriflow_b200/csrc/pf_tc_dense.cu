@@ -46,6 +46,7 @@ struct DnState {
   uint8_t* image;    // [L][layer_bytes]   bf16(W)
   uint8_t* image3;   // [L][layer_bytes3]  bf16 hi | lo of W, chunk by chunk (split tier and training forward)
   uint8_t* imagep;   // [L][2][DP_LAYER_BYTES]  pair form of image3 (pf_tc_pair.cuh), NULL when the pair kernel is off
+  uint8_t* image2;   // [L][2][D2_LAYER_BYTES]  pair form of image (pf_tc_pair2.cuh: inference, two tiles in flight), or NULL
   long long* prof;
 };
 
@@ -772,6 +773,7 @@ __global__ void __launch_bounds__(DN_THREADS, 1) tc_dense_forward_kernel(const D
 }
 
 #include "pf_tc_pair.cuh"
+#include "pf_tc_pair2.cuh"
 
 }  // namespace pf
 using namespace pf;
@@ -828,9 +830,13 @@ pf_status pf_dn_pack(pf_flow* f, cudaStream_t st) {
     const char* pp = getenv("PF_TRAIN_PAIR");
     const bool pair_on = s.D == 11 && f->sm_count >= 2 && !(pp && pp[0] == '0');
     if (e == cudaSuccess && pair_on) e = cudaMalloc(&t->imagep, (size_t)s.L * 2 * DP_LAYER_BYTES);
+    const char* p2 = getenv("PF_DENSE_PAIR");
+    const bool pair2_on = s.D == 11 && f->sm_count >= 2 && p2 && p2[0] == '1';   // opt-in: +4 % only (profiles/experiments/r02_dense_pair2.md)
+    if (e == cudaSuccess && pair2_on) e = cudaMalloc(&t->image2, (size_t)s.L * 2 * D2_LAYER_BYTES);
     if (e != cudaSuccess) {
       if (t->image) cudaFree(t->image);
       if (t->image3) cudaFree(t->image3);
+      if (t->imagep) cudaFree(t->imagep);
       delete t;
       return cuda_fail(e, "dense density image allocation", __FILE__, __LINE__);
     }
@@ -845,6 +851,10 @@ pf_status pf_dn_pack(pf_flow* f, cudaStream_t st) {
     dp_pack_kernel<<<dim3(DP_PACK_SLOTS, s.L, 2), 256, 0, st>>>(s, t->imagep, f->W0, f->Wa, f->Wb, f->Wf);
     PF_LAUNCH_CHECK(f);
   }
+  if (t->image2) {
+    d2_pack_kernel<<<dim3(2 + 7 * 16, s.L, 2), 256, 0, st>>>(s, t->image2, f->W0, f->Wa, f->Wb, f->Wf);
+    PF_LAUNCH_CHECK(f);
+  }
   PF_TRY(pf_tt_pack(f, st));   // backward images of the fused training step (pf_tc_train.cu)
   return PF_OK;
 }
@@ -856,6 +866,7 @@ void pf_dn_destroy(pf_flow* f) {
   cudaFree(t->image);
   cudaFree(t->image3);
   if (t->imagep) cudaFree(t->imagep);
+  if (t->image2) cudaFree(t->image2);
   if (t->prof) cudaFree(t->prof);
   delete t;
   f->dense = nullptr;
@@ -939,7 +950,19 @@ pf_status pf_dn_forward(pf_flow* f, cudaStream_t st, const float* x, const float
     a.err = err;
     a.prof = t->prof;
     if (split == 3) PF_TRY((dn_launch<3, false>(f, st, a)));
-    else PF_TRY((dn_launch<1, false>(f, st, a)));
+    else if (t->image2) {     // bf16 operands: CTA pairs, two tiles in flight per pair
+      static bool attr_done[64] = {};
+      const int dev = f->desc.device;
+      if (dev < 64 && !attr_done[dev]) {
+        PF_CUDA(cudaFuncSetAttribute(tc_dense_pair2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, D2_SMEM));
+        attr_done[dev] = true;
+      }
+      a.image = t->image2;
+      const int n_super = (a.n_tiles + 1) / 2;
+      const int pairs = n_super < f->sm_count / 2 ? n_super : f->sm_count / 2;
+      tc_dense_pair2_kernel<<<2 * pairs, D2_THREADS, D2_SMEM, st>>>(a);
+      PF_LAUNCH_CHECK(f);
+    } else PF_TRY((dn_launch<1, false>(f, st, a)));
   }
   dn_prof_report(f, t, st);
   return PF_OK;
