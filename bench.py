@@ -427,6 +427,28 @@ def run_ours(args):
                 "roofline_frac_burst": tf_full / float(peaks()[0]["bf16_tflops"]),
                 "kernels": "split-bf16 tcgen05 GEMMs (calls of >= 512 rows)" if args.tier == "bf16" else "FP32-FMA GEMMs"}
 
+    # the same full step with the flow's parameters re-homed in ONE flat buffer (GraphedNLLStep.flatten_parameters):
+    # clip + AdamW touch two tensors instead of 181.  Measured last: it moves the parameters' storage.
+    flat = gstep.flatten_parameters()
+    opt_flat = torch.optim.AdamW([flat] + other_params, lr=0.0, weight_decay=0.0, fused=True)
+
+    def step_train_flat(i):
+        loss = step_train(i)
+        gstep.clip_grad_norm_(5.0, other_params)
+        opt_flat.step()
+        return loss
+
+    ms_train_flat, _ = timed(step_train_flat, args.steps, args.warmup)
+    ms_full_flat = None
+    if full is not None:
+        def step_train_full_flat(i):
+            loss = step_train_full(i)
+            gstep.clip_grad_norm_(5.0, other_params)
+            opt_flat.step()
+            return loss
+        ms_full_flat, _ = timed(step_train_full_flat, args.steps, args.warmup)
+        full["e2e_flat_ms"] = ms_full_flat / args.steps
+
     pk, pk_kind = peaks()
     rows_s = R * world * args.steps / (ms * 1e-3)
     flop_row = F_X + F_CTX / n
@@ -505,6 +527,10 @@ def run_ours(args):
                   "e2e_includes": "flow-only step + torch.nn.utils.clip_grad_norm_(5.0) + fused AdamW.step() over all flow "
                                   "+ rank-embedding parameters + the re-pack of the updated weights (train_lean_npe.py:363-368); "
                                   "lr = 0 keeps the benchmarked weights fixed while every tensor is rewritten in place",
+                  "e2e_flat_ms": ms_train_flat / args.steps,
+                  "e2e_flat_includes": "the same step through GraphedNLLStep.flatten_parameters(): flow parameters as views "
+                                       "of one flat buffer, GraphedNLLStep.clip_grad_norm_(5.0) + fused AdamW over [flat, rank "
+                                       "embedding] + the re-pack (same arithmetic as e2e_ms; tests/test_gpu_round2.py)",
                   "repack_ms": ms_pack / args.steps, "repack_launches": int(launches_pack // max(1, args.steps)),
                   "ms_per_step_eager_autograd": ms_train_eager / args.steps,
                   "full_batch_1gpu": full,

@@ -167,6 +167,12 @@ class NSFPosteriorFlow(nn.Module):
             self._handle = ops.FlowHandle(self.features, self.context_features, self.hidden_features,
                                           self.num_layers, self.num_bins, self.tail_bound, FLOW_NORM_BOUND,
                                           self.tier, dev)
+        fp = getattr(self, "_flat_param", None)
+        if fp is not None and fp._version != self._flat_seen:
+            # GraphedNLLStep.flatten_parameters(): the optimizer writes the flat buffer the parameters alias -- their own
+            # version counters do not move, so the pack key is bumped here
+            self._flat_seen = fp._version
+            self._handle.pack_key = None
         self._handle.ensure_packed(w)
         return self._handle
 

@@ -100,6 +100,7 @@ class GraphedNLLStep:
         self.flow_params = model.flow.layer_weights()
         self._gbuf = None
         self.flat_grad = None
+        self.flat_param = None
         self.last_launches = 0
 
     def _capture(self, cap: int):
@@ -149,8 +150,9 @@ class GraphedNLLStep:
             return bool(self.slots)
         if not self.model.flow.handle().fused_training:      # GEMM-per-launch kernels: more rows = more time
             return False
+        # one wave of tiles: the chain kernels give every 128-row tile a PAIR of SMs (csrc/pf_tc_pair.cuh)
         n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
-        return B * int(self.model.max_signals) <= 128 * n_sm
+        return B * int(self.model.max_signals) <= 128 * (n_sm // 2)
 
     def _capture_slots(self, B: int, ctx_requires_grad: bool):
         import math
@@ -244,7 +246,29 @@ class GraphedNLLStep:
             context.backward(st["gcontext"])
         return st["loss"].detach()
 
+    def _ensure_packed(self):
+        """re-pack if an optimizer step changed the weights (the cached parameter list skips NSFPosteriorFlow.handle()'s
+        per-call walk over the module tree: ~0.3 ms of host time per step)"""
+        flow = self.model.flow
+        fh = flow._handle
+        if fh is None or fh.device != self.flow_params[0].device:
+            return flow.handle()
+        fp = self.flat_param
+        if fp is not None and fp._version != flow._flat_seen:      # flat mode: the optimizer wrote the flat buffer
+            flow._flat_seen = fp._version
+            fh.pack_key = None
+        fh.ensure_packed(self.flow_params)
+        return fh
+
     def _assign_flow_grads(self):
+        if self.flat_param is not None:
+            # flat-parameter mode: every step is a fresh gradient; the optimizer owns `flat_param` only
+            self.flat_grad.copy_(self.flat_step)
+            self.flat_param.grad = self.flat_grad
+            if self.flow_params[0].grad is not self._gbuf[0]:
+                for p, v in zip(self.flow_params, self._gbuf):
+                    p.grad = v
+            return
         fresh = [i for i, p in enumerate(self.flow_params) if p.requires_grad and p.grad is None]
         if len(fresh) == len(self.flow_params):
             # the usual step (zero_grad(set_to_none=True) before it): ONE flat copy, then .grad = the views
@@ -278,11 +302,7 @@ class GraphedNLLStep:
     def __call__(self, params: Tensor, nsig: Tensor, context: Tensor) -> Tensor:
         m = self.model
         if context.is_cuda:
-            fh0 = m.flow._handle
-            if fh0 is None or fh0.device != self.flow_params[0].device:
-                m.flow.handle()
-            else:
-                fh0.ensure_packed(self.flow_params)
+            self._ensure_packed()
             if self._use_slots(int(context.shape[0]), context.device):
                 return self._call_slots(params, nsig.to(context.device), context)
         event, rank = signal_rows(nsig.to(context.device), int(m.max_signals))
@@ -304,11 +324,7 @@ class GraphedNLLStep:
             return context.sum() * 0.0
         # re-pack if an optimizer step changed the weights (the cached parameter list skips NSFPosteriorFlow.handle()'s
         # per-call walk over the module tree: ~0.3 ms of host time per step)
-        fh = m.flow._handle
-        if fh is None or fh.device != self.flow_params[0].device:
-            m.flow.handle()
-        else:
-            fh.ensure_packed(self.flow_params)
+        self._ensure_packed()
         cap = (R + self.bucket - 1) // self.bucket * self.bucket
         st = self.graphs.get(cap)
         if st is None:
@@ -336,6 +352,51 @@ class GraphedNLLStep:
         if ctx_full.requires_grad:
             ctx_full.backward(st["gctx"][:R])
         return st["loss"].detach()
+
+    def flatten_parameters(self) -> torch.nn.Parameter:
+        """Re-home every flow parameter as a view of ONE flat fp32 buffer (the layout of `flat_grad`) and return that
+        buffer as a Parameter whose `.grad` is the flat gradient buffer.  An optimizer built over
+        `[step.flatten_parameters(), *other_params]` and `step.clip_grad_norm_()` then touch one tensor instead of 180:
+        the reference's `clip_grad_norm_(model.parameters(), 5.0)` + `AdamW.step()` cost 0.54 + 0.47 ms of host-bound
+        multi-tensor work per step (scripts/prof_opt.py) next to a 1.26 ms flow step; on the flat buffer they are
+        0.04 + ~0.05 ms.  AdamW is elementwise, so the update is the same numbers (one weight decay for all tensors, as
+        `train_lean_npe.py` builds it).  The module's own parameters stay valid (they alias the buffer: state_dict,
+        sampling and `.grad` per tensor all keep working); every step is a fresh gradient (no accumulation across calls
+        in this mode).  Call after the model is on its device."""
+        if self.flat_param is None:
+            self._ensure_flat()
+            flat = torch.empty_like(self.flat_grad)
+            o = 0
+            with torch.no_grad():
+                for p in self.flow_params:
+                    v = flat[o:o + p.numel()].view(p.shape)
+                    v.copy_(p.data)
+                    p.data = v
+                    o += p.numel()
+            self.graphs.clear()              # graphs captured before the move hold the old parameter tensors
+            self.slot_graphs.clear()
+            self.flat_param = torch.nn.Parameter(flat, requires_grad=True)
+            self.flat_param.grad = self.flat_grad
+            self._flat_seen = self.flat_param._version
+            # NSFPosteriorFlow.handle() re-packs when the flat buffer is written.  object.__setattr__: a plain attribute,
+            # NOT a registered parameter of the module (state_dict / named_parameters stay the reference's)
+            object.__setattr__(self.model.flow, "_flat_param", self.flat_param)
+            object.__setattr__(self.model.flow, "_flat_seen", self.flat_param._version)
+        return self.flat_param
+
+    def clip_grad_norm_(self, max_norm: float, extra_params=()) -> Tensor:
+        """`torch.nn.utils.clip_grad_norm_` over the flow's flat gradient buffer (+ `extra_params`): same total norm and
+        the same scaling, two small kernels for the flow instead of a 180-tensor multi-tensor pass."""
+        sq = torch.linalg.vector_norm(self.flat_grad).square()
+        extra = [p.grad for p in extra_params if p.grad is not None]
+        for gde in extra:
+            sq = sq + torch.linalg.vector_norm(gde).square()
+        total = sq.sqrt()
+        coef = torch.clamp(max_norm / (total + 1e-6), max=1.0)
+        self.flat_grad.mul_(coef)
+        for gde in extra:
+            gde.mul_(coef)
+        return total
 
     def allreduce(self, extra_params=()) -> int:
         """Data-parallel gradient exchange after a step: ONE all-reduce (sum) of the flat flow-gradient

@@ -505,3 +505,100 @@ def test_split_tier_trains_on_the_fused_kernels():
     # ORDER (and with it the last fp32 bits) differs from launch to launch
     for a, b in zip(grads["bf16"], grads["bf16x3"]):
         assert float((a - b).abs().max()) <= 1e-5 * float(a.abs().max())
+
+
+# ------------------------------------------------------------------------------------------------
+# CTA-pair chain kernels (tcgen05 cta_group::2) against the one-CTA kernels they replace
+# ------------------------------------------------------------------------------------------------
+def test_pair_kernels_equal_the_one_cta_kernels_beyond_one_wave(monkeypatch):
+    """The fused training step runs its forward / backward chain kernels on CTA pairs by default (64 rows of a tile per
+    CTA); PF_TRAIN_PAIR=0 (read at the first pack of a handle) keeps the one-CTA kernels.  Same operands, same products,
+    different instruction forms: results agree to fp32 accumulation order.  9 637 rows = 76 tiles: more tiles than the
+    74 pairs of a B200 (persistent loop wraps), last tile ragged (37 rows: the second CTA of its pair holds no row)."""
+    spec, w, g = load_golden("lean_default")
+    gen = torch.Generator().manual_seed(77)
+    R = 9637
+    x0 = (torch.rand(R, spec.features, generator=gen) * 2 - 1).cuda()
+    c0 = torch.randn(R, spec.context_features, generator=gen).cuda()
+    out = {}
+    for pair in ("1", "0"):
+        monkeypatch.setenv("PF_TRAIN_PAIR", pair)
+        flow = make_flow(spec, w, "cuda", tier="bf16")
+        assert flow.handle().fused_training
+        x = x0.clone().requires_grad_(True)
+        ctx = c0.clone().requires_grad_(True)
+        nll = flow.compute_psd_aware_nll(x, ctx, None)
+        (nll.sum() / R).backward()
+        flow.handle().check()
+        grads = [p.grad.clone() for p in flow.layer_weights()]
+        out[pair] = (nll.detach().clone(), x.grad.clone(), ctx.grad.clone(), grads)
+        del flow
+    a, b = out["1"], out["0"]
+    assert bool(torch.isfinite(a[0]).all())
+    assert float((a[0] - b[0]).abs().max()) <= 1e-4 * float(b[0].abs().max())
+    for k in (1, 2):
+        assert float((a[k] - b[k]).abs().max()) <= 1e-4 * float(b[k].abs().max()), k
+    worst = 0.0
+    for ga, gb in zip(a[3], b[3]):
+        worst = max(worst, float((ga - gb).abs().max()) / max(1e-12, float(gb.abs().max())))
+    assert worst <= 1e-3, worst           # weight gradients: sums over 9 637 rows of bf16 products, order differs per tile
+
+
+def test_flat_parameter_mode_matches_the_per_tensor_optimizer_path():
+    """GraphedNLLStep.flatten_parameters(): clip + AdamW over ONE flat tensor (+ the rank embedding) must move the weights
+    exactly as the reference's clip_grad_norm_(model.parameters(), 5.0) + AdamW over 181 tensors does, and every later
+    call -- through the step or straight through the flow -- must see the updated weights (re-pack keyed on the flat
+    buffer's version: the aliasing parameters' own counters do not move)."""
+    import posteriflow_b200 as P
+    spec = O.FlowSpec()
+    w = O.init_weights(spec, seed=4, stress=False)
+    rank_w = torch.randn(5, 32, generator=torch.Generator().manual_seed(9))
+
+    def build():
+        m = P.LeanNPE(tier="bf16")
+        m.flow.load_state_dict(O.full_state_dict(spec, w), strict=True)
+        with torch.no_grad():
+            m.rank_embed.weight.copy_(rank_w)
+        return m.to("cuda")
+
+    ma, mb = build(), build()
+    sa, sb = P.GraphedNLLStep(ma), P.GraphedNLLStep(mb)
+    flat = sa.flatten_parameters()
+    assert all(p.data_ptr() >= flat.data_ptr() and p.data_ptr() < flat.data_ptr() + 4 * flat.numel() for p in sa.flow_params)
+    opt_a = torch.optim.AdamW([flat, ma.rank_embed.weight], lr=2e-3, weight_decay=1e-4, fused=True)
+    pb = [p for p in list(mb.flow.parameters()) + list(mb.rank_embed.parameters()) if p.requires_grad]
+    opt_b = torch.optim.AdamW(pb, lr=2e-3, weight_decay=1e-4, fused=True)
+    gen = torch.Generator().manual_seed(41)
+    sc = O.Scaler()
+    probe_x = (torch.rand(64, 11, generator=gen) * 2 - 1).cuda()
+    probe_c = torch.randn(64, 288, generator=gen).cuda()
+    for it in range(3):
+        B = 40
+        nsig = (torch.multinomial(torch.tensor([.55, .20, .12, .08, .05]), B, replacement=True, generator=gen) + 1).cuda()
+        params = sc.denormalize(torch.rand(B, 5, 11, generator=gen) * 2 - 1).cuda()
+        ctx = torch.randn(B, 256, generator=gen).cuda()
+        opt_a.zero_grad(set_to_none=True)
+        ma.rank_embed.weight.grad = None
+        la = sa(params, nsig, ctx)
+        na = sa.clip_grad_norm_(5.0, [ma.rank_embed.weight])
+        opt_a.step()
+        opt_b.zero_grad(set_to_none=True)
+        lb = sb(params, nsig, ctx)
+        nb = torch.nn.utils.clip_grad_norm_(pb, 5.0)
+        opt_b.step()
+        assert abs(float(la) - float(lb)) <= 1e-5 * max(1.0, abs(float(lb))), (it, float(la), float(lb))
+        assert abs(float(na) - float(nb)) <= 1e-4 * float(nb), (it, float(na), float(nb))
+        for (n1, p1), (n2, p2) in zip(ma.flow.named_parameters(), mb.flow.named_parameters()):
+            # Adam normalises every entry: one whose gradient is ~eps may move differently when the two runs' atomically
+            # accumulated gradients differ in the last bit -- the median entry must agree to rounding, the worst closely
+            d = (p1 - p2).abs()
+            assert float(d.median()) <= 1e-7 and float(d.max()) <= 2e-4, (it, n1, float(d.median()), float(d.max()))
+        # straight through the flow (not through the step): the updated weights must be the packed ones
+        with torch.no_grad():
+            za, _ = ma.flow.forward(probe_x, probe_c)
+            zb, _ = mb.flow.forward(probe_x, probe_c)
+        assert float((za - zb).abs().max()) <= 5e-3 * max(1.0, float(zb.abs().max())), it
+    # and the weights did move
+    w0 = O.full_state_dict(spec, w)
+    k0 = next(k for k in w0 if k.endswith("final_layer.weight"))
+    assert float((ma.flow.state_dict()[k0].cpu() - w0[k0]).abs().max()) > 1e-4
