@@ -206,6 +206,29 @@ __device__ __forceinline__ void tmem_store_words(uint32_t dst, const uint32_t* w
   tmem_wait_st();
 }
 
+// NWO consecutive bf16x2 words of one row into an operand array in the UMMA K-major no-swizzle layout (16 bytes of a row per
+// 8-column group, groups 2048 bytes apart), starting at word A4 of a 16-byte row chunk: 16- / 8-byte stores wherever the
+// alignment allows.  Word-by-word, every store of a warp hit 8 banks four times over (rows are 16 bytes apart): 7 stores =
+// 28 shared-memory wavefronts per thread group against ~8 here.  All indices are compile-time (no local memory).
+template <int A4, int NWO>
+__device__ __forceinline__ void store_words_umma(uint8_t* p /* first word's address */, const uint32_t* w) {
+  constexpr int HEAD = (4 - A4) < NWO ? (4 - A4) : NWO;
+  if (HEAD == 4) *reinterpret_cast<uint4*>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+  else if (HEAD == 3) { *reinterpret_cast<uint32_t*>(p) = w[0]; *reinterpret_cast<uint2*>(p + 4) = make_uint2(w[1], w[2]); }
+  else if (HEAD == 2) *reinterpret_cast<uint2*>(p) = make_uint2(w[0], w[1]);
+  else *reinterpret_cast<uint32_t*>(p) = w[0];
+  uint8_t* q = p - 4 * A4 + 2048;           // word 0 of the next column group
+  constexpr int FULL = (NWO - HEAD) / 4, REM = (NWO - HEAD) % 4;
+#pragma unroll
+  for (int c = 0; c < FULL; ++c)
+    *reinterpret_cast<uint4*>(q + 2048 * c) = make_uint4(w[HEAD + 4 * c], w[HEAD + 4 * c + 1], w[HEAD + 4 * c + 2], w[HEAD + 4 * c + 3]);
+  uint8_t* r = q + 2048 * FULL;
+  constexpr int I = HEAD + 4 * FULL;
+  if (REM == 3) { *reinterpret_cast<uint2*>(r) = make_uint2(w[I], w[I + 1]); *reinterpret_cast<uint32_t*>(r + 8) = w[I + 2]; }
+  else if (REM == 2) *reinterpret_cast<uint2*>(r) = make_uint2(w[I], w[I + 1]);
+  else if (REM == 1) *reinterpret_cast<uint32_t*>(r) = w[I];
+}
+
 struct RegQ {
   const float* q;
   __device__ __forceinline__ float operator()(int i) const { return q[i]; }
@@ -315,11 +338,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_sampler_kernel(const TcArgs 
     };
     auto store_smem = [&](uint8_t* arr, int slot0, const uint32_t* w) {
       const uint32_t b0 = (uint32_t)slot0 * 2 + 4 * wo;
-#pragma unroll
-      for (int i = 0; i < NWH; ++i) {
-        if (i < nwo) {
-          const uint32_t bo = b0 + 4 * i;
-          *reinterpret_cast<uint32_t*>(arr + (bo >> 4) * 2048 + rowoff + (bo & 15)) = w[i];
+      uint8_t* p = arr + (b0 >> 4) * 2048 + rowoff + (b0 & 15);
+      constexpr int N0 = NWH, N1 = NW - NWH;
+      if (half == 0) {
+        switch ((b0 >> 2) & 3) {
+          case 0: store_words_umma<0, N0>(p, w); break;
+          case 1: store_words_umma<1, N0>(p, w); break;
+          case 2: store_words_umma<2, N0>(p, w); break;
+          default: store_words_umma<3, N0>(p, w); break;
+        }
+      } else {
+        switch ((b0 >> 2) & 3) {
+          case 0: store_words_umma<0, N1>(p, w); break;
+          case 1: store_words_umma<1, N1>(p, w); break;
+          case 2: store_words_umma<2, N1>(p, w); break;
+          default: store_words_umma<3, N1>(p, w); break;
         }
       }
       fence_proxy_async_smem();
