@@ -220,14 +220,24 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(DP_THREADS, 1) tc_de
         // ---- five hidden stages: I, A1, B1, A2, B2 ----
 #pragma unroll 1
         for (int st = 0; st < 5 && ok; ++st) {
-          if (!(ok = wait(acc_bar, acc_par, 10 + st))) break;
-          mark(1);
-          acc_par ^= 1;
-          tc_fence_after();
           const bool res = (st == 0 || st == 2 || st == 4);
           const float* bias = cst + st * DN_H;
           const int sec = st == 0 ? 0 : (st == 2 ? 1 : 2);
           uint8_t* gimg = a.sv.img + dn_img_off(l, st, tile, a.sv.tiles);
+          // the row's context terms / gates of a 32-column block (global memory, one 128-byte line per column and warp):
+          // independent of the accumulator, so the first block's are loaded BEFORE the wait on the tensor pipe and the
+          // second block's while the first block's operand words are being stored
+          float g[32];
+          auto load_gates = [&](int c0) {
+            const float* pg = plt + (size_t)(sec * DN_H + c0) * DN_ROWS;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) g[i] = __ldg(pg + (size_t)i * DN_ROWS);
+          };
+          if (res) load_gates(gcol0);
+          if (!(ok = wait(acc_bar, acc_par, 10 + st))) break;
+          mark(1);
+          acc_par ^= 1;
+          tc_fence_after();
 #pragma unroll 1
           for (int b = 0; b < 2; ++b) {
             const int c0 = gcol0 + 32 * b;                       // hidden units c0 .. c0 + 31
@@ -244,10 +254,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(DP_THREADS, 1) tc_de
                 o[i + 2] = fmaf(__uint_as_float(v[i + 2]), ASC, t4.z); o[i + 3] = fmaf(__uint_as_float(v[i + 3]), ASC, t4.w);
               }
             } else {
-              float g[32];
-              const float* pg = plt + (size_t)(sec * DN_H + c0) * DN_ROWS;
-#pragma unroll
-              for (int i = 0; i < 32; ++i) g[i] = __ldg(pg + (size_t)i * DN_ROWS);
               if (st == 0) {                  // h0 = acc + b0 + relu(c0)
                 tmem_wait_ld();
 #pragma unroll
@@ -265,6 +271,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(DP_THREADS, 1) tc_de
               for (int i = 0; i < 32; ++i) ow[i] = __float_as_uint(o[i]);
               tmem_st16(tl + 128 + tc, ow);
               tmem_st16(tl + 128 + tc + 16, ow + 16);
+              if (b == 0) load_gates(c0 + 32);
             }
 #pragma unroll
             for (int i = 0; i < 4; ++i) {

@@ -242,10 +242,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BP_THREADS, 1) tt_ba
         // k = 4: d h0 = residual + [h0 > 0] acc (operand), relu(context) gradient
 #pragma unroll 1
         for (int k = 0; k < 5 && ok; ++k) {
-          if (!(ok = wait(acc_bar, acc_par, 52 + k))) break;
-          acc_par ^= 1;
-          tc_fence_after();
-          mark(2);
           const bool res_in = (k == 2 || k == 4), gate = (k == 0 || k == 2), has_mask = k >= 1;
           const int mimg = k == 1 ? TT_A_U2 : (k == 2 ? TT_A_H1 : (k == 3 ? TT_A_U1 : TT_A_H0));
           const uint8_t* mbase = a.img + tt_img_off(l, mimg, TT_NA, tile, a.n_tiles);
@@ -254,15 +250,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BP_THREADS, 1) tt_ba
           const uint8_t* vlbase = a.img + tt_img_off(l, vimg + 1, TT_NA, tile, a.n_tiles);
           const int sec = k == 0 ? 2 : (k == 2 ? 1 : 0);
           uint8_t* gout = a.gimg + tt_img_off(l, TT_G_V2 + k, TT_NG, tile, a.n_tiles);
-#pragma unroll 1
-          for (int b = 0; b < 2; ++b) {
-            const int c0 = gcol0 + 32 * b;
-            const uint32_t tc = (uint32_t)(tcol0 + 32 * b);
-            uint32_t v[32], hr[32];
-            tmem_ld32(tl + tc, v);
-            if (res_in) tmem_ld32(tl + 128 + tc, hr);
-            uint32_t mkw[16], vhw[16], vlw[16];      // 32 bf16 each: relu mask source, pre-gate value hi / lo
-            float g[32];
+          uint32_t mkw[16], vhw[16], vlw[16];      // 32 bf16 each: relu mask source, pre-gate value hi / lo
+          float g[32];
+          // what a 32-column block reads from the forward's saves: independent of the accumulator, so the FIRST block's
+          // loads are issued before the wait on the tensor pipe (their L2 round trip runs under the MMAs)
+          auto load_saved = [&](int c0) {
             if (has_mask) {
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
@@ -283,6 +275,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BP_THREADS, 1) tt_ba
 #pragma unroll
               for (int i = 0; i < 32; ++i) g[i] = __ldg(projr + (size_t)(sec * TT_H + c0 + i) * TT_ROWS);
             }
+          };
+          load_saved(gcol0);
+          if (!(ok = wait(acc_bar, acc_par, 52 + k))) break;
+          acc_par ^= 1;
+          tc_fence_after();
+          mark(2);
+#pragma unroll 1
+          for (int b = 0; b < 2; ++b) {
+            const int c0 = gcol0 + 32 * b;
+            const uint32_t tc = (uint32_t)(tcol0 + 32 * b);
+            uint32_t v[32], hr[32];
+            tmem_ld32(tl + tc, v);
+            if (res_in) tmem_ld32(tl + 128 + tc, hr);
             tmem_wait_ld();
             float o[32];
 #pragma unroll
@@ -322,6 +327,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BP_THREADS, 1) tt_ba
               store_image(a.gimg + tt_img_off(l, TT_G_C0, TT_NG, tile, a.n_tiles),
                           a.gimg + tt_img_off(l, TT_G_C0L, TT_NG, tile, a.n_tiles), c0, gc);
             }
+            if (b == 0) load_saved(c0 + 32);   // the second block's saves: in flight while this block's operand words are stored
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               uint4 w4, l4;
