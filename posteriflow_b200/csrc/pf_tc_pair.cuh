@@ -98,9 +98,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(DP_THREADS, 1) tc_de
   float* ybuf = reinterpret_cast<float*>(smem + DP_OFF_Y);
   float* red = reinterpret_cast<float*>(smem + DP_OFF_RED);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + DP_OFF_BAR);
-  uint64_t* full = bars;                       // [NSLOT] this CTA's half of a weight chunk landed
+  uint64_t* full = bars;                       // [NSLOT] weight chunk landed: this CTA's half -- and, in the leader, the peer's
+                                               // (second arrival, relayed by the peer's warp 8: one barrier to poll per chunk)
   uint64_t* empty = bars + DP_NSLOT;           // [NSLOT] the pair's MMAs reading the slot completed (multicast commit)
-  uint64_t* pfull = bars + 2 * DP_NSLOT;       // [NSLOT] leader only: the peer's half landed (relayed by the peer's warp 8)
   uint64_t* acc_bar = bars + 3 * DP_NSLOT;     // hidden-stage accumulator complete (multicast commit)
   uint64_t* accf_bar = acc_bar + 1;            // [3] final stages FA, FB, FC
   uint64_t* op_bar = acc_bar + 4;              // leader only: operands of the next stage written, 8 + 8 warp arrivals
@@ -112,7 +112,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(DP_THREADS, 1) tc_de
   const uint32_t rank = cluster_cta_rank();
   const int n_pairs = (int)(gridDim.x >> 1), pair = (int)(blockIdx.x >> 1);
   if (tid == 0) {
-    for (int i = 0; i < DP_NSLOT; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); mbar_init(&pfull[i], 1); }
+    for (int i = 0; i < DP_NSLOT; ++i) { mbar_init(&full[i], rank == 0 ? 2 : 1); mbar_init(&empty[i], 1); }
     mbar_init(acc_bar, 1);
     for (int i = 0; i < 3; ++i) mbar_init(&accf_bar[i], 1);
     mbar_init(op_bar, 16);
@@ -400,7 +400,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(DP_THREADS, 1) tc_de
       for (int tile = pair; tile < a.n_tiles && ok; tile += n_pairs)
         for (int i = 0; i < s.L * DP_PACK_SLOTS && ok; ++i) {
           if (!(ok = wait(&full[slot], full_par, 31))) break;
-          if (elect_one_sync()) mbar_arrive_remote(&pfull[slot], 0);
+          if (elect_one_sync()) mbar_arrive_remote(&full[slot], 0);
           __syncwarp();
           if (++slot == DP_NSLOT) { slot = 0; full_par ^= 1; }
         }
@@ -420,7 +420,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(DP_THREADS, 1) tc_de
       int ready = 0;
       auto confirm = [&]() {
         while (ready < DP_NSLOT) {
-          if (!mbar_test_wait(&full[cslot], cpar) || !mbar_test_wait(&pfull[cslot], cpar)) break;
+          if (!mbar_test_wait(&full[cslot], cpar)) break;
           ++ready;
           if (++cslot == DP_NSLOT) { cslot = 0; cpar ^= 1; }
         }
@@ -452,7 +452,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(DP_THREADS, 1) tc_de
               const long long t1 = mprof ? clock64() : 0;
               if (ready == 0) {
                 if (!(ok = wait(&full[cslot], cpar, 31))) break;
-                if (!(ok = wait(&pfull[cslot], cpar, 32))) break;
                 ++ready;
                 if (++cslot == DP_NSLOT) { cslot = 0; cpar ^= 1; }
               }

@@ -75,9 +75,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BP_THREADS, 1) tt_ba
   float* gy_s = reinterpret_cast<float*>(smem + BP_OFF_GY);
   float* gxd_s = reinterpret_cast<float*>(smem + BP_OFF_GXD);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BP_OFF_BAR);
-  uint64_t* full = bars;                       // [NSLOT] this CTA's half of a weight chunk landed
+  uint64_t* full = bars;                       // [NSLOT] weight chunk landed: this CTA's half -- and, in the leader, the peer's
+                                               // (second arrival, relayed by the peer's warp 8: one barrier to poll per chunk)
   uint64_t* empty = bars + BP_NSLOT;           // [NSLOT] the pair's MMAs reading the slot completed (multicast commit)
-  uint64_t* pfull = bars + 2 * BP_NSLOT;       // [NSLOT] leader only: the peer's half landed (relay)
   uint64_t* acc_bar = bars + 3 * BP_NSLOT;     // MMAs of the current stage complete (multicast commit)
   uint64_t* op_bar = acc_bar + 1;              // leader only: operand tile(s) of the next stage written, 8 + 8 warp arrivals
   volatile int* abort_s = reinterpret_cast<volatile int*>(acc_bar + 2);
@@ -88,7 +88,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BP_THREADS, 1) tt_ba
   const uint32_t rank = cluster_cta_rank();
   const int n_pairs = (int)(gridDim.x >> 1), pair = (int)(blockIdx.x >> 1);
   if (tid == 0) {
-    for (int i = 0; i < BP_NSLOT; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); mbar_init(&pfull[i], 1); }
+    for (int i = 0; i < BP_NSLOT; ++i) { mbar_init(&full[i], rank == 0 ? 2 : 1); mbar_init(&empty[i], 1); }
     mbar_init(acc_bar, 1);
     mbar_init(op_bar, 16);
     *abort_s = 0;
@@ -380,7 +380,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BP_THREADS, 1) tt_ba
       for (int tile = pair; tile < a.n_tiles && ok; tile += n_pairs)
         for (int i = 0; i < per_tile && ok; ++i) {
           if (!(ok = wait(&full[slot], full_par, 31))) break;
-          if (elect_one_sync()) mbar_arrive_remote(&pfull[slot], 0);   // this CTA's half of the chunk has landed
+          if (elect_one_sync()) mbar_arrive_remote(&full[slot], 0);   // this CTA's half of the chunk has landed
           __syncwarp();
           if (++slot == BP_NSLOT) { slot = 0; full_par ^= 1; }
         }
@@ -394,7 +394,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BP_THREADS, 1) tt_ba
       int ready = 0;
       auto confirm = [&]() {
         while (ready < BP_NSLOT) {
-          if (!mbar_test_wait(&full[cslot], cpar) || !mbar_test_wait(&pfull[cslot], cpar)) break;
+          if (!mbar_test_wait(&full[cslot], cpar)) break;
           ++ready;
           if (++cslot == BP_NSLOT) { cslot = 0; cpar ^= 1; }
         }
@@ -417,7 +417,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BP_THREADS, 1) tt_ba
             for (int c = 0; c < nk && ok; ++c) {
               if (ready == 0) {
                 if (!(ok = wait(&full[cslot], cpar, 31))) break;
-                if (!(ok = wait(&pfull[cslot], cpar, 32))) break;
                 ++ready;
                 if (++cslot == BP_NSLOT) { cslot = 0; cpar ^= 1; }
               }
