@@ -222,6 +222,32 @@ pf_status pf_flow_backward(pf_flow* flow, const void* saved, const float* ctx, c
                            const float* glogdet, float* gx, float* gctx, const pf_layer_grads* grads,
                            void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- glue of the fused training step ---------------------------------------------------------- */
+
+/* Replaces the tensor glue of `batch_nll` (experiments/train_lean_npe.py:108-127) around the two flow calls, in the form
+ * that runs EVERY (event, rank) slot as a flow row with weight [rank < nsig] / count (posteriflow_b200/train.py):
+ *   x[b*S + r, :]     = ParamScaler.normalize(params[b, r, :])  (lean_npe.py:100-109)   or 0 for an absent slot
+ *   cfull[b*S + r, :] = context[b, :] | rank_emb[r, :]           (LeanNPE._full_context, lean_npe.py:296-304)
+ *   w[b*S + r]        = [r < nsig[b]] * inv,   inv = *inv_count if use_inv && *use_inv > 0 (the global count of a
+ *                       data-parallel job) else 1 / max(1, sum_b min(nsig[b], S))       (train_lean_npe.py:127)
+ * params [B, S, D] physical, nsig [B] int64, context [B, context_dim], rank_emb [S, C - context_dim]; x [B*S, D],
+ * cfull [B*S, C], w [B*S].  One kernel instead of ~20 elementwise launches. */
+pf_status pf_slot_prepare(const float* params, const int64_t* nsig, const float* context, const float* rank_emb,
+                          const pf_scaler* scaler, const float* inv_count, const float* use_inv, int32_t B, int32_t S,
+                          int32_t D, int32_t context_dim, int32_t C, float* x, float* cfull, float* w, int32_t device,
+                          void* stream);
+
+/* Replaces `loss = (nll * w).sum()` of the same function with nll = compute_psd_aware_nll(log_sigma = 0)
+ * (flows.py:727-779) and the first step of its backward: loss[0] = sum_r w_r (0.5 (|z_r|^2 + D log 2 pi) - logdet_r),
+ * gz[r, :] = w_r z[r, :], glogdet[r] = -w_r.  One block, fixed reduction tree (deterministic). */
+pf_status pf_slot_loss(const float* z, const float* logdet, const float* w, int64_t rows, int32_t D, float* loss, float* gz,
+                       float* glogdet, int32_t device, void* stream);
+
+/* Replaces autograd's backward of the context gather and of the rank embedding (lean_npe.py:296-304):
+ * gcontext[b, :] = sum_r gcfull[b*S + r, :context_dim],  grank_emb[r, :] = sum_b gcfull[b*S + r, context_dim:]. */
+pf_status pf_slot_ctx_grad(const float* gcfull, int32_t B, int32_t S, int32_t context_dim, int32_t C, float* gcontext,
+                           float* grank_emb, int32_t device, void* stream);
+
 /* ---- serving epilogue ------------------------------------------------------------------------ */
 
 /* Replaces the tail of one iteration of infer()'s sampling loop (inference/pipeline.py:180, 57-76, 184-186):

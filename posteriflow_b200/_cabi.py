@@ -25,7 +25,7 @@ EXPORTS = [
     "pf_sample_fused", "pf_flow_forward", "pf_flow_backward", "pf_flow_workspace_bytes",
     "pf_flow_saved_bytes", "pf_flow_last_launch_count", "pf_flow_hidden_perm", "pf_status_str",
     "pf_last_cuda_error", "pf_abi_version", "pf_physical_logq", "pf_posterior_summary", "pf_flow_check", "pf_flow_fused_training",
-    "pf_sample_fused_static",
+    "pf_sample_fused_static", "pf_slot_prepare", "pf_slot_loss", "pf_slot_ctx_grad",
 ]
 
 _fp = C.c_void_p  # every device pointer is passed as an integer address
@@ -89,6 +89,13 @@ def load_library() -> C.CDLL:
     lib.pf_sample_fused.restype = i32
     lib.pf_sample_fused_static.argtypes = [C.c_void_p, _fp, C.POINTER(Scaler), _fp, u64, i64, i64, _fp, _fp, _fp, u32, _fp]
     lib.pf_sample_fused_static.restype = i32
+    lib.pf_slot_prepare.argtypes = [_fp, _fp, _fp, _fp, C.POINTER(Scaler), _fp, _fp, i32, i32, i32, i32, i32, _fp, _fp, _fp,
+                                    i32, _fp]
+    lib.pf_slot_prepare.restype = i32
+    lib.pf_slot_loss.argtypes = [_fp, _fp, _fp, i64, i32, _fp, _fp, _fp, i32, _fp]
+    lib.pf_slot_loss.restype = i32
+    lib.pf_slot_ctx_grad.argtypes = [_fp, i32, i32, i32, i32, _fp, _fp, i32, _fp]
+    lib.pf_slot_ctx_grad.restype = i32
     lib.pf_flow_forward.argtypes = [C.c_void_p, _fp, _fp, _fp, i64, i64, i64, _fp, _fp, _fp, _fp, u32, _fp, _fp,
                                     sz, _fp]
     lib.pf_flow_forward.restype = i32

@@ -16,7 +16,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIBDIR = os.path.join(PKG, "lib")
 LIB = os.path.join(LIBDIR, "libposteriflow_b200.so")
-SOURCES = ["pf_pack.cu", "pf_fp32.cu", "pf_tc.cu", "pf_tc_dense.cu", "pf_tc_train.cu", "pf_summary.cu", "pf_static.cu"]
+SOURCES = ["pf_pack.cu", "pf_fp32.cu", "pf_tc.cu", "pf_tc_dense.cu", "pf_tc_train.cu", "pf_summary.cu", "pf_static.cu", "pf_glue.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
 

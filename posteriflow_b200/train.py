@@ -177,27 +177,40 @@ class GraphedNLLStep:
         wbuf = torch.zeros(cap, device=dev)
         emb = m.rank_embed.weight
 
+        # the glue around the two flow calls as three kernels of the library (csrc/pf_glue.cu) instead of ~30 ATen launches
+        # (0.16 ms of a 1.10 ms step): slot preparation, loss + its first backward step, context / embedding gradients;
+        # the weight gradients are accumulated straight into the flat buffer's views (no 25 MB copy afterwards)
+        import ctypes as C_
+        from . import _cabi as A_
+        from .ops import _scaler_struct, _stream, backward_into
+        lib = fh.lib
+        sc_struct, sc_keep = _scaler_struct(sc.lo, sc.hi, sc.log_mask, sc.circ_mask)
+        zbuf_loss = torch.zeros(1, device=dev)
+        gzbuf = torch.zeros(cap, D, device=dev)
+        glbuf = torch.zeros(cap, device=dev)
+        gcbuf = torch.zeros(cap, C, device=dev)
+        gcontext = torch.zeros(B, m.context_dim, device=dev)
+        gemb = torch.zeros(S, C - m.context_dim, device=dev)
+        emb_c = emb.detach()
+        assert emb_c.is_contiguous() and emb_c.shape[0] >= S and emb_c.shape[1] == C - m.context_dim
+        idx = fh.index
+
         def body():
-            present = (torch.arange(S, device=dev).unsqueeze(0) < st["nsig"].unsqueeze(1))          # [B, S]
-            count = present.sum().to(torch.float32).clamp_min(1.0)
-            inv = torch.where(st["use_inv"] > 0, st["inv_count"], 1.0 / count)     # global count under data parallelism
-            p = torch.where(present.unsqueeze(2), st["params"], fill)
-            xbuf[:R].copy_(sc.normalize(p).reshape(R, D))
-            # slot (b, r) = row b * S + r: broadcast copies, no gather kernels
-            c3 = cbuf[:R].view(B, S, C)
-            c3[:, :, :m.context_dim].copy_(st["context"].unsqueeze(1).expand(B, S, m.context_dim))
-            c3[:, :, m.context_dim:].copy_(emb.detach()[:S].unsqueeze(0).expand(B, S, C - m.context_dim))
-            wbuf[:R].copy_(present.reshape(R).to(torch.float32) * inv)
+            with torch.cuda.device(idx):
+                A_.check(lib.pf_slot_prepare(st["params"].data_ptr(), st["nsig"].data_ptr(), st["context"].data_ptr(),
+                                             emb_c.data_ptr(), C_.byref(sc_struct), st["inv_count"].data_ptr(),
+                                             st["use_inv"].data_ptr(), B, S, D, m.context_dim, C, xbuf.data_ptr(),
+                                             cbuf.data_ptr(), wbuf.data_ptr(), idx, _stream()), "pf_slot_prepare")
             z, ld, saved = torch.ops.posteriflow.nsf_forward(xbuf, cbuf, weights, fh.id, 1, True, no_r2c)
-            nll = 0.5 * ((z * z).sum(dim=1) + const) - ld
-            loss = (nll * wbuf).sum()
-            outs = torch.ops.posteriflow.nsf_backward(saved, cbuf, z * wbuf.unsqueeze(1), -wbuf, weights, fh.id, 1)
-            gw = list(outs[2:])
-            torch._foreach_copy_(self._step_views, gw)
-            g3 = outs[1][:R].reshape(B, S, C)
-            gcontext = g3[..., :m.context_dim].sum(dim=1)                  # backward of the row gather ...
-            gemb = g3[..., m.context_dim:].sum(dim=0)                      # ... and of the rank embedding
-            return loss, gcontext, gemb
+            with torch.cuda.device(idx):
+                A_.check(lib.pf_slot_loss(z.data_ptr(), ld.data_ptr(), wbuf.data_ptr(), cap, D, zbuf_loss.data_ptr(),
+                                          gzbuf.data_ptr(), glbuf.data_ptr(), idx, _stream()), "pf_slot_loss")
+            self.flat_step.zero_()
+            backward_into(fh, saved, cbuf, gzbuf, glbuf, self._step_views, gcbuf)
+            with torch.cuda.device(idx):
+                A_.check(lib.pf_slot_ctx_grad(gcbuf.data_ptr(), B, S, m.context_dim, C, gcontext.data_ptr(),
+                                              gemb.data_ptr(), idx, _stream()), "pf_slot_ctx_grad")
+            return zbuf_loss.reshape(()), gcontext, gemb
 
         s = torch.cuda.Stream(device=dev)
         s.wait_stream(torch.cuda.current_stream(dev))
@@ -210,9 +223,10 @@ class GraphedNLLStep:
         with torch.cuda.graph(g):
             st["loss"], st["gcontext"], st["gemb"] = body()
         # everything the captured kernels read or write must outlive this frame: the graph holds raw addresses
-        st["keep"] = (xbuf, cbuf, wbuf, fill, no_r2c, weights, emb)
+        st["keep"] = (xbuf, cbuf, wbuf, fill, no_r2c, weights, emb, emb_c, sc_struct, sc_keep, zbuf_loss, gzbuf, glbuf, gcbuf,
+                      gcontext, gemb)
         st["graph"] = g
-        st["launches"] = fh.launches - l0
+        st["launches"] = fh.launches - l0 + 3        # + the three glue kernels (not calls on the flow handle)
         return st
 
     def _call_slots(self, params: Tensor, nsig: Tensor, context: Tensor) -> Tensor:
