@@ -118,17 +118,25 @@ class GraphedNLLStep:
 
         self._ensure_flat()
 
+        # loss + its first backward step as one library kernel, weight gradients accumulated straight into the views of the
+        # flat buffer that the data-parallel all-reduce exchanges (csrc/pf_glue.cu, ops.backward_into): no ATen glue and no
+        # 25 MB gradient copy inside the replay
+        from . import _cabi as A_
+        from .ops import _stream, backward_into
+        lib, idx = fh.lib, fh.index
+        loss_buf = torch.zeros(1, device=dev)
+        gzbuf = torch.zeros(cap, D, device=dev)
+        glbuf = torch.zeros(cap, device=dev)
+        gcbuf = torch.zeros(cap, C, device=dev)
+
         def body():
             z, ld, saved = torch.ops.posteriflow.nsf_forward(st["x"], st["ctx"], weights, fh.id, 1, True, no_r2c)
-            nll = 0.5 * ((z * z).sum(dim=1) + const) - ld
-            loss = (nll * st["w"]).sum()
-            outs = torch.ops.posteriflow.nsf_backward(saved, st["ctx"], z * st["w"].unsqueeze(1), -st["w"], weights,
-                                                      fh.id, 1)
-            gw = list(outs[2:])
-            # inside the graph: the step's flow-weight gradients go straight into the views of the flat buffer that the
-            # data-parallel all-reduce exchanges (one multi-tensor copy per replay instead of one per step on the host)
-            torch._foreach_copy_(self._step_views, gw)
-            return loss, outs[1], gw
+            with torch.cuda.device(idx):
+                A_.check(lib.pf_slot_loss(z.data_ptr(), ld.data_ptr(), st["w"].data_ptr(), cap, D, loss_buf.data_ptr(),
+                                          gzbuf.data_ptr(), glbuf.data_ptr(), idx, _stream()), "pf_slot_loss")
+            self.flat_step.zero_()
+            backward_into(fh, saved, st["ctx"], gzbuf, glbuf, self._step_views, gcbuf)
+            return loss_buf.reshape(()), gcbuf, (loss_buf, gzbuf, glbuf)
 
         s = torch.cuda.Stream(device=dev)
         s.wait_stream(torch.cuda.current_stream(dev))
@@ -141,7 +149,7 @@ class GraphedNLLStep:
         with torch.cuda.graph(g):
             st["loss"], st["gctx"], st["gw"] = body()
         st["graph"] = g
-        st["launches"] = fh.launches - l0      # library kernels inside one replay
+        st["launches"] = fh.launches - l0 + 1      # library kernels inside one replay (+ the loss kernel)
         return st
 
     # -- slot mode ---------------------------------------------------------------------------------------------------
