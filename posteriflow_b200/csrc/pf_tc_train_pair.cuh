@@ -104,7 +104,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BP_THREADS, 1) tt_ba
   const uint32_t tmem = *tmem_slot;
 
   auto wait = [&](uint64_t* bar, uint32_t parity, int code) -> bool {
-    for (uint32_t i = 0; i < (1u << 26); ++i) {
+    for (uint32_t i = 0; i < (1u << 22); ++i) {
       if (mbar_try_wait(bar, parity)) return true;            // suspends in hardware: a spinning probe loop would take
       if ((i & 1023) == 1023 && *abort_s) return false;          // issue slots from the row warps of the same scheduler
     }
