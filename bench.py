@@ -384,6 +384,7 @@ def run_ours(args):
     counted["kernels"] = 0
     ms_train, _ = timed(step_train, args.steps, args.warmup)
     launches_train = counted["kernels"] * args.steps // (args.steps + args.warmup)   # counted per call, timed calls only
+    kernels_shard = int(gstep.last_launches)        # library kernels of one replay of THIS step (later steps overwrite it)
     l0 = fh.launches
     ms_train_opt, pack_launches = timed(step_train_opt, args.steps, args.warmup)
     ms_train_eager, _ = timed(step_train_eager, args.steps, args.warmup)
@@ -522,7 +523,7 @@ def run_ours(args):
                      "full_config_seconds_extrapolated": 3e8 / max(c5_rows_s, 1.0)}},
         "train": {"metric": "nll_train_steps_per_sec", "value": args.steps / (ms_train * 1e-3), "unit": "steps/s",
                   "events_per_gpu": Bt, "flow_rows_per_gpu": Rt, "ms_per_step": ms_train / args.steps,
-                  "gpu_launches": int(launches_train), "kernels_per_step": int(gstep.last_launches),
+                  "gpu_launches": int(launches_train), "kernels_per_step": kernels_shard,
                   "e2e_ms": ms_train_opt / args.steps,
                   "e2e_includes": "flow-only step + torch.nn.utils.clip_grad_norm_(5.0) + fused AdamW.step() over all flow "
                                   "+ rank-embedding parameters + the re-pack of the updated weights (train_lean_npe.py:363-368); "
