@@ -248,6 +248,19 @@ pf_status pf_slot_loss(const float* z, const float* logdet, const float* w, int6
 pf_status pf_slot_ctx_grad(const float* gcfull, int32_t B, int32_t S, int32_t context_dim, int32_t C, float* gcontext,
                            float* grank_emb, int32_t device, void* stream);
 
+/* The compact form of the same glue: only the PRESENT (event, rank) pairs become flow rows (event-major), for batches whose
+ * slots would not fit one wave of tiles.  pf_rows_prepare writes offs[b] = sum_{b' < b} min(nsig[b'], S) (offs[B] = R, the
+ * number of rows; int32 [B + 1]) and rows [0, cap): row offs[b] + k = (event b, rank k) as in pf_slot_prepare with
+ * w = inv, inv = *inv_count if use_inv && *use_inv > 0 else 1 / max(1, R); rows [R, cap) get x = 0, w = 0.
+ * pf_rows_ctx_grad sums d loss / d full-context rows back per event and per rank.  Replaces signal_rows' nonzero + the
+ * index_select / cat / normalize / index_add kernels of batch_nll and its autograd (train_lean_npe.py:108-127). */
+pf_status pf_rows_prepare(const float* params, const int64_t* nsig, const float* context, const float* rank_emb,
+                          const pf_scaler* scaler, const float* inv_count, const float* use_inv, int32_t B, int32_t S,
+                          int32_t D, int32_t context_dim, int32_t C, int32_t cap, int32_t* offs, float* x, float* cfull,
+                          float* w, int32_t device, void* stream);
+pf_status pf_rows_ctx_grad(const float* gcfull, const int32_t* offs, int32_t B, int32_t S, int32_t context_dim, int32_t C,
+                           float* gcontext, float* grank_emb, int32_t device, void* stream);
+
 /* ---- serving epilogue ------------------------------------------------------------------------ */
 
 /* Replaces the tail of one iteration of infer()'s sampling loop (inference/pipeline.py:180, 57-76, 184-186):

@@ -26,6 +26,7 @@ EXPORTS = [
     "pf_flow_saved_bytes", "pf_flow_last_launch_count", "pf_flow_hidden_perm", "pf_status_str",
     "pf_last_cuda_error", "pf_abi_version", "pf_physical_logq", "pf_posterior_summary", "pf_flow_check", "pf_flow_fused_training",
     "pf_sample_fused_static", "pf_slot_prepare", "pf_slot_loss", "pf_slot_ctx_grad",
+    "pf_rows_prepare", "pf_rows_ctx_grad",
 ]
 
 _fp = C.c_void_p  # every device pointer is passed as an integer address
@@ -92,6 +93,11 @@ def load_library() -> C.CDLL:
     lib.pf_slot_prepare.argtypes = [_fp, _fp, _fp, _fp, C.POINTER(Scaler), _fp, _fp, i32, i32, i32, i32, i32, _fp, _fp, _fp,
                                     i32, _fp]
     lib.pf_slot_prepare.restype = i32
+    lib.pf_rows_prepare.argtypes = [_fp, _fp, _fp, _fp, C.POINTER(Scaler), _fp, _fp, i32, i32, i32, i32, i32, i32, _fp, _fp, _fp,
+                                    _fp, i32, _fp]
+    lib.pf_rows_prepare.restype = i32
+    lib.pf_rows_ctx_grad.argtypes = [_fp, _fp, i32, i32, i32, i32, _fp, _fp, i32, _fp]
+    lib.pf_rows_ctx_grad.restype = i32
     lib.pf_slot_loss.argtypes = [_fp, _fp, _fp, i64, i32, _fp, _fp, _fp, i32, _fp]
     lib.pf_slot_loss.restype = i32
     lib.pf_slot_ctx_grad.argtypes = [_fp, i32, i32, i32, i32, _fp, _fp, i32, _fp]

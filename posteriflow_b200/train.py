@@ -92,9 +92,11 @@ class GraphedNLLStep:
     size.  Absent slots carry weight zero (their parameters are replaced by a fixed in-range value first): they add
     exactly nothing to the loss and to every gradient."""
 
-    def __init__(self, model, bucket: int = 128, distributed: bool = False, slots: Optional[bool] = None):
+    def __init__(self, model, bucket: int = 128, distributed: bool = False, slots: Optional[bool] = None,
+                 compact: bool = True):
         self.model, self.bucket, self.distributed = model, int(bucket), distributed
         self.slots = slots
+        self.compact = compact          # rows mode through pf_rows_prepare / pf_rows_ctx_grad (False: the ATen gather path)
         self.slot_graphs = {}
         self.graphs = {}
         self.flow_params = model.flow.layer_weights()
@@ -162,13 +164,16 @@ class GraphedNLLStep:
         n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
         return B * int(self.model.max_signals) <= 128 * (n_sm // 2)
 
-    def _capture_slots(self, B: int, ctx_requires_grad: bool):
+    def _capture_slots(self, B: int, ctx_requires_grad: bool, compact_cap: Optional[int] = None):
+        """`compact_cap` None: one flow row per (event, rank) slot.  An integer: the COMPACT form -- only the present pairs
+        become rows (event-major, found on the device from a prefix sum of nsig), padded to `compact_cap` rows with weight 0;
+        the graph is then keyed on (B, compact_cap) and the host reads only the row count, to choose the bucket."""
         import math
         m = self.model
         dev = self.flow_params[0].device
         D, C, S = m.flow.features, m.flow.context_features, int(m.max_signals)
         R = B * S
-        cap = (R + 127) // 128 * 128
+        cap = (R + 127) // 128 * 128 if compact_cap is None else int(compact_cap)
         st = {"params": torch.zeros(B, S, D, device=dev), "nsig": torch.zeros(B, dtype=torch.long, device=dev),
               "context": torch.zeros(B, m.context_dim, device=dev), "inv_count": torch.zeros((), device=dev),
               "use_inv": torch.zeros((), device=dev)}
@@ -202,13 +207,21 @@ class GraphedNLLStep:
         emb_c = emb.detach()
         assert emb_c.is_contiguous() and emb_c.shape[0] >= S and emb_c.shape[1] == C - m.context_dim
         idx = fh.index
+        offs = torch.zeros(B + 1, dtype=torch.int32, device=dev)
 
         def body():
             with torch.cuda.device(idx):
-                A_.check(lib.pf_slot_prepare(st["params"].data_ptr(), st["nsig"].data_ptr(), st["context"].data_ptr(),
-                                             emb_c.data_ptr(), C_.byref(sc_struct), st["inv_count"].data_ptr(),
-                                             st["use_inv"].data_ptr(), B, S, D, m.context_dim, C, xbuf.data_ptr(),
-                                             cbuf.data_ptr(), wbuf.data_ptr(), idx, _stream()), "pf_slot_prepare")
+                if compact_cap is None:
+                    A_.check(lib.pf_slot_prepare(st["params"].data_ptr(), st["nsig"].data_ptr(), st["context"].data_ptr(),
+                                                 emb_c.data_ptr(), C_.byref(sc_struct), st["inv_count"].data_ptr(),
+                                                 st["use_inv"].data_ptr(), B, S, D, m.context_dim, C, xbuf.data_ptr(),
+                                                 cbuf.data_ptr(), wbuf.data_ptr(), idx, _stream()), "pf_slot_prepare")
+                else:
+                    A_.check(lib.pf_rows_prepare(st["params"].data_ptr(), st["nsig"].data_ptr(), st["context"].data_ptr(),
+                                                 emb_c.data_ptr(), C_.byref(sc_struct), st["inv_count"].data_ptr(),
+                                                 st["use_inv"].data_ptr(), B, S, D, m.context_dim, C, cap, offs.data_ptr(),
+                                                 xbuf.data_ptr(), cbuf.data_ptr(), wbuf.data_ptr(), idx, _stream()),
+                             "pf_rows_prepare")
             z, ld, saved = torch.ops.posteriflow.nsf_forward(xbuf, cbuf, weights, fh.id, 1, True, no_r2c)
             with torch.cuda.device(idx):
                 A_.check(lib.pf_slot_loss(z.data_ptr(), ld.data_ptr(), wbuf.data_ptr(), cap, D, zbuf_loss.data_ptr(),
@@ -216,8 +229,12 @@ class GraphedNLLStep:
             self.flat_step.zero_()
             backward_into(fh, saved, cbuf, gzbuf, glbuf, self._step_views, gcbuf)
             with torch.cuda.device(idx):
-                A_.check(lib.pf_slot_ctx_grad(gcbuf.data_ptr(), B, S, m.context_dim, C, gcontext.data_ptr(),
-                                              gemb.data_ptr(), idx, _stream()), "pf_slot_ctx_grad")
+                if compact_cap is None:
+                    A_.check(lib.pf_slot_ctx_grad(gcbuf.data_ptr(), B, S, m.context_dim, C, gcontext.data_ptr(),
+                                                  gemb.data_ptr(), idx, _stream()), "pf_slot_ctx_grad")
+                else:
+                    A_.check(lib.pf_rows_ctx_grad(gcbuf.data_ptr(), offs.data_ptr(), B, S, m.context_dim, C,
+                                                  gcontext.data_ptr(), gemb.data_ptr(), idx, _stream()), "pf_rows_ctx_grad")
             return zbuf_loss.reshape(()), gcontext, gemb
 
         s = torch.cuda.Stream(device=dev)
@@ -232,17 +249,19 @@ class GraphedNLLStep:
             st["loss"], st["gcontext"], st["gemb"] = body()
         # everything the captured kernels read or write must outlive this frame: the graph holds raw addresses
         st["keep"] = (xbuf, cbuf, wbuf, fill, no_r2c, weights, emb, emb_c, sc_struct, sc_keep, zbuf_loss, gzbuf, glbuf, gcbuf,
-                      gcontext, gemb)
+                      gcontext, gemb, offs)
         st["graph"] = g
-        st["launches"] = fh.launches - l0 + 3        # + the three glue kernels (not calls on the flow handle)
+        # + the glue kernels (not calls on the flow handle): prepare (scan + prepare when compact), loss, context gradients
+        st["launches"] = fh.launches - l0 + (3 if compact_cap is None else 4)
         return st
 
-    def _call_slots(self, params: Tensor, nsig: Tensor, context: Tensor) -> Tensor:
+    def _call_slots(self, params: Tensor, nsig: Tensor, context: Tensor, compact_cap: Optional[int] = None) -> Tensor:
         m = self.model
         B = int(context.shape[0])
-        st = self.slot_graphs.get(B)
+        key = B if compact_cap is None else (B, int(compact_cap))
+        st = self.slot_graphs.get(key)
         if st is None:
-            st = self.slot_graphs[B] = self._capture_slots(B, context.requires_grad)
+            st = self.slot_graphs[key] = self._capture_slots(B, context.requires_grad, compact_cap)
         with torch.no_grad():
             st["params"].copy_(params[:, :int(m.max_signals), :])
             st["nsig"].copy_(nsig)
@@ -327,6 +346,14 @@ class GraphedNLLStep:
             self._ensure_packed()
             if self._use_slots(int(context.shape[0]), context.device):
                 return self._call_slots(params, nsig.to(context.device), context)
+            if self.compact:
+                # rows mode, compact form: the host learns only HOW MANY rows there are (to choose the bucket); which
+                # (event, rank) pair each row is gets worked out on the device inside the graph
+                nsig_d = nsig.to(context.device)
+                R = int(nsig_d.clamp(0, int(m.max_signals)).sum())
+                if R > 0:
+                    cap = (R + self.bucket - 1) // self.bucket * self.bucket
+                    return self._call_slots(params, nsig_d, context, compact_cap=cap)
         event, rank = signal_rows(nsig.to(context.device), int(m.max_signals))
         R = int(event.numel())
         if R == 0:

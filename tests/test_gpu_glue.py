@@ -235,7 +235,7 @@ def test_batch_nll_fused_matches_loop_and_oracle():
     assert float((c1.grad - c2.grad).abs().max()) <= 1e-4 * scale
 
 
-@pytest.mark.parametrize("tier", ["fp32", "bf16", "bf16-rows"])
+@pytest.mark.parametrize("tier", ["fp32", "bf16", "bf16-rows", "bf16-rows-aten"])
 def test_graphed_nll_step_matches_batch_nll(tier, monkeypatch):
     """GraphedNLLStep (one CUDA-graph replay per step, rows padded to a bucket with zero weight) == batch_nll +
     backward through autograd: same loss, same gradient of the context, the rank embedding and every flow weight;
@@ -244,14 +244,16 @@ def test_graphed_nll_step_matches_batch_nll(tier, monkeypatch):
     import posteriflow_b200 as P
     # "bf16": the fused training kernels in SLOT mode (every (event, rank) slot with weight [rank < nsig] / count, gather /
     # scaler / embedding and their backward inside the graph); "bf16-rows": the same kernels over the gathered rows
-    slots = None if tier != "bf16-rows" else False
-    tier = "bf16" if tier == "bf16-rows" else tier
+    # (compact form: pf_rows_prepare / pf_rows_ctx_grad inside the graph); "bf16-rows-aten": the gather done by ATen outside it
+    slots = None if not tier.startswith("bf16-rows") else False
+    compact = tier != "bf16-rows-aten"
+    tier = "bf16" if tier.startswith("bf16-rows") else tier
     if tier == "bf16":       # capture the split-bf16 tcgen05 GEMMs too (by default they serve calls of >= 512 rows)
         monkeypatch.setenv("PF_TRAIN_TC_MIN_ROWS", "0")
     spec, w, g = load_golden("lean_glue")
     m = lean_model(w, g, tier=tier)
     sc = O.Scaler()
-    step = P.GraphedNLLStep(m, bucket=64, slots=slots)
+    step = P.GraphedNLLStep(m, bucket=64, slots=slots, compact=compact)
     assert step._use_slots(40, torch.device("cuda")) == (tier == "bf16" and slots is None)
     gen = torch.Generator().manual_seed(12)
     tol = 1e-4 if tier == "fp32" else 5e-4
@@ -279,4 +281,35 @@ def test_graphed_nll_step_matches_batch_nll(tier, monkeypatch):
             step(params, nsig.cuda(), c3)
             n0 = "flow.transform._transforms.1.autoregressive_net.final_layer.weight"
             assert float((m.get_parameter(n0).grad - 2 * ref_g[n0]).abs().max()) <= 2 * tol * float(ref_g[n0].abs().max())
-    assert len(step.graphs) <= 2
+    assert len(step.graphs) + len(step.slot_graphs) <= 2
+    assert bool(step.graphs) == (not compact)
+
+
+@pytest.mark.parametrize("B", [300, 2500])
+def test_compact_rows_form_with_empty_events_and_a_long_prefix_sum(B):
+    """The compact rows form (prefix sum of nsig -> (event, rank) of every row on the device) against the ATen gather path on
+    a batch with events of 0 signals, of more than max_signals (clamped), and B beyond one element per scan thread."""
+    import posteriflow_b200 as P
+    spec, w, g = load_golden("lean_glue")
+    m = lean_model(w, g, tier="bf16")
+    sc = O.Scaler()
+    gen = torch.Generator().manual_seed(B)
+    nsig = torch.randint(0, 8, (B,), generator=gen)               # 0 .. 7 with max_signals = 5
+    nsig[0], nsig[-1] = 0, 0
+    params = sc.denormalize(torch.rand(B, 5, 11, generator=gen) * 2 - 1).cuda()
+    ctx = torch.randn(B, 256, generator=gen)
+    out = {}
+    for compact in (False, True):
+        step = P.GraphedNLLStep(m, slots=False, compact=compact)
+        m.zero_grad(set_to_none=True)
+        c = ctx.cuda().requires_grad_(True)
+        loss = step(params, nsig.cuda(), c)
+        out[compact] = (float(loss), c.grad.clone(), m.rank_embed.weight.grad.clone(),
+                        [p.grad.clone() for p in m.flow.layer_weights()])
+    a, b = out[False], out[True]
+    assert abs(a[0] - b[0]) <= 1e-5 * max(1.0, abs(a[0]))
+    assert float((a[1] - b[1]).abs().max()) <= 1e-5 * float(a[1].abs().max())
+    assert float((a[1][nsig == 0]).abs().max()) == 0.0 and float((b[1][nsig.cuda() == 0]).abs().max()) == 0.0
+    assert float((a[2] - b[2]).abs().max()) <= 1e-5 * float(a[2].abs().max())
+    for ga, gb in zip(a[3], b[3]):      # row order differs (rank-major vs event-major): atomics / tile sums in another order
+        assert float((ga - gb).abs().max()) <= 2e-5 * max(1e-12, float(ga.abs().max()))
