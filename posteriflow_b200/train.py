@@ -90,7 +90,13 @@ class GraphedNLLStep:
     static, so the row gather, the scaler, the rank embedding, their backward and the signal count move INTO the
     captured graph -- no `nonzero` (a host sync), no ATen glue around the replay, one graph for every batch of that
     size.  Absent slots carry weight zero (their parameters are replaced by a fixed in-range value first): they add
-    exactly nothing to the loss and to every gradient."""
+    exactly nothing to the loss and to every gradient.
+
+    **Compact rows form** (`compact=True`, the default for batches beyond one wave): only the present pairs become flow
+    rows, but WHICH pair a row is gets worked out on the device inside the graph (prefix sum of nsig, `pf_rows_prepare` /
+    `pf_rows_ctx_grad` of csrc/pf_glue.cu), so the ATen gather around the replay goes away here too; the host reads the
+    row count only, to choose the bucket.  `compact=False` keeps the gather with ATen (the form the first paragraph
+    describes), which the tests hold against it."""
 
     def __init__(self, model, bucket: int = 128, distributed: bool = False, slots: Optional[bool] = None,
                  compact: bool = True):
