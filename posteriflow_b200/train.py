@@ -89,7 +89,7 @@ class GraphedNLLStep:
     slot of the batch with weight [rank < nsig] / count instead of gathering the present signals first: all shapes are
     static, so the row gather, the scaler, the rank embedding, their backward and the signal count move INTO the
     captured graph -- no `nonzero` (a host sync), no ATen glue around the replay, one graph for every batch of that
-    size.  Absent slots carry weight zero (their parameters are replaced by a fixed in-range value first): they add
+    size.  Absent slots carry weight zero and x = 0 (their parameters are never read): they add
     exactly nothing to the loss and to every gradient.
 
     **Compact rows form** (`compact=True`, the default for batches beyond one wave): only the present pairs become flow
@@ -112,7 +112,6 @@ class GraphedNLLStep:
         self.last_launches = 0
 
     def _capture(self, cap: int):
-        import math
         m = self.model
         dev = self.flow_params[0].device
         D, C = m.flow.features, m.flow.context_features
@@ -120,7 +119,6 @@ class GraphedNLLStep:
               "w": torch.zeros(cap, device=dev)}
         fh = m.flow.handle()
         weights = [p.detach() for p in self.flow_params]
-        const = D * math.log(2 * math.pi)
         from .ops import no_row2ctx
         no_r2c = no_row2ctx(st["x"])
 
@@ -174,7 +172,6 @@ class GraphedNLLStep:
         """`compact_cap` None: one flow row per (event, rank) slot.  An integer: the COMPACT form -- only the present pairs
         become rows (event-major, found on the device from a prefix sum of nsig), padded to `compact_cap` rows with weight 0;
         the graph is then keyed on (B, compact_cap) and the host reads only the row count, to choose the bucket."""
-        import math
         m = self.model
         dev = self.flow_params[0].device
         D, C, S = m.flow.features, m.flow.context_features, int(m.max_signals)
@@ -185,12 +182,10 @@ class GraphedNLLStep:
               "use_inv": torch.zeros((), device=dev)}
         fh = m.flow.handle()
         weights = [p.detach() for p in self.flow_params]
-        const = D * math.log(2 * math.pi)
         from .ops import no_row2ctx
         no_r2c = no_row2ctx(st["params"])
         self._ensure_flat()
         sc = m.scaler
-        fill = sc.denormalize(torch.zeros(D, device=dev))                  # an in-range physical value for absent slots
         xbuf = torch.zeros(cap, D, device=dev)
         cbuf = torch.zeros(cap, C, device=dev)
         wbuf = torch.zeros(cap, device=dev)
@@ -254,7 +249,7 @@ class GraphedNLLStep:
         with torch.cuda.graph(g):
             st["loss"], st["gcontext"], st["gemb"] = body()
         # everything the captured kernels read or write must outlive this frame: the graph holds raw addresses
-        st["keep"] = (xbuf, cbuf, wbuf, fill, no_r2c, weights, emb, emb_c, sc_struct, sc_keep, zbuf_loss, gzbuf, glbuf, gcbuf,
+        st["keep"] = (xbuf, cbuf, wbuf, no_r2c, weights, emb, emb_c, sc_struct, sc_keep, zbuf_loss, gzbuf, glbuf, gcbuf,
                       gcontext, gemb, offs)
         st["graph"] = g
         # + the glue kernels (not calls on the flow handle): prepare (scan + prepare when compact), loss, context gradients
