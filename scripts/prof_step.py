@@ -39,4 +39,4 @@ for _ in range(reps):
 e1.record()
 torch.cuda.synchronize()
 print(f"B {B}: {e0.elapsed_time(e1) / reps:.3f} ms per step (back to back, no L2 flush), loss {float(loss):.4f}, "
-      f"slots {bool(step.slot_graphs)}, kernels per replay {step.last_launches}")
+      f"fused glue {bool(step.slot_graphs)} (slot mode {step._use_slots(B, dev)}), kernels per replay {step.last_launches}")
