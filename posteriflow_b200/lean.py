@@ -188,6 +188,49 @@ class LeanNPE(nn.Module):
         return theta
 
     @torch.no_grad()
+    def sample_posterior_host(self, context: Tensor, rank: int = 0, n_samples: int = 256, out: Optional[Tensor] = None,
+                              chunk_events: Optional[int] = None, seed: Optional[int] = None) -> Tensor:
+        """`sample_posterior(None, rank, n_samples, context=context)` for a consumer on the HOST (the reference's callers
+        move every batch of draws off the device: `samples.cpu().numpy()`, pipeline.py:186, overlap_benchmark.py:60-64):
+        `context` [E, context_dim] may live in (pinned) host memory, the result is theta [E, n, D] in pinned host memory
+        (`out`, allocated if None).  Events go through the sampler in chunks and chunk i's device-to-host copy runs on a
+        side stream under chunk i + 1's sampling, so only the last chunk's copy (1/8 of the output by default) is not
+        hidden.  Chunk i draws its noise in-kernel under the Philox key `dist.shard_seed(seed, i)` (disjoint streams).
+        The caller's stream is made to wait for the copies: synchronize it (or the device) before reading `out`."""
+        from .dist import shard_seed
+        dev = self.rank_embed.weight.device
+        E, D = int(context.shape[0]), self.flow.features
+        if out is None:
+            out = torch.empty(E, n_samples, D, dtype=torch.float32, pin_memory=True)
+        if tuple(out.shape) != (E, n_samples, D) or out.dtype != torch.float32 or out.is_cuda:
+            raise ValueError(f"out must be a host float32 tensor of shape {(E, n_samples, D)}")
+        if E == 0:
+            return out
+        chunk = int(chunk_events) if chunk_events else max(1, (E + 7) // 8)
+        if seed is None:
+            seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        cur = torch.cuda.current_stream(dev)
+        copy = getattr(self, "_copy_stream", None)
+        if copy is None or copy.device != dev:
+            copy = torch.cuda.Stream(device=dev)
+            object.__setattr__(self, "_copy_stream", copy)
+        c_dev = context.to(dev, non_blocking=True)
+        r = torch.full((E,), rank, dtype=torch.long, device=dev)
+        ctx = self._full_context(c_dev, r)
+        copy.wait_stream(cur)             # `out` may still be read by earlier work of the caller's stream
+        for i, e0 in enumerate(range(0, E, chunk)):
+            e1 = min(E, e0 + chunk)
+            th = sample_fused(self.flow, self.scaler, ctx[e0:e1], n_samples, z=None, seed=shard_seed(seed, i))[0]
+            done = torch.cuda.Event()
+            done.record(cur)
+            copy.wait_event(done)
+            with torch.cuda.stream(copy):
+                out[e0:e1].copy_(th, non_blocking=True)
+            th.record_stream(copy)
+        cur.wait_stream(copy)
+        return out
+
+    @torch.no_grad()
     def sample_with_log_prob(self, strain: Optional[Tensor], rank: int = 0, n_samples: int = 256,
                              asd_bands: Optional[Tensor] = None, context: Optional[Tensor] = None,
                              z: Optional[Tensor] = None, sort_masses: bool = True):

@@ -602,3 +602,30 @@ def test_flat_parameter_mode_matches_the_per_tensor_optimizer_path():
     w0 = O.full_state_dict(spec, w)
     k0 = next(k for k in w0 if k.endswith("final_layer.weight"))
     assert float((ma.flow.state_dict()[k0].cpu() - w0[k0]).abs().max()) > 1e-4
+
+
+def test_sample_posterior_host_is_the_chunked_sampler_with_overlapped_copies():
+    """LeanNPE.sample_posterior_host: pinned host theta whose chunk i equals the fused sampler on events [e0, e1) under the
+    Philox key shard_seed(seed, i) bit for bit (the side-stream copies neither tear nor reorder anything), for chunk sizes
+    that do and do not divide the event count; a second call into the same `out` overwrites it safely."""
+    import posteriflow_b200 as P
+    from posteriflow_b200.dist import shard_seed
+    torch.manual_seed(5)
+    m = P.LeanNPE(tier="bf16").cuda()
+    g = torch.Generator().manual_seed(9)
+    E, n = 37, 300
+    ctx_host = torch.randn(E, 256, generator=g).pin_memory()
+    out = None
+    for chunk, seed in ((None, 11), (5, 12), (64, 13)):
+        out = m.sample_posterior_host(ctx_host, rank=1, n_samples=n, out=out, chunk_events=chunk, seed=seed)
+        torch.cuda.synchronize()
+        assert out.is_pinned() and tuple(out.shape) == (E, n, 11)
+        c = chunk or (E + 7) // 8
+        full = m._full_context(ctx_host.cuda(), torch.full((E,), 1, dtype=torch.long, device="cuda"))
+        for i, e0 in enumerate(range(0, E, c)):
+            e1 = min(E, e0 + c)
+            ref = P.sample_fused(m.flow, m.scaler, full[e0:e1], n, z=None, seed=shard_seed(seed, i))[0]
+            assert torch.equal(out[e0:e1], ref.cpu()), (chunk, i)
+    assert not torch.equal(out[0], out[1])
+    with pytest.raises(ValueError):
+        m.sample_posterior_host(ctx_host, n_samples=n, out=torch.empty(E, n, 10))
