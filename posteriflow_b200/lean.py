@@ -191,7 +191,7 @@ class LeanNPE(nn.Module):
     def sample_posterior_host(self, context: Tensor, rank: int = 0, n_samples: int = 256, out: Optional[Tensor] = None,
                               chunk_events: Optional[int] = None, seed: Optional[int] = None) -> Tensor:
         """`sample_posterior(None, rank, n_samples, context=context)` for a consumer on the HOST (the reference's callers
-        move every batch of draws off the device: `samples.cpu().numpy()`, pipeline.py:186, overlap_benchmark.py:60-64):
+        move every batch of draws off the device: `.cpu().numpy()`, pipeline.py:179, overlap_benchmark.py:59):
         `context` [E, context_dim] may live in (pinned) host memory, the result is theta [E, n, D] in pinned host memory
         (`out`, allocated if None).  Events go through the sampler in chunks and chunk i's device-to-host copy runs on a
         side stream under chunk i + 1's sampling, so only the last chunk's copy (1/8 of the output by default) is not
