@@ -9,9 +9,11 @@
 //                        residual gradient in tensor memory.  Relu masks, gates and pre-gate values come from the images
 //                        the forward saved; the gradient operand tiles it builds in shared memory are written out once
 //                        (bulk copy shared -> global) as the images the weight-gradient kernel contracts.
-//   tt_wgrad_kernel      one CTA per (layer, weight matrix, 128-row block of the matrix): D[out, in] = sum over ALL flow rows
+//   tt_wgrad_kernel      one CTA per (layer, weight matrix) -- both 128-row blocks of the matrix in two accumulators against
+//                        ONE fetch of the activations; the 288-wide context matrices stay one block per CTA --:
+//                        D[out, in] = sum over ALL flow rows
 //                        of G[row, out] A[row, in] -- both operands are the saved row-major tile images, fed to tcgen05.mma
-//                        as MN-major operands (the contraction index is the tile row), double-buffered bulk loads; bias
+//                        as MN-major operands (the contraction index is the tile row), bulk loads through two rings; bias
 //                        gradients are the column sums of the same G tiles.  Plain read-modify-write stores into nflows'
 //                        own weight layout: every output entry has exactly one owner CTA (no atomics).
 #include <cuda_fp16.h>
@@ -621,20 +623,28 @@ struct TtWgArgs {
   int64_t R;
   const int* perm;         // [H] sorted slot -> nflows unit
   int mn_swap;             // descriptor convention switch (PF_MN_SWAP; bring-up aid)
+  int wide;                // job table: 1 = WG_JOBS_WIDE per layer (both gradient halves against ONE fetch of the activations)
   int* err;
   pf_layer_grads g[TT_MAX_L];
 };
 
 constexpr int WG_THREADS = 192;       // 4 epilogue / column-sum warps, MMA issuer, loader
-constexpr int WG_STAGES = 2;
+constexpr int WG_NA = 2;              // ring of second operands (activation / x / context image of a tile)
+constexpr int WG_NG = 3;              // ring of gradient blocks (two of them when a job has one block per tile)
 constexpr int WG_GBYTES = 32768;      // [128 rows x 128 columns] of a gradient image
 constexpr int WG_ABYTES = 65536;      // [128 rows x 256 columns] activation image
-constexpr int WG_STAGE = WG_GBYTES + TT_CIMG;     // sized for the widest second operand (the context image)
-constexpr int WG_OFF_BAR = WG_STAGES * WG_STAGE;
+// wide job: 2 x 64 KB + 3 x 32 KB; context job: 2 x 72 KB + 2 x 32 KB
+constexpr int WG_OFF_BAR = (WG_NA * WG_ABYTES + WG_NG * WG_GBYTES) > (WG_NA * TT_CIMG + 2 * WG_GBYTES)
+                               ? (WG_NA * WG_ABYTES + WG_NG * WG_GBYTES) : (WG_NA * TT_CIMG + 2 * WG_GBYTES);
 constexpr int WG_OFF_EPI = 128 * (TT_CIMG_COLS + 1) * 4;   // epilogue: row pointers behind the staged [128][N + 1] block
-static_assert(WG_OFF_EPI + 128 * 12 <= WG_OFF_BAR, "epilogue staging must fit in the operand stages");
-constexpr int WG_SMEM = WG_OFF_BAR + 128;
+static_assert(WG_OFF_EPI + 128 * 12 <= WG_NA * TT_CIMG + 2 * WG_GBYTES, "epilogue staging must fit in the operand rings");
+constexpr int WG_SMEM = WG_OFF_BAR + 256;
+static_assert(WG_SMEM <= 232448, "shared memory of the weight-gradient kernel");
 constexpr int WG_JOBS = 20;           // per layer: final 4 | 4 hidden matrices x 2 | initial 2 | 3 context layers x 2
+// Wide table: final PA | final PB | 4 hidden matrices | initial (each: BOTH 128-column gradient blocks, two accumulators)
+// | 3 context layers x 2.  96 KB of operands per 1 024 tensor cycles in the narrow form, 128 KB per 2 048 in the wide one, and
+// 130 CTAs are one wave instead of 200 in two: 177 -> 159 us at 7 608 rows (PF_WGRAD_WIDE=0 keeps the narrow table).
+constexpr int WG_JOBS_WIDE = 13;
 
 // instruction descriptor, kind::f16: bf16 x bf16 -> fp32, BOTH operands MN-major (bits 15 / 16), dense
 __host__ __device__ constexpr uint32_t umma_idesc_bf16_mn(int M, int N) {
@@ -645,29 +655,50 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
   extern __shared__ __align__(128) uint8_t smem[];
   const TtShape& s = a.s;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + WG_OFF_BAR);
-  uint64_t* full = bars;                    // [STAGES] tile images landed
-  uint64_t* empty = bars + WG_STAGES;       // [STAGES] MMAs + column sums done with the stage (1 commit + 4 warps)
-  uint64_t* acc_bar = bars + 2 * WG_STAGES;
+  uint64_t* afull = bars;                   // [WG_NA] second operand of a tile landed
+  uint64_t* aempty = bars + WG_NA;          // [WG_NA] every MMA of the tile done (1 commit)
+  uint64_t* gfull = bars + 2 * WG_NA;       // [WG_NG] gradient block landed
+  uint64_t* gempty = gfull + WG_NG;         // [WG_NG] MMAs + column sums done with the block (1 commit + 4 warps)
+  uint64_t* acc_bar = gempty + WG_NG;
   volatile int* abort_s = reinterpret_cast<volatile int*>(acc_bar + 1);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 2);
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   // ---- decode the job ----
-  const int l = blockIdx.x / WG_JOBS, jk = blockIdx.x % WG_JOBS;
-  // 0 final | 1 Wb2 | 2 Wa2 | 3 Wb1 | 4 Wa1 | 5 W0 | 6 context_layer | 7 blocks.0.context_layer | 8 blocks.1.context_layer
-  const int mat = jk < 4 ? 0 : 1 + (jk - 4) / 2;
-  const int mt = jk < 4 ? (jk & 1) : ((jk - 4) & 1);   // 128-column block of the gradient image
-  const int gwhich = jk < 2 ? TT_G_PA : (jk < 4 ? TT_G_PB : (mat <= 5 ? TT_G_V2 + (mat - 1) : TT_G_C0 + (mat - 6)));
+  // mat: 0 final | 1 Wb2 | 2 Wa2 | 3 Wb1 | 4 Wa1 | 5 W0 | 6 context_layer | 7 blocks.0.context_layer | 8 blocks.1.context_layer
+  // mt0: first 128-column block of the gradient image, nh: blocks of this job (accumulator h at TMEM column 256 h)
+  int l, mat, mt0, nh;
+  bool is_pa = false;
+  if (a.wide) {
+    l = blockIdx.x / WG_JOBS_WIDE;
+    const int j = blockIdx.x % WG_JOBS_WIDE;
+    if (j < 2) { mat = 0; is_pa = j == 0; mt0 = 0; nh = 2; }
+    else if (j < 7) { mat = j - 1; mt0 = 0; nh = 2; }
+    else { mat = 6 + (j - 7) / 2; mt0 = (j - 7) & 1; nh = 1; }
+  } else {
+    l = blockIdx.x / WG_JOBS;
+    const int jk = blockIdx.x % WG_JOBS;
+    mat = jk < 4 ? 0 : 1 + (jk - 4) / 2;
+    mt0 = jk < 4 ? (jk & 1) : ((jk - 4) & 1);
+    is_pa = jk < 2;
+    nh = 1;
+  }
+  const int gwhich = mat == 0 ? (is_pa ? TT_G_PA : TT_G_PB) : (mat <= 5 ? TT_G_V2 + (mat - 1) : TT_G_C0 + (mat - 6));
   const int awhich = mat == 0 ? TT_A_H2 : (mat == 1 ? TT_A_U2 : (mat == 2 ? TT_A_H1 : (mat == 3 ? TT_A_U1 : TT_A_H0)));
   const int N = mat == 5 ? 16 : (mat >= 6 ? TT_CIMG_COLS : 256);
   const uint32_t abytes = mat == 5 ? TT_XT : (mat >= 6 ? TT_CIMG : WG_ABYTES);
-  const uint8_t* gsrc = a.gimg + tt_img_off(l, gwhich, TT_NG, 0, a.tiles) + (size_t)mt * WG_GBYTES;
+  const uint8_t* gsrc = a.gimg + tt_img_off(l, gwhich, TT_NG, 0, a.tiles) + (size_t)mt0 * WG_GBYTES;
   const uint8_t* asrc = mat == 5 ? a.xt + (size_t)l * a.tiles * TT_XT
                                  : (mat >= 6 ? a.cimg : a.img + tt_img_off(l, awhich, TT_NA, 0, a.tiles));
   const size_t astride = mat == 5 ? TT_XT : (mat >= 6 ? TT_CIMG : TT_IMG);
+  const uint32_t aslot = mat >= 6 ? TT_CIMG : WG_ABYTES;      // ring geometry of this job
+  const int ng = nh == 2 ? WG_NG : 2;
+  uint8_t* const gring = smem + WG_NA * aslot;
+  const int units = a.tiles * nh;                             // (tile, gradient block) pairs, tile-major
 
   if (tid == 0) {
-    for (int i = 0; i < WG_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 5); }
+    for (int i = 0; i < WG_NA; ++i) { mbar_init(&afull[i], 1); mbar_init(&aempty[i], 1); }
+    for (int i = 0; i < WG_NG; ++i) { mbar_init(&gfull[i], 1); mbar_init(&gempty[i], 5); }
     mbar_init(acc_bar, 1);
     *abort_s = 0;
     fence_mbar_init();
@@ -694,12 +725,14 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
     // 16-byte load (a quarter warp covers one 128-byte core matrix: conflict-free), keeps 8 partial column sums, and the
     // 8 threads of a column group are reduced by shuffles once per tile
     const int cg = m >> 3, r8 = m & 7;
-    float bs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float bs[2][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) bs[0][i] = bs[1][i] = 0.f;
     uint32_t st = 0, par = 0;
     bool ok = true;
-    for (int t = 0; t < a.tiles && ok; ++t) {
-      if (!(ok = wait(&full[st], par, 70))) break;
-      const uint8_t* gb = smem + st * WG_STAGE + (size_t)cg * 2048 + r8 * 16;
+    for (int u = 0; u < units && ok; ++u) {
+      if (!(ok = wait(&gfull[st], par, 70))) break;
+      const uint8_t* gb = gring + st * WG_GBYTES + (size_t)cg * 2048 + r8 * 16;
       float ps[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll 4
       for (int rg = 0; rg < 16; ++rg) {
@@ -710,27 +743,30 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
         ps[6] += __uint_as_float(w.w << 16); ps[7] += __uint_as_float(w.w & 0xffff0000u);
       }
       __syncwarp();
-      if (lane == 0) mbar_arrive(&empty[st]);         // shared memory is no longer read: the stage may be refilled
+      if (lane == 0) mbar_arrive(&gempty[st]);        // shared memory is no longer read: the block may be refilled
+      const bool second = nh == 2 && (u & 1);
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         float v = ps[i];
         v += __shfl_xor_sync(0xffffffffu, v, 1);
         v += __shfl_xor_sync(0xffffffffu, v, 2);
         v += __shfl_xor_sync(0xffffffffu, v, 4);
-        bs[i] += v;
+        if (second) bs[1][i] += v; else bs[0][i] += v;
       }
-      if (++st == WG_STAGES) { st = 0; par ^= 1; }
+      if (++st == (uint32_t)ng) { st = 0; par ^= 1; }
     }
     // thread m needs the sum of column m: column group m / 8, element m % 8 -- held (identically) by the 8 threads of
     // that group: pick it with a shuffle from lane (m / 8 % 4) * 8 of this warp ... the group lives in this very warp
-    float bsum = 0.f;
+    float bsum2[2] = {0.f, 0.f};
     {
       const int src_lane = ((m >> 3) & 3) * 8;      // any lane of column group m / 8 (all eight hold the same sums)
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float v = __shfl_sync(0xffffffffu, bs[i], src_lane);
-        if ((m & 7) == i) bsum = v;
-      }
+      for (int h = 0; h < 2; ++h)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float v = __shfl_sync(0xffffffffu, bs[h][i], src_lane);
+          if ((m & 7) == i) bsum2[h] = v;
+        }
     }
     if (ok) ok = wait(acc_bar, 0, 71);
     tc_fence_after();
@@ -739,12 +775,15 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
     // different rows of the gradient (32 sectors per instruction, and a permuted column on top).  The block is staged in
     // the (now idle) operand stages as S[row][column in nflows' order], row pitch N + 1 floats (conflict-free both ways),
     // then each warp walks whole rows with consecutive lanes on consecutive columns.
-    bar_sync(1, 128);                               // every epilogue warp is done reading the last operand stage
     const bool go = ok && !*abort_s;
     float* S = reinterpret_cast<float*>(smem);
     const int ldS = N + 1;
     float** rowptr = reinterpret_cast<float**>(smem + WG_OFF_EPI);
     int* roww = reinterpret_cast<int*>(smem + WG_OFF_EPI + 128 * sizeof(float*));
+    for (int h = 0; h < nh; ++h) {
+    const int mt = mt0 + h;
+    const float bsum = h == 0 ? bsum2[0] : bsum2[1];
+    bar_sync(1, 128);         // every epilogue warp is done reading the last operand block / the previous block's staging
     if (go) {
       const pf_layer_grads& g = a.g[l];
       const int gm = mt * 128 + m;                  // column within the gradient image
@@ -753,7 +792,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
       float* bdst = nullptr;
       int wr = -1;                                  // row index in nflows' space (mask rule)
       if (mat == 0) {
-        const int first = jk < 2 ? 1 : 1 + s.ga, cnt = jk < 2 ? s.ga : s.gb;
+        const int first = is_pa ? 1 : 1 + s.ga, cnt = is_pa ? s.ga : s.gb;
         if (gm / TT_PCOL < cnt && gm % TT_PCOL < TT_MULT) {
           wr = (first + gm / TT_PCOL) * TT_MULT + gm % TT_PCOL;
           if (g.final_w) wrow = g.final_w + (size_t)wr * TT_H;
@@ -779,7 +818,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
       rowptr[m] = wrow;
       // threshold of the mask comparison (see the write-back below); rows without a destination never pass it
       roww[m] = mat >= 6 ? 0 : (mat == 0 ? (wr >= 0 ? wr / TT_MULT : -1) : hidden_degree(wr, s.D));
-      const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16);
+      const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)h * 256u;
       float* srow = S + (size_t)m * ldS;
       for (int c0 = 0; c0 < N; c0 += 16) {
         uint32_t v[16];
@@ -831,6 +870,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
         }
       }
     }
+    }      // blocks of the job
   } else if (warp == 4) {
     // ---- MMA issuer ----
     const int NH = mat >= 6 ? N / 2 : N;              // the context image is 288 columns wide: two N = 144 instructions
@@ -839,39 +879,56 @@ __global__ void __launch_bounds__(WG_THREADS, 1) tt_wgrad_kernel(const TtWgArgs 
     uint32_t st = 0, par = 0;
     bool ok = true;
     for (int t = 0; t < a.tiles && ok; ++t) {
-      if (!(ok = wait(&full[st], par, 72))) break;
-      tc_fence_after();
-      const uint32_t gb = smem_u32(smem + st * WG_STAGE), ab = gb + WG_GBYTES;
-      if (elect_one_sync()) {
+      const uint32_t as = (uint32_t)t & 1u;
+      if (!(ok = wait(&afull[as], ((uint32_t)t >> 1) & 1u, 72))) break;
+      const uint32_t ab = smem_u32(smem + as * aslot);
+      for (int h = 0; h < nh && ok; ++h) {
+        if (!(ok = wait(&gfull[st], par, 74))) break;
+        tc_fence_after();
+        const uint32_t gb = smem_u32(gring + st * WG_GBYTES);
+        if (elect_one_sync()) {
+          const uint32_t acc = tmem + (uint32_t)h * 256u;
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks) {
-          const uint64_t ad = umma_smem_desc(gb + (uint32_t)ks * 256u, lbo, sbo);
-          const uint64_t bd = umma_smem_desc(ab + (uint32_t)ks * 256u, lbo, sbo);
-          umma_ss(tmem, ad, bd, idesc, (t > 0 || ks > 0) ? 1u : 0u);
-          if (mat >= 6) {     // columns NH .. 2 NH - 1: NH / 8 column groups further into the image
-            const uint64_t bd2 = umma_smem_desc(ab + (uint32_t)(NH / 8) * 2048u + (uint32_t)ks * 256u, lbo, sbo);
-            umma_ss(tmem + (uint32_t)NH, ad, bd2, idesc, (t > 0 || ks > 0) ? 1u : 0u);
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint64_t ad = umma_smem_desc(gb + (uint32_t)ks * 256u, lbo, sbo);
+            const uint64_t bd = umma_smem_desc(ab + (uint32_t)ks * 256u, lbo, sbo);
+            umma_ss(acc, ad, bd, idesc, (t > 0 || ks > 0) ? 1u : 0u);
+            if (mat >= 6) {     // columns NH .. 2 NH - 1: NH / 8 column groups further into the image
+              const uint64_t bd2 = umma_smem_desc(ab + (uint32_t)(NH / 8) * 2048u + (uint32_t)ks * 256u, lbo, sbo);
+              umma_ss(acc + (uint32_t)NH, ad, bd2, idesc, (t > 0 || ks > 0) ? 1u : 0u);
+            }
+          }
+          umma_commit(&gempty[st]);
+          if (h + 1 == nh) {
+            umma_commit(&aempty[as]);
+            if (t + 1 == a.tiles) umma_commit(acc_bar);
           }
         }
-        umma_commit(&empty[st]);
-        if (t + 1 == a.tiles) umma_commit(acc_bar);
+        __syncwarp();
+        if (++st == (uint32_t)ng) { st = 0; par ^= 1; }
       }
-      __syncwarp();
-      if (++st == WG_STAGES) { st = 0; par ^= 1; }
     }
   } else {
     // ---- loader ----
     uint32_t st = 0, par = 1;
     bool ok = true;
     for (int t = 0; t < a.tiles && ok; ++t) {
-      if (!(ok = wait(&empty[st], par, 73))) break;
+      const uint32_t as = (uint32_t)t & 1u;
+      if (!(ok = wait(&aempty[as], (((uint32_t)t >> 1) & 1u) ^ 1u, 73))) break;
       if (elect_one_sync()) {
-        mbar_arrive_expect_tx(&full[st], WG_GBYTES + abytes);
-        bulk_g2s(smem + st * WG_STAGE, gsrc + (size_t)t * TT_IMG, WG_GBYTES, &full[st]);
-        bulk_g2s(smem + st * WG_STAGE + WG_GBYTES, asrc + (size_t)t * astride, abytes, &full[st]);
+        mbar_arrive_expect_tx(&afull[as], abytes);
+        bulk_g2s(smem + as * aslot, asrc + (size_t)t * astride, abytes, &afull[as]);
       }
       __syncwarp();
-      if (++st == WG_STAGES) { st = 0; par ^= 1; }
+      for (int h = 0; h < nh && ok; ++h) {
+        if (!(ok = wait(&gempty[st], par, 75))) break;
+        if (elect_one_sync()) {
+          mbar_arrive_expect_tx(&gfull[st], WG_GBYTES);
+          bulk_g2s(gring + st * WG_GBYTES, gsrc + (size_t)t * TT_IMG + (size_t)h * WG_GBYTES, WG_GBYTES, &gfull[st]);
+        }
+        __syncwarp();
+        if (++st == (uint32_t)ng) { st = 0; par ^= 1; }
+      }
     }
   }
   tc_fence_before();
@@ -1404,7 +1461,9 @@ pf_status pf_tt_wgrad(pf_flow* f, cudaStream_t st, const TtSaved& sv, const TtWo
   a.mn_swap = sw && sw[0] == '1';
   a.err = f->tg_err;
   for (int l = 0; l < f->L; ++l) a.g[l] = grads[l];
-  tt_wgrad_kernel<<<f->L * WG_JOBS, WG_THREADS, WG_SMEM, st>>>(a);
+  static const bool wide = [] { const char* e = getenv("PF_WGRAD_WIDE"); return !(e && e[0] == '0'); }();
+  a.wide = wide ? 1 : 0;
+  tt_wgrad_kernel<<<f->L * (wide ? WG_JOBS_WIDE : WG_JOBS), WG_THREADS, WG_SMEM, st>>>(a);
   PF_LAUNCH_CHECK(f);
   return PF_OK;
 }
