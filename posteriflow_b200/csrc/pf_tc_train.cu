@@ -1336,12 +1336,23 @@ pf_status pf_tt_ctxproj(pf_flow* f, cudaStream_t st, const float* ctx, int64_t R
   a.CK = t->CK;
   a.NB = f->L * 3;
   a.tiles = tiles;
-  // column-block groups per tile: enough CTAs for ~2 waves of the SMs, never more groups than blocks
-  int groups = (2 * f->sm_count + tiles - 1) / tiles;
-  if (groups < 1) groups = 1;
-  if (groups > a.NB) groups = a.NB;
-  a.nb_per_cta = (a.NB + groups - 1) / groups;
-  groups = (a.NB + a.nb_per_cta - 1) / a.nb_per_cta;
+  // Column blocks per CTA: one CTA per SM (shared memory), so the launch runs in ceil(CTAs / SMs) waves of
+  // (blocks per CTA + a fixed part: context image load, pipeline fill, last epilogue ~ 0.3 blocks) each.  "About two
+  // waves" used to give 300 CTAs for 60 tiles (and for 20): 2.03 waves = three, the last one with 4 CTAs.  Take the
+  // split with the lowest modelled time instead.
+  int best_nb = a.NB;
+  {
+    double best = 1e30;
+    for (int nb = 1; nb <= a.NB; ++nb) {
+      const int g = (a.NB + nb - 1) / nb;
+      const int64_t ctas = (int64_t)tiles * g;
+      const int64_t waves = (ctas + f->sm_count - 1) / f->sm_count;
+      const double cost = (double)waves * ((double)nb + 0.3);
+      if (cost < best - 1e-9) { best = cost; best_nb = nb; }
+    }
+  }
+  a.nb_per_cta = best_nb;
+  const int groups = (a.NB + a.nb_per_cta - 1) / a.nb_per_cta;
   a.err = f->tg_err;
   tt_ctxproj_kernel<<<dim3(tiles, groups), CP_THREADS, CP_SMEM, st>>>(a);
   PF_LAUNCH_CHECK(f);
