@@ -1,5 +1,6 @@
 """GPU parity of the LeanNPE glue (ParamScaler epilogue, rank embedding, context broadcast, rail mask)
 and size-independent properties of the flow at larger sizes."""
+import math
 import numpy as np
 import pytest
 import torch
@@ -313,3 +314,91 @@ def test_compact_rows_form_with_empty_events_and_a_long_prefix_sum(B):
     assert float((a[2] - b[2]).abs().max()) <= 1e-5 * float(a[2].abs().max())
     for ga, gb in zip(a[3], b[3]):      # row order differs (rank-major vs event-major): atomics / tile sums in another order
         assert float((ga - gb).abs().max()) <= 2e-5 * max(1e-12, float(ga.abs().max()))
+
+
+@pytest.mark.parametrize("B,S", [(1, 1), (7, 5), (1030, 5), (300, 3)])
+def test_glue_entry_points_against_torch(B, S):
+    """pf_slot_prepare / pf_rows_prepare / pf_slot_loss / pf_slot_ctx_grad / pf_rows_ctx_grad called through the C-ABI on raw
+    buffers, against the torch expressions they replace (train_lean_npe.py:108-127, lean_npe.py:100-109, 296-304): slot and
+    compact layouts, events without a signal, nsig beyond S, padding rows, both normalisations (local count / external)."""
+    import ctypes as C_
+    from posteriflow_b200 import _cabi as A
+    from posteriflow_b200.ops import _scaler_struct
+    lib = A.load_library()
+    dev = torch.device("cuda")
+    g = torch.Generator().manual_seed(B * 10 + S)
+    sc = O.Scaler()
+    D, cd, Cc = 11, 256, 288
+    nsig = torch.randint(0, S + 3, (B,), generator=g)
+    if B > 2:
+        nsig[0] = 0
+    if int(nsig.clamp(max=S).sum()) == 0:
+        nsig[-1] = 1
+    n = nsig.clamp(max=S)
+    params = sc.denormalize(torch.rand(B, S, D, generator=g) * 2 - 1)
+    ctx = torch.randn(B, cd, generator=g)
+    emb = torch.randn(S + 1, Cc - cd, generator=g)               # one spare row, as LeanNPE's embedding may have
+    pd, nd, cdv, ed = params.to(dev), nsig.to(dev), ctx.to(dev), emb.to(dev)
+    sstruct, keep = _scaler_struct(sc.lo.to(dev), sc.hi.to(dev), sc.log_mask.to(dev), sc.circ_mask.to(dev))
+    inv_ext = torch.tensor(0.125, device=dev)
+    xn = sc.normalize(params)                                   # [B, S, D]
+    R = int(n.sum())
+    for use_ext in (0.0, 1.0):
+        use = torch.tensor(use_ext, device=dev)
+        inv = 0.125 if use_ext else 1.0 / max(1, R)
+        # ---- slot layout ----
+        x = torch.full((B * S, D), 7.0, device=dev)
+        cf = torch.full((B * S, Cc), 7.0, device=dev)
+        w = torch.full((B * S,), 7.0, device=dev)
+        A.check(lib.pf_slot_prepare(pd.data_ptr(), nd.data_ptr(), cdv.data_ptr(), ed.data_ptr(), C_.byref(sstruct),
+                                    inv_ext.data_ptr(), use.data_ptr(), B, S, D, cd, Cc, x.data_ptr(), cf.data_ptr(),
+                                    w.data_ptr(), 0, None), "pf_slot_prepare")
+        present = (torch.arange(S)[None, :] < n[:, None])        # [B, S]
+        assert torch.allclose(x.cpu().view(B, S, D), xn * present[..., None], atol=2e-6)
+        assert torch.equal(cf.cpu().view(B, S, Cc)[..., :cd], ctx[:, None, :].expand(B, S, cd))
+        assert torch.equal(cf.cpu().view(B, S, Cc)[..., cd:], emb[None, :S, :].expand(B, S, Cc - cd))
+        assert torch.allclose(w.cpu().view(B, S), present.float() * inv, rtol=1e-6, atol=0)
+        # ---- compact layout, padded to a bucket ----
+        cap = (R + 127) // 128 * 128
+        offs = torch.zeros(B + 1, dtype=torch.int32, device=dev)
+        x2 = torch.full((cap, D), 7.0, device=dev)
+        cf2 = torch.zeros(cap, Cc, device=dev)
+        w2 = torch.full((cap,), 7.0, device=dev)
+        A.check(lib.pf_rows_prepare(pd.data_ptr(), nd.data_ptr(), cdv.data_ptr(), ed.data_ptr(), C_.byref(sstruct),
+                                    inv_ext.data_ptr(), use.data_ptr(), B, S, D, cd, Cc, cap, offs.data_ptr(), x2.data_ptr(),
+                                    cf2.data_ptr(), w2.data_ptr(), 0, None), "pf_rows_prepare")
+        ref_offs = torch.cat([torch.zeros(1, dtype=torch.long), n.cumsum(0)])
+        assert torch.equal(offs.cpu().long(), ref_offs)
+        ev = torch.repeat_interleave(torch.arange(B), n)
+        rk = torch.cat([torch.arange(int(k)) for k in n]) if R else torch.zeros(0, dtype=torch.long)
+        assert torch.allclose(x2.cpu()[:R], xn[ev, rk], atol=2e-6) and float(x2[R:].abs().max() if cap > R else 0) == 0.0
+        assert torch.equal(cf2.cpu()[:R], torch.cat([ctx[ev], emb[rk]], dim=1))
+        assert torch.allclose(w2.cpu()[:R], torch.full((R,), inv), rtol=1e-6, atol=0)
+        assert cap == R or float(w2[R:].abs().max()) == 0.0
+        # ---- loss + first backward step on the compact rows ----
+        z = torch.randn(cap, D, generator=g).to(dev)
+        ld = torch.randn(cap, generator=g).to(dev)
+        loss = torch.zeros(1, device=dev)
+        gz = torch.empty(cap, D, device=dev)
+        gl = torch.empty(cap, device=dev)
+        A.check(lib.pf_slot_loss(z.data_ptr(), ld.data_ptr(), w2.data_ptr(), cap, D, loss.data_ptr(), gz.data_ptr(),
+                                 gl.data_ptr(), 0, None), "pf_slot_loss")
+        nll = 0.5 * (z.double() ** 2).sum(1) + 0.5 * D * math.log(2 * math.pi) - ld.double()
+        ref_loss = float((nll * w2.double()).sum())
+        assert abs(float(loss) - ref_loss) <= 1e-5 * max(1.0, abs(ref_loss))
+        assert torch.allclose(gz, z * w2[:, None]) and torch.equal(gl, -w2)
+        # ---- context / embedding gradients: compact and slot ----
+        gfull = torch.randn(cap, Cc, generator=g).to(dev)
+        gfull[R:] = 0
+        gc = torch.full((B, cd), 7.0, device=dev)
+        ge = torch.full((S, Cc - cd), 7.0, device=dev)
+        A.check(lib.pf_rows_ctx_grad(gfull.data_ptr(), offs.data_ptr(), B, S, cd, Cc, gc.data_ptr(), ge.data_ptr(), 0, None),
+                "pf_rows_ctx_grad")
+        ref_gc = torch.zeros(B, cd, dtype=torch.float64).index_add_(0, ev, gfull.cpu()[:R, :cd].double())
+        ref_ge = torch.zeros(S, Cc - cd, dtype=torch.float64).index_add_(0, rk, gfull.cpu()[:R, cd:].double())
+        assert torch.allclose(gc.cpu().double(), ref_gc, atol=1e-5) and torch.allclose(ge.cpu().double(), ref_ge, atol=2e-4)
+        gslot = torch.randn(B * S, Cc, generator=g).to(dev)
+        A.check(lib.pf_slot_ctx_grad(gslot.data_ptr(), B, S, cd, Cc, gc.data_ptr(), ge.data_ptr(), 0, None), "pf_slot_ctx_grad")
+        assert torch.allclose(gc.cpu().double(), gslot.cpu().double().view(B, S, Cc)[..., :cd].sum(1), atol=1e-5)
+        assert torch.allclose(ge.cpu().double(), gslot.cpu().double().view(B, S, Cc)[..., cd:].sum(0), atol=2e-4)
+    torch.cuda.synchronize()
