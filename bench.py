@@ -338,6 +338,7 @@ def run_ours(args):
     sc_cpu = P.ParamScaler()
     params_b = sc_cpu.denormalize(torch.rand(Bt, 5, D, generator=g) * 2 - 1).to(dev)   # [B, max_signals, 11] physical
     nsig_dev = nsig.to(dev)
+    nsig_pin = nsig.clone().pin_memory()
     tctx = torch.randn(Bt, 256, generator=g).to(dev).requires_grad_(True)
     ev, rk = ev.to(dev), rk.to(dev)
     params = [p for p in model.parameters() if p.requires_grad]
@@ -356,7 +357,7 @@ def run_ours(args):
         for p in params:
             p.grad = None
         tctx.grad = None
-        loss = gstep(params_b, nsig_dev, tctx)
+        loss = gstep(params_b, nsig_pin, tctx)        # nsig as the data loader leaves it (pinned host): compact rows form
         counted["kernels"] += gstep.last_launches
         if world > 1:
             gstep.allreduce(extra_params=other_params)
@@ -536,7 +537,7 @@ def run_ours(args):
                   "full_batch_1gpu": full,
                   "api": "posteriflow_b200.GraphedNLLStep (batch_nll forward + backward captured in one CUDA graph per "
                          "row bucket)",
-                  "includes": "batch_nll (one flow call for all signal ranks): row gather, scaler.normalize, rank embedding, flow "
+                  "includes": "batch_nll (one flow call for all signal ranks; nsig handed over as a pinned HOST tensor, as a data loader leaves it, so the compact rows form needs no device sync for the row count): row gather, scaler.normalize, rank embedding, flow "
                               "forward+backward (all weights, context), "
                               + ("NCCL gradient all-reduce" if world > 1 else "no all-reduce at 1 GPU")
                               + "; EXCLUDED: the strain encoder (north_star leaves it in PyTorch; synthetic N(0,1) contexts of "

@@ -92,7 +92,8 @@ class GraphedNLLStep:
     size.  Absent slots carry weight zero and x = 0 (their parameters are never read): they add
     exactly nothing to the loss and to every gradient.
 
-    **Compact rows form** (`compact=True`, the default for batches beyond one wave): only the present pairs become flow
+    **Compact rows form** (`compact=True`; the default for batches beyond one wave, and for EVERY batch whose `nsig` is
+    passed as a host tensor -- the row count then needs no device sync): only the present pairs become flow
     rows, but WHICH pair a row is gets worked out on the device inside the graph (prefix sum of nsig, `pf_rows_prepare` /
     `pf_rows_ctx_grad` of csrc/pf_glue.cu), so the ATen gather around the replay goes away here too; the host reads the
     row count only, to choose the bucket.  `compact=False` keeps the gather with ATen (the form the first paragraph
@@ -345,6 +346,14 @@ class GraphedNLLStep:
         m = self.model
         if context.is_cuda:
             self._ensure_packed()
+            if self.compact and not nsig.is_cuda and self.slots is not True and self.model.flow.handle().fused_training:
+                # `nsig` still on the HOST (where a data loader leaves it): the row count costs no device sync, so the
+                # compact form is free -- and it gives the three streaming kernels (context projection, weight gradients,
+                # d ctx) ~1.9 B rows instead of the max_signals x B slots of slot mode (8 tiles instead of 20 at B = 512)
+                R = int(nsig.clamp(0, int(m.max_signals)).sum())
+                if R > 0:
+                    cap = (R + self.bucket - 1) // self.bucket * self.bucket
+                    return self._call_slots(params, nsig.to(context.device, non_blocking=True), context, compact_cap=cap)
             if self._use_slots(int(context.shape[0]), context.device):
                 return self._call_slots(params, nsig.to(context.device), context)
             if self.compact:

@@ -402,3 +402,34 @@ def test_glue_entry_points_against_torch(B, S):
         assert torch.allclose(gc.cpu().double(), gslot.cpu().double().view(B, S, Cc)[..., :cd].sum(1), atol=1e-5)
         assert torch.allclose(ge.cpu().double(), gslot.cpu().double().view(B, S, Cc)[..., cd:].sum(0), atol=2e-4)
     torch.cuda.synchronize()
+
+
+def test_host_nsig_takes_the_compact_form_and_matches_slot_mode():
+    """`nsig` left on the host (data loader): GraphedNLLStep takes the compact rows form without a device sync -- same loss
+    and gradients as the slot-mode step the device tensor gets."""
+    import posteriflow_b200 as P
+    spec, w, g = load_golden("lean_glue")
+    m = lean_model(w, g, tier="bf16")
+    sc = O.Scaler()
+    gen = torch.Generator().manual_seed(21)
+    B = 200
+    nsig = torch.multinomial(torch.tensor([.55, .20, .12, .08, .05]), B, replacement=True, generator=gen) + 1
+    nsig[3] = 0
+    params = sc.denormalize(torch.rand(B, 5, 11, generator=gen) * 2 - 1).cuda()
+    ctx = torch.randn(B, 256, generator=gen)
+    out = {}
+    for where in ("device", "host"):
+        step = P.GraphedNLLStep(m)
+        m.zero_grad(set_to_none=True)
+        c = ctx.cuda().requires_grad_(True)
+        loss = step(params, nsig.cuda() if where == "device" else nsig.pin_memory(), c)
+        keys = list(step.slot_graphs)
+        assert len(keys) == 1 and isinstance(keys[0], tuple) == (where == "host")      # (B, cap) = compact, B = slots
+        out[where] = (float(loss), c.grad.clone(), m.rank_embed.weight.grad.clone(),
+                      [p.grad.clone() for p in m.flow.layer_weights()])
+    a, b = out["device"], out["host"]
+    assert abs(a[0] - b[0]) <= 1e-5 * max(1.0, abs(a[0]))
+    assert float((a[1] - b[1]).abs().max()) <= 1e-5 * float(a[1].abs().max())
+    assert float((a[2] - b[2]).abs().max()) <= 1e-5 * float(a[2].abs().max())
+    for ga, gb in zip(a[3], b[3]):
+        assert float((ga - gb).abs().max()) <= 2e-5 * max(1e-12, float(ga.abs().max()))
