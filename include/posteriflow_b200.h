@@ -239,7 +239,8 @@ pf_status pf_slot_prepare(const float* params, const int64_t* nsig, const float*
 
 /* Replaces `loss = (nll * w).sum()` of the same function with nll = compute_psd_aware_nll(log_sigma = 0)
  * (flows.py:727-779) and the first step of its backward: loss[0] = sum_r w_r (0.5 (|z_r|^2 + D log 2 pi) - logdet_r),
- * gz[r, :] = w_r z[r, :], glogdet[r] = -w_r.  One block, fixed reduction tree (deterministic). */
+ * gz[r, :] = w_r z[r, :], glogdet[r] = -w_r.  One cluster of eight CTAs, partial sums combined
+ * through distributed shared memory in a fixed order (deterministic, no scratch, no atomics). */
 pf_status pf_slot_loss(const float* z, const float* logdet, const float* w, int64_t rows, int32_t D, float* loss, float* gz,
                        float* glogdet, int32_t device, void* stream);
 
